@@ -1,0 +1,300 @@
+// extern "C" entry points declared in include/gsr.h: argument checks, workspace carving, stage ordering.
+// Orchestration counterpart of the reference's CudaRasterizer::Rasterizer (rasterizer_impl.cu:197-447).
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+#include "../../include/gsr.h"
+#include "gsr_kernels.h"
+
+using namespace gsr;
+
+namespace {
+
+thread_local char g_err[512] = "";
+
+int fail(int code, const char* fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+// After each stage: launch-error check always; full synchronise + check when debug (reference CHECK_CUDA).
+#define GSR_STAGE(name)                                                                           \
+    do {                                                                                          \
+        cudaError_t e_ = cudaGetLastError();                                                      \
+        if (e_ == cudaSuccess && debug) e_ = cudaStreamSynchronize(s);                            \
+        if (e_ != cudaSuccess) return fail(GSR_ERR_CUDA, "%s: %s", name, cudaGetErrorString(e_)); \
+    } while (0)
+
+int tile_bits(int tiles)
+{
+    int bits = 0;
+    while ((1 << bits) < tiles) bits++;
+    return bits < 1 ? 1 : bits;
+}
+
+}  // namespace
+
+extern "C" {
+
+int gsr_version(void) { return 1000; }
+
+const char* gsr_last_error(void) { return g_err; }
+
+size_t gsr_geometry_bytes(int P)
+{
+    GeomView g;
+    return geom_layout(nullptr, P > 0 ? P : 1, g);
+}
+
+size_t gsr_image_bytes(int W, int H)
+{
+    ImageView v;
+    return image_layout(nullptr, W, H, v);
+}
+
+size_t gsr_binning_bytes(int64_t num_rendered, int W, int H)
+{
+    (void)W; (void)H;
+    BinView b;
+    return bin_layout(nullptr, num_rendered, b);
+}
+
+size_t gsr_pose_scratch_bytes(int P) { return (size_t)pose_blocks(P > 0 ? P : 1) * 6 * sizeof(float); }
+
+int gsr_forward_prepare(int P, int sh_degree, int M, const float* means3D, const float* scales,
+                        float scale_modifier, const float* rotations, const float* opacities,
+                        const float* shs, const float* cov3D_precomp, const float* colors_precomp,
+                        const float* viewmatrix, const float* projmatrix, const float* campos, int W, int H,
+                        float tanfovx, float tanfovy, int prefiltered, int* radii, void* geometry,
+                        size_t geometry_bytes, int64_t* num_rendered_host, void* stream, int debug)
+{
+    cudaStream_t s = (cudaStream_t)stream;
+    if (!num_rendered_host) return fail(GSR_ERR_INVALID, "num_rendered_host is NULL");
+    *num_rendered_host = 0;
+    if (P < 0 || W <= 0 || H <= 0) return fail(GSR_ERR_INVALID, "bad sizes P=%d W=%d H=%d", P, W, H);
+    if (P == 0) return GSR_OK;  // rasterize_points.cu:83 -- nothing launched
+    if (!means3D || !opacities || !viewmatrix || !projmatrix || !radii || !geometry)
+        return fail(GSR_ERR_INVALID, "means3D, opacities, matrices, radii and geometry workspace are required");
+    if ((shs == nullptr) == (colors_precomp == nullptr))
+        return fail(GSR_ERR_INVALID, "provide exactly one of SHs or precomputed colors");
+    if (((scales == nullptr) || (rotations == nullptr)) == (cov3D_precomp == nullptr))
+        return fail(GSR_ERR_INVALID, "provide exactly one of scale/rotation pair or precomputed 3D covariance");
+    if (shs && (sh_degree < 0 || sh_degree > 3 || (sh_degree + 1) * (sh_degree + 1) > M))
+        return fail(GSR_ERR_INVALID, "sh_degree %d needs %d coefficients, M=%d", sh_degree,
+                    (sh_degree + 1) * (sh_degree + 1), M);
+    if (shs && !campos) return fail(GSR_ERR_INVALID, "campos is required with SHs");
+    if (div_up(W, TILE) > 65535 || div_up(H, TILE) > 65535) return fail(GSR_ERR_INVALID, "image too large");
+    GeomView g;
+    if (gsr_geometry_bytes(P) > geometry_bytes)
+        return fail(GSR_ERR_WORKSPACE, "geometry workspace too small: %zu < %zu", geometry_bytes, gsr_geometry_bytes(P));
+    geom_layout((char*)geometry, P, g);
+
+    PreprocessArgs a;
+    a.P = P; a.D = sh_degree; a.M = M;
+    a.means3D = means3D; a.scales = scales; a.scale_modifier = scale_modifier; a.rotations = rotations;
+    a.opacities = opacities; a.shs = shs; a.cov3D_precomp = cov3D_precomp; a.colors_precomp = colors_precomp;
+    a.viewmatrix = viewmatrix; a.projmatrix = projmatrix; a.campos = campos ? campos : viewmatrix;
+    a.W = W; a.H = H; a.tanfovx = tanfovx; a.tanfovy = tanfovy; a.prefiltered = prefiltered; a.radii = radii;
+    launch_preprocess(a, g, s);
+    GSR_STAGE("preprocess");
+
+    // "how many instances?" travels to the host (8 bytes, into the caller's -- ideally pinned -- word) while
+    // the GPU keeps sorting; bit 62 of the counter flags a prefilter violation
+    cudaEvent_t ev;
+    cudaError_t e = cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
+    if (e != cudaSuccess) return fail(GSR_ERR_CUDA, "event: %s", cudaGetErrorString(e));
+    cudaMemcpyAsync(num_rendered_host, g.counters, sizeof(int64_t), cudaMemcpyDeviceToHost, s);
+    cudaEventRecord(ev, s);
+
+    // low 32 key bits (depth) sorted over Gaussians, before duplication
+    launch_init_sort_input(g, P, s);
+    const int cur = radix_sort_pairs(g.sort_keys, g.sort_vals, P, 0, 32, g.hist, g.digit_total, s);
+    if (cur != 0) {  // keep the invariant "sort_vals[0] holds the depth order"
+        cudaMemcpyAsync(g.sort_vals[0], g.sort_vals[1], sizeof(uint32_t) * (size_t)P, cudaMemcpyDeviceToDevice, s);
+    }
+    launch_offsets_scan(g.tiles, g.sort_vals[0], g.offsets, g.block_sums, P, s);
+
+    e = cudaEventSynchronize(ev);
+    cudaEventDestroy(ev);
+    if (e != cudaSuccess) return fail(GSR_ERR_CUDA, "preprocess/count: %s", cudaGetErrorString(e));
+    GSR_STAGE("depth sort + offsets");
+    const unsigned long long raw = (unsigned long long)*num_rendered_host;
+    *num_rendered_host = 0;
+    if (raw >> 62) return fail(GSR_ERR_PREFILTER, "Point is filtered although prefiltered is set. This shouldn't happen!");
+    if (raw > 0x7fffffffull) return fail(GSR_ERR_OVERFLOW, "%llu tile instances", raw);
+    *num_rendered_host = (int64_t)raw;
+    return GSR_OK;
+}
+
+int gsr_forward_render(int P, int W, int H, int64_t num_rendered, const float* background,
+                       const float* colors_precomp, void* geometry, void* binning, size_t binning_bytes,
+                       void* image, float* out_color, float* out_depth, float* out_alpha, void* stream, int debug)
+{
+    cudaStream_t s = (cudaStream_t)stream;
+    (void)colors_precomp;
+    if (W <= 0 || H <= 0) return fail(GSR_ERR_INVALID, "bad image size");
+    if (!out_color || !out_depth || !out_alpha) return fail(GSR_ERR_INVALID, "outputs are required");
+    if (P == 0) {  // reference returns zero images without launching (rasterize_points.cu:68-71,83)
+        cudaMemsetAsync(out_color, 0, sizeof(float) * 3 * (size_t)W * H, s);
+        cudaMemsetAsync(out_depth, 0, sizeof(float) * (size_t)W * H, s);
+        cudaMemsetAsync(out_alpha, 0, sizeof(float) * (size_t)W * H, s);
+        return GSR_OK;
+    }
+    if (!geometry || !binning || !image || !background)
+        return fail(GSR_ERR_INVALID, "workspaces and background are required");
+    if (gsr_binning_bytes(num_rendered, W, H) > binning_bytes)
+        return fail(GSR_ERR_WORKSPACE, "binning workspace too small: %zu < %zu", binning_bytes,
+                    gsr_binning_bytes(num_rendered, W, H));
+    GeomView g;
+    geom_layout((char*)geometry, P, g);
+    ImageView iv;
+    image_layout((char*)image, W, H, iv);
+    BinView b;
+    bin_layout((char*)binning, num_rendered, b);
+    const int gx = div_up(W, TILE), gy = div_up(H, TILE), tiles = gx * gy;
+
+    if (num_rendered > 0) {
+        launch_emit(g, g.sort_vals[0], P, gx, b.keys[0], b.vals[0], s);
+        GSR_STAGE("emit");
+        const int cur = radix_sort_pairs(b.keys, b.vals, num_rendered, 0, tile_bits(tiles), b.hist, b.digit_total, s);
+        if (cur != 0) {  // invariant: keys[0]/vals[0] hold the sorted list
+            cudaMemcpyAsync(b.keys[0], b.keys[1], sizeof(uint32_t) * (size_t)num_rendered, cudaMemcpyDeviceToDevice, s);
+            cudaMemcpyAsync(b.vals[0], b.vals[1], sizeof(uint32_t) * (size_t)num_rendered, cudaMemcpyDeviceToDevice, s);
+        }
+        GSR_STAGE("tile sort");
+    }
+    launch_tile_ranges(b.keys[0], num_rendered, iv.ranges, tiles, s);
+    GSR_STAGE("tile ranges");
+    launch_render_forward(W, H, iv.ranges, b.vals[0], g, background, out_color, out_depth, out_alpha, iv.n_contrib, s);
+    GSR_STAGE("render");
+    return GSR_OK;
+}
+
+int gsr_backward(int P, int sh_degree, int M, int W, int H, int64_t num_rendered, const float* background,
+                 const float* means3D, const int* radii, const float* colors_precomp, const float* scales,
+                 const float* rotations, float scale_modifier, const float* cov3D_precomp,
+                 const float* viewmatrix, const float* projmatrix, const float* campos, float tanfovx,
+                 float tanfovy, const float* shs, const float* out_alpha, const float* dL_dout_color,
+                 const float* dL_dout_depth, const float* dL_dout_alpha, const void* geometry,
+                 const void* binning, const void* image, void* grad_scratch, float* dL_dmeans2D,
+                 float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh,
+                 float* dL_dscales, float* dL_drotations, float* dL_dpose, void* pose_scratch, void* stream,
+                 int debug)
+{
+    cudaStream_t s = (cudaStream_t)stream;
+    if (P == 0) {
+        if (dL_dpose) cudaMemsetAsync(dL_dpose, 0, 6 * sizeof(float), s);
+        return GSR_OK;
+    }
+    if (!means3D || !radii || !viewmatrix || !projmatrix || !geometry || !binning || !image || !grad_scratch ||
+        !out_alpha || !dL_dout_color || !background)
+        return fail(GSR_ERR_INVALID, "required pointer is NULL");
+    if (!dL_dmeans2D || !dL_dopacity || !dL_dmeans3D) return fail(GSR_ERR_INVALID, "required gradient output is NULL");
+    if (colors_precomp && !dL_dcolors) return fail(GSR_ERR_INVALID, "dL_dcolors is required with colors_precomp");
+    if (shs && !dL_dsh) return fail(GSR_ERR_INVALID, "dL_dsh is required with shs");
+    if (scales && (!dL_dscales || !dL_drotations || !rotations))
+        return fail(GSR_ERR_INVALID, "dL_dscales/dL_drotations are required with scales");
+    if (cov3D_precomp && !dL_dcov3D) return fail(GSR_ERR_INVALID, "dL_dcov3D is required with cov3D_precomp");
+    if (dL_dpose && !pose_scratch) return fail(GSR_ERR_INVALID, "pose_scratch is required with dL_dpose");
+    GeomView g;
+    geom_layout((char*)geometry, P, g);
+    ImageView iv;
+    image_layout((char*)image, W, H, iv);
+    BinView b;
+    bin_layout((char*)binning, num_rendered, b);
+
+    cudaMemsetAsync(grad_scratch, 0, (size_t)P * 12 * sizeof(float), s);
+    if (num_rendered > 0) {
+        launch_render_backward(W, H, iv.ranges, b.vals[0], g, background, out_alpha, iv.n_contrib, dL_dout_color,
+                               dL_dout_depth, dL_dout_alpha, (float*)grad_scratch, s);
+        GSR_STAGE("render backward");
+    }
+    PreprocessBwdArgs a;
+    a.P = P; a.D = sh_degree; a.M = M;
+    a.means3D = means3D; a.radii = radii; a.shs = shs; a.scales = scales; a.rotations = rotations;
+    a.scale_modifier = scale_modifier; a.cov3D_precomp = cov3D_precomp; a.colors_precomp = colors_precomp;
+    a.viewmatrix = viewmatrix; a.projmatrix = projmatrix; a.campos = campos ? campos : viewmatrix;
+    a.W = W; a.H = H; a.tanfovx = tanfovx; a.tanfovy = tanfovy;
+    a.grad_scratch = (const float*)grad_scratch;
+    a.dL_dmeans2D = dL_dmeans2D; a.dL_dcolors = colors_precomp ? dL_dcolors : nullptr; a.dL_dopacity = dL_dopacity;
+    a.dL_dmeans3D = dL_dmeans3D; a.dL_dcov3D = dL_dcov3D; a.dL_dsh = shs ? dL_dsh : nullptr;
+    a.dL_dscales = scales ? dL_dscales : nullptr; a.dL_drotations = scales ? dL_drotations : nullptr;
+    a.dL_dpose = dL_dpose; a.pose_scratch = (float*)pose_scratch;
+    launch_preprocess_backward(a, g, s);
+    GSR_STAGE("preprocess backward");
+    return GSR_OK;
+}
+
+int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                     uint8_t* present, void* stream)
+{
+    (void)projmatrix;
+    cudaStream_t s = (cudaStream_t)stream;
+    const int debug = 0;
+    if (P == 0) return GSR_OK;
+    if (!means3D || !viewmatrix || !present) return fail(GSR_ERR_INVALID, "required pointer is NULL");
+    launch_mark_visible(P, means3D, viewmatrix, present, s);
+    GSR_STAGE("mark_visible");
+    return GSR_OK;
+}
+
+// ---- parity accessor ----------------------------------------------------------------------------
+namespace {
+__global__ void unpack_geom_kernel(int P, GeomView g, float* depths, float* means2D, float* conic_opacity, float* rgb,
+                                   uint32_t* tiles_touched, uint8_t* clamped)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    const bool vis = g.tiles[i] != 0;
+    if (depths) depths[i] = vis ? __uint_as_float(g.depth_key[i]) : 0.f;
+    if (means2D) {
+        means2D[2 * i] = vis ? g.xy[i].x : 0.f;
+        means2D[2 * i + 1] = vis ? g.xy[i].y : 0.f;
+    }
+    if (conic_opacity) {
+        const float4 c = vis ? g.conic_op[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+        conic_opacity[4 * i] = c.x; conic_opacity[4 * i + 1] = c.y; conic_opacity[4 * i + 2] = c.z; conic_opacity[4 * i + 3] = c.w;
+    }
+    if (rgb) {
+        const float4 c = vis ? g.rgb_depth[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+        rgb[3 * i] = c.x; rgb[3 * i + 1] = c.y; rgb[3 * i + 2] = c.z;
+    }
+    if (tiles_touched) tiles_touched[i] = g.tiles[i];
+    if (clamped) {
+        const uint8_t c = vis ? g.clamped[i] : 0;
+        clamped[3 * i] = c & 1; clamped[3 * i + 1] = (c >> 1) & 1; clamped[3 * i + 2] = (c >> 2) & 1;
+    }
+}
+}  // namespace
+
+int gsr_debug_dump(int P, int W, int H, int64_t num_rendered, const void* geometry, const void* binning,
+                   const void* image, uint64_t* keys_sorted, uint32_t* point_list, uint32_t* ranges,
+                   uint32_t* n_contrib, float* depths, float* means2D, float* conic_opacity, float* rgb,
+                   uint32_t* tiles_touched, uint8_t* clamped, void* stream)
+{
+    cudaStream_t s = (cudaStream_t)stream;
+    const int debug = 1;
+    if (P == 0) return GSR_OK;
+    GeomView g;
+    geom_layout((char*)geometry, P, g);
+    ImageView iv;
+    image_layout((char*)image, W, H, iv);
+    BinView b;
+    bin_layout((char*)binning, num_rendered, b);
+    const int tiles = div_up(W, TILE) * div_up(H, TILE);
+    if (keys_sorted && num_rendered > 0) launch_build_keys(b.keys[0], b.vals[0], g.depth_key, num_rendered, keys_sorted, s);
+    if (point_list && num_rendered > 0)
+        cudaMemcpyAsync(point_list, b.vals[0], sizeof(uint32_t) * (size_t)num_rendered, cudaMemcpyDeviceToDevice, s);
+    if (ranges) cudaMemcpyAsync(ranges, iv.ranges, sizeof(uint2) * (size_t)tiles, cudaMemcpyDeviceToDevice, s);
+    if (n_contrib) cudaMemcpyAsync(n_contrib, iv.n_contrib, sizeof(uint32_t) * (size_t)W * H, cudaMemcpyDeviceToDevice, s);
+    unpack_geom_kernel<<<div_up(P, 256), 256, 0, s>>>(P, g, depths, means2D, conic_opacity, rgb, tiles_touched, clamped);
+    GSR_STAGE("debug dump");
+    return GSR_OK;
+}
+
+}  // extern "C"

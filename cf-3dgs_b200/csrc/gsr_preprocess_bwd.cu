@@ -1,0 +1,284 @@
+// Fused backward of the per-Gaussian preprocess.
+// Semantics: reference backward.cu:144-274 (computeCov2DCUDA), :346-412 (preprocessCUDA) with
+// computeColorFromSH backward (:20-139) and computeCov3D backward (:278-341); host glue
+// rasterize_points.cu:158-167 (ten zero-filled tensors).
+//
+// One kernel instead of two, and every output element is written exactly once (zeros for culled
+// Gaussians), so nothing has to be pre-zeroed.  The 3D covariance is recomputed from scale/rotation
+// instead of being stored by the forward (saves 48 B/Gaussian of traffic).  Optionally reduces the rigid
+// pose gradient (sum g, sum p x g) per block -- row N1 of SURVEY.md section 8a.
+#include "gsr_kernels.h"
+#include "gsr_math.cuh"
+
+namespace gsr {
+
+constexpr int PB_THREADS = 256;
+
+int pose_blocks(int P) { return div_up(P, PB_THREADS); }
+
+__device__ __forceinline__ float block_sum_256(float v, float* red)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+    __syncthreads();
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < PB_THREADS / 32; w++) t += red[w];
+    __syncthreads();
+    return t;
+}
+
+__global__ void __launch_bounds__(PB_THREADS)
+preprocess_backward_kernel(PreprocessBwdArgs a, GeomView g)
+{
+    __shared__ float sV[16], sP[16], sCam[3];
+    __shared__ float red[PB_THREADS / 32];
+    if (threadIdx.x < 16) {
+        sV[threadIdx.x] = a.viewmatrix[threadIdx.x];
+        sP[threadIdx.x] = a.projmatrix[threadIdx.x];
+    }
+    if (threadIdx.x < 3) sCam[threadIdx.x] = a.campos[threadIdx.x];
+    __syncthreads();
+
+    const int idx = blockIdx.x * PB_THREADS + threadIdx.x;
+    float gmx = 0.f, gmy = 0.f, gmz = 0.f;   // dL/dmeans3D
+    float px = 0.f, py = 0.f, pz = 0.f;
+    if (idx < a.P) {
+        const bool vis = a.radii[idx] > 0;
+        float dmean2x = 0.f, dmean2y = 0.f, dopac = 0.f, dcol0 = 0.f, dcol1 = 0.f, dcol2 = 0.f;
+        float dcov[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        float dscale[3] = {0.f, 0.f, 0.f};
+        float4 drot = make_float4(0.f, 0.f, 0.f, 0.f);
+        const int ncoef = (a.D + 1) * (a.D + 1);
+        float* dsh = a.dL_dsh ? a.dL_dsh + (size_t)idx * a.M * 3 : nullptr;
+        if (vis) {
+            const float4* rec = reinterpret_cast<const float4*>(a.grad_scratch + (size_t)idx * 12);
+            const float4 q0 = rec[0], q1 = rec[1], q2 = rec[2];
+            dmean2x = q0.x; dmean2y = q0.y;
+            const float dc0 = q0.z, dc1 = q0.w, dc2 = q1.x;
+            dopac = q1.y;
+            dcol0 = q1.z; dcol1 = q1.w; dcol2 = q2.x;
+            const float ddepth = q2.y;
+            px = a.means3D[3 * idx]; py = a.means3D[3 * idx + 1]; pz = a.means3D[3 * idx + 2];
+            float c3[6];
+            float4 rq = make_float4(0.f, 0.f, 0.f, 0.f);
+            float sc0 = 0.f, sc1 = 0.f, sc2 = 0.f;
+            if (a.cov3D_precomp) {
+#pragma unroll
+                for (int k = 0; k < 6; k++) c3[k] = a.cov3D_precomp[6 * (size_t)idx + k];
+            } else {
+                rq = reinterpret_cast<const float4*>(a.rotations)[idx];
+                sc0 = a.scales[3 * idx]; sc1 = a.scales[3 * idx + 1]; sc2 = a.scales[3 * idx + 2];
+                cov3d_from_scale_rot(sc0, sc1, sc2, a.scale_modifier, rq, c3);
+            }
+            const float fy = __fdiv_rn((float)a.H, __fmul_rn(2.0f, a.tanfovy));
+            const float fx = __fdiv_rn((float)a.W, __fmul_rn(2.0f, a.tanfovx));
+            Cov2D cv;
+            cov2d_chain(px, py, pz, fx, fy, a.tanfovx, a.tanfovy, c3, sV, cv);
+            // ---- conic -> cov2D -> cov3D, T, J, t  (backward.cu:171-273) ----
+            const float limx = 1.3f * a.tanfovx, limy = 1.3f * a.tanfovy;
+            const float x_grad_mul = (cv.txtz < -limx || cv.txtz > limx) ? 0.f : 1.f;
+            const float y_grad_mul = (cv.tytz < -limy || cv.tytz > limy) ? 0.f : 1.f;
+            const float ca = cv.a + 0.3f, cb = cv.b, cc = cv.c + 0.3f;
+            const float denom = ca * cc - cb * cb;
+            float dL_da = 0.f, dL_db = 0.f, dL_dc = 0.f;
+            const float denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
+            const float* T0 = cv.T0;
+            const float* T1 = cv.T1;
+            if (denom2inv != 0.f) {
+                dL_da = denom2inv * (-cc * cc * dc0 + 2 * cb * cc * dc1 + (denom - ca * cc) * dc2);
+                dL_dc = denom2inv * (-ca * ca * dc2 + 2 * ca * cb * dc1 + (denom - ca * cc) * dc0);
+                dL_db = denom2inv * 2 * (cb * cc * dc0 - (denom + 2 * cb * cb) * dc1 + ca * cb * dc2);
+                dcov[0] = T0[0] * T0[0] * dL_da + T0[0] * T1[0] * dL_db + T1[0] * T1[0] * dL_dc;
+                dcov[3] = T0[1] * T0[1] * dL_da + T0[1] * T1[1] * dL_db + T1[1] * T1[1] * dL_dc;
+                dcov[5] = T0[2] * T0[2] * dL_da + T0[2] * T1[2] * dL_db + T1[2] * T1[2] * dL_dc;
+                dcov[1] = 2 * T0[0] * T0[1] * dL_da + (T0[0] * T1[1] + T0[1] * T1[0]) * dL_db + 2 * T1[0] * T1[1] * dL_dc;
+                dcov[2] = 2 * T0[0] * T0[2] * dL_da + (T0[0] * T1[2] + T0[2] * T1[0]) * dL_db + 2 * T1[0] * T1[2] * dL_dc;
+                dcov[4] = 2 * T0[2] * T0[1] * dL_da + (T0[1] * T1[2] + T0[2] * T1[1]) * dL_db + 2 * T1[1] * T1[2] * dL_dc;
+            }
+            const float vk[3][3] = {{c3[0], c3[1], c3[2]}, {c3[1], c3[3], c3[4]}, {c3[2], c3[4], c3[5]}};
+            float dT0[3], dT1[3];
+#pragma unroll
+            for (int k = 0; k < 3; k++) {
+                const float u0 = T0[0] * vk[k][0] + T0[1] * vk[k][1] + T0[2] * vk[k][2];
+                const float u1 = T1[0] * vk[k][0] + T1[1] * vk[k][1] + T1[2] * vk[k][2];
+                dT0[k] = 2 * u0 * dL_da + u1 * dL_db;
+                dT1[k] = 2 * u1 * dL_dc + u0 * dL_db;
+            }
+            const float dJ00 = sV[0] * dT0[0] + sV[4] * dT0[1] + sV[8] * dT0[2];
+            const float dJ02 = sV[2] * dT0[0] + sV[6] * dT0[1] + sV[10] * dT0[2];
+            const float dJ11 = sV[1] * dT1[0] + sV[5] * dT1[1] + sV[9] * dT1[2];
+            const float dJ12 = sV[2] * dT1[0] + sV[6] * dT1[1] + sV[10] * dT1[2];
+            const float tzi = 1.f / cv.tz, tz2 = tzi * tzi, tz3 = tz2 * tzi;
+            const float dtx = x_grad_mul * -fx * tz2 * dJ02;
+            const float dty = y_grad_mul * -fy * tz2 * dJ12;
+            const float dtz = -fx * tz2 * dJ00 - fy * tz2 * dJ11 + (2 * fx * cv.tx) * tz3 * dJ02 +
+                              (2 * fy * cv.ty) * tz3 * dJ12;
+            gmx = sV[0] * dtx + sV[1] * dty + sV[2] * dtz;
+            gmy = sV[4] * dtx + sV[5] * dty + sV[6] * dtz;
+            gmz = sV[8] * dtx + sV[9] * dty + sV[10] * dtz;
+            // ---- 2D mean -> 3D mean through the projection (backward.cu:372-389) ----
+            const float hw = xform_row(sP, 3, px, py, pz);
+            const float mw = 1.0f / (hw + 0.0000001f);
+            const float mul1 = (sP[0] * px + sP[4] * py + sP[8] * pz + sP[12]) * mw * mw;
+            const float mul2 = (sP[1] * px + sP[5] * py + sP[9] * pz + sP[13]) * mw * mw;
+            gmx += (sP[0] * mw - sP[3] * mul1) * dmean2x + (sP[1] * mw - sP[3] * mul2) * dmean2y;
+            gmy += (sP[4] * mw - sP[7] * mul1) * dmean2x + (sP[5] * mw - sP[7] * mul2) * dmean2y;
+            gmz += (sP[8] * mw - sP[11] * mul1) * dmean2x + (sP[9] * mw - sP[11] * mul2) * dmean2y;
+            // ---- depth (backward.cu:391-403) ----
+            const float mul3 = sV[2] * px + sV[6] * py + sV[10] * pz + sV[14];
+            gmx += (sV[2] - sV[3] * mul3) * ddepth;
+            gmy += (sV[6] - sV[7] * mul3) * ddepth;
+            gmz += (sV[10] - sV[11] * mul3) * ddepth;
+            // ---- SH (backward.cu:20-139) ----
+            if (a.shs) {
+                const float* sh = a.shs + (size_t)idx * a.M * 3;
+                const uint8_t cl = g.clamped[idx];
+                const float dR = (cl & 1) ? 0.f : dcol0, dG = (cl & 2) ? 0.f : dcol1, dB = (cl & 4) ? 0.f : dcol2;
+                const float ox = px - sCam[0], oy = py - sCam[1], oz = pz - sCam[2];
+                const float len = sqrtf(ox * ox + oy * oy + oz * oz);
+                const float x = ox / len, y = oy / len, z = oz / len;
+                float basis[16];
+                sh_basis(a.D, x, y, z, basis);
+#pragma unroll
+                for (int k = 0; k < 16; k++) {
+                    if (k < ncoef) {
+                        dsh[3 * k] = basis[k] * dR;
+                        dsh[3 * k + 1] = basis[k] * dG;
+                        dsh[3 * k + 2] = basis[k] * dB;
+                    }
+                }
+                // d colour / d direction, summed over channels with the channel gradient
+#define SHD(k) (sh[3 * (k)] * dR + sh[3 * (k) + 1] * dG + sh[3 * (k) + 2] * dB)
+                float ddx = 0.f, ddy = 0.f, ddz = 0.f;
+                if (a.D > 0) {
+                    const float s1 = SHD(1), s2 = SHD(2), s3 = SHD(3);
+                    ddx = -SH_C1 * s3; ddy = -SH_C1 * s1; ddz = SH_C1 * s2;
+                    if (a.D > 1) {
+                        const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+                        const float s4 = SHD(4), s5 = SHD(5), s6 = SHD(6), s7 = SHD(7), s8 = SHD(8);
+                        ddx += SH_C2[0] * y * s4 + SH_C2[2] * 2.f * -x * s6 + SH_C2[3] * z * s7 + SH_C2[4] * 2.f * x * s8;
+                        ddy += SH_C2[0] * x * s4 + SH_C2[1] * z * s5 + SH_C2[2] * 2.f * -y * s6 + SH_C2[4] * 2.f * -y * s8;
+                        ddz += SH_C2[1] * y * s5 + SH_C2[2] * 2.f * 2.f * z * s6 + SH_C2[3] * x * s7;
+                        if (a.D > 2) {
+                            const float s9 = SHD(9), s10 = SHD(10), s11 = SHD(11), s12 = SHD(12), s13 = SHD(13),
+                                        s14 = SHD(14), s15 = SHD(15);
+                            ddx += SH_C3[0] * s9 * 3.f * 2.f * xy + SH_C3[1] * s10 * yz + SH_C3[2] * s11 * -2.f * xy +
+                                   SH_C3[3] * s12 * -3.f * 2.f * xz + SH_C3[4] * s13 * (-3.f * xx + 4.f * zz - yy) +
+                                   SH_C3[5] * s14 * 2.f * xz + SH_C3[6] * s15 * 3.f * (xx - yy);
+                            ddy += SH_C3[0] * s9 * 3.f * (xx - yy) + SH_C3[1] * s10 * xz +
+                                   SH_C3[2] * s11 * (-3.f * yy + 4.f * zz - xx) + SH_C3[3] * s12 * -3.f * 2.f * yz +
+                                   SH_C3[4] * s13 * -2.f * xy + SH_C3[5] * s14 * -2.f * yz + SH_C3[6] * s15 * -3.f * 2.f * xy;
+                            ddz += SH_C3[1] * s10 * xy + SH_C3[2] * s11 * 4.f * 2.f * yz +
+                                   SH_C3[3] * s12 * 3.f * (2.f * zz - xx - yy) + SH_C3[4] * s13 * 4.f * 2.f * xz +
+                                   SH_C3[5] * s14 * (xx - yy);
+                        }
+                    }
+                }
+#undef SHD
+                // through the normalisation (auxiliary.h:107-120)
+                const float sum2 = ox * ox + oy * oy + oz * oz;
+                const float inv32 = 1.0f / sqrtf(sum2 * sum2 * sum2);
+                gmx += ((sum2 - ox * ox) * ddx - oy * ox * ddy - oz * ox * ddz) * inv32;
+                gmy += (-ox * oy * ddx + (sum2 - oy * oy) * ddy - oz * oy * ddz) * inv32;
+                gmz += (-ox * oz * ddx - oy * oz * ddy + (sum2 - oz * oz) * ddz) * inv32;
+            }
+            // ---- cov3D -> scale, rotation (backward.cu:278-341) ----
+            if (a.scales) {
+                const float r = rq.x, x = rq.y, y = rq.z, z = rq.w;
+                // glm columns of R
+                const float R[3][3] = {{1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y)},
+                                       {2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x)},
+                                       {2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y)}};
+                const float s[3] = {a.scale_modifier * sc0, a.scale_modifier * sc1, a.scale_modifier * sc2};
+                const float dS[3][3] = {{dcov[0], 0.5f * dcov[1], 0.5f * dcov[2]},
+                                        {0.5f * dcov[1], dcov[3], 0.5f * dcov[4]},
+                                        {0.5f * dcov[2], 0.5f * dcov[4], dcov[5]}};
+                float dMt[3][3];  // dMt[c][k] = dL_dM[k][c],  dL_dM[c][r] = 2 * sum_k M[k][r] * dS[c][k]
+#pragma unroll
+                for (int c = 0; c < 3; c++)
+#pragma unroll
+                    for (int k = 0; k < 3; k++)
+                        dMt[c][k] = 2.0f * (s[c] * R[0][c] * dS[k][0] + s[c] * R[1][c] * dS[k][1] + s[c] * R[2][c] * dS[k][2]);
+#pragma unroll
+                for (int c = 0; c < 3; c++) dscale[c] = R[0][c] * dMt[c][0] + R[1][c] * dMt[c][1] + R[2][c] * dMt[c][2];
+#pragma unroll
+                for (int c = 0; c < 3; c++)
+#pragma unroll
+                    for (int k = 0; k < 3; k++) dMt[c][k] *= s[c];
+                drot.x = 2 * z * (dMt[0][1] - dMt[1][0]) + 2 * y * (dMt[2][0] - dMt[0][2]) + 2 * x * (dMt[1][2] - dMt[2][1]);
+                drot.y = 2 * y * (dMt[1][0] + dMt[0][1]) + 2 * z * (dMt[2][0] + dMt[0][2]) + 2 * r * (dMt[1][2] - dMt[2][1]) - 4 * x * (dMt[2][2] + dMt[1][1]);
+                drot.z = 2 * x * (dMt[1][0] + dMt[0][1]) + 2 * r * (dMt[2][0] - dMt[0][2]) + 2 * z * (dMt[1][2] + dMt[2][1]) - 4 * y * (dMt[2][2] + dMt[0][0]);
+                drot.w = 2 * r * (dMt[0][1] - dMt[1][0]) + 2 * x * (dMt[2][0] + dMt[0][2]) + 2 * y * (dMt[1][2] + dMt[2][1]) - 4 * z * (dMt[1][1] + dMt[0][0]);
+            }
+        }
+        // ---- write every output exactly once ----
+        if (dsh) {
+            const int first_zero = vis ? ncoef : 0;
+            for (int k = first_zero * 3; k < a.M * 3; k++) dsh[k] = 0.f;
+        }
+        a.dL_dmeans2D[3 * idx] = dmean2x;
+        a.dL_dmeans2D[3 * idx + 1] = dmean2y;
+        a.dL_dmeans2D[3 * idx + 2] = 0.f;
+        a.dL_dopacity[idx] = dopac;
+        a.dL_dmeans3D[3 * idx] = gmx;
+        a.dL_dmeans3D[3 * idx + 1] = gmy;
+        a.dL_dmeans3D[3 * idx + 2] = gmz;
+        if (a.dL_dcolors) {
+            a.dL_dcolors[3 * idx] = dcol0;
+            a.dL_dcolors[3 * idx + 1] = dcol1;
+            a.dL_dcolors[3 * idx + 2] = dcol2;
+        }
+        if (a.dL_dcov3D) {
+#pragma unroll
+            for (int k = 0; k < 6; k++) a.dL_dcov3D[6 * (size_t)idx + k] = dcov[k];
+        }
+        if (a.dL_dscales) {
+            a.dL_dscales[3 * idx] = dscale[0];
+            a.dL_dscales[3 * idx + 1] = dscale[1];
+            a.dL_dscales[3 * idx + 2] = dscale[2];
+        }
+        if (a.dL_drotations) reinterpret_cast<float4*>(a.dL_drotations)[idx] = drot;
+    }
+    if (a.dL_dpose) {
+        // rigid pose gradient at xi = 0 for p' = Exp(xi) p:  d/dnu = g,  d/domega = p x g
+        const float v0 = block_sum_256(gmx, red), v1 = block_sum_256(gmy, red), v2 = block_sum_256(gmz, red);
+        const float w0 = block_sum_256(py * gmz - pz * gmy, red);
+        const float w1 = block_sum_256(pz * gmx - px * gmz, red);
+        const float w2 = block_sum_256(px * gmy - py * gmx, red);
+        if (threadIdx.x == 0) {
+            float* o = a.pose_scratch + (size_t)blockIdx.x * 6;
+            o[0] = v0; o[1] = v1; o[2] = v2; o[3] = w0; o[4] = w1; o[5] = w2;
+        }
+    }
+}
+
+// deterministic second stage: one block sums the per-block partials in double
+__global__ void __launch_bounds__(256) pose_reduce_kernel(const float* __restrict__ partial, int nblk, float* __restrict__ out)
+{
+    __shared__ double red[8];
+    for (int c = 0; c < 6; c++) {
+        double v = 0.0;
+        for (int i = threadIdx.x; i < nblk; i += 256) v += (double)partial[(size_t)i * 6 + c];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double t = 0.0;
+            for (int w = 0; w < 8; w++) t += red[w];
+            out[c] = (float)t;
+        }
+        __syncthreads();
+    }
+}
+
+void launch_preprocess_backward(const PreprocessBwdArgs& a, const GeomView& g, cudaStream_t s)
+{
+    const int nblk = div_up(a.P, PB_THREADS);
+    preprocess_backward_kernel<<<nblk, PB_THREADS, 0, s>>>(a, g);
+    if (a.dL_dpose) pose_reduce_kernel<<<1, 256, 0, s>>>(a.pose_scratch, nblk, a.dL_dpose);
+}
+
+}  // namespace gsr

@@ -1,0 +1,221 @@
+// Backward tile blend.  Semantics: reference backward.cu:415-601 (renderCUDA): per pixel, back to front from
+// n_contrib, T restarts at T_final = 1 - alpha_out and is unwound with T = T / (1 - alpha) -- the same
+// recurrence, not an algebraic equivalent, so nearly opaque pixels behave like the reference.
+//
+// The reference issues 10 global float atomics per blended (pixel, Gaussian) pair.  Here the 32 lanes of a
+// warp always look at the same Gaussian, so the 10 partials are summed across the warp with shuffles, the 8
+// warps of the CTA accumulate into a per-batch shared-memory table, and each CTA flushes one 48-byte record
+// per touched Gaussian with three 16-byte vector reductions (red.global.add.v4.f32).  Entries that cannot
+// reach alpha >= 1/255 in the tile / in the warp's 8x4 footprint are rejected exactly as in the forward.
+//
+// Gradient record per Gaussian (grad_scratch, 12 floats):
+//   0 mean2D.x  1 mean2D.y  2 conic.x  3 conic.y | 4 conic.w  5 opacity  6 colour.r  7 colour.g |
+//   8 colour.b  9 depth  10,11 unused
+#include "gsr_blend.cuh"
+#include "gsr_kernels.h"
+
+namespace gsr {
+
+constexpr int NGRAD = 12;
+
+__device__ __forceinline__ float warp_sum(float v)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+template <bool HAS_DEPTH, bool HAS_ALPHA>
+__global__ void __launch_bounds__(BLEND_THREADS)
+render_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges,
+                       const uint32_t* __restrict__ point_list, GeomView g, const float* __restrict__ bg,
+                       const float* __restrict__ out_alpha, const uint32_t* __restrict__ n_contrib,
+                       const float* __restrict__ dL_dcolor, const float* __restrict__ dL_ddepth,
+                       const float* __restrict__ dL_dalpha, float* __restrict__ grad)
+{
+    __shared__ Staged sm;
+    __shared__ uint32_t sm_gid[BATCH];
+    __shared__ __align__(16) float acc[BATCH][NGRAD];
+
+    const int tile = blockIdx.x;
+    const int tile_x = tile % grid_x, tile_y = tile / grid_x;
+    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int fx0 = tile_x * TILE + (warp & 1) * FOOT_W, fy0 = tile_y * TILE + (warp >> 1) * FOOT_H;
+    const int pix_x = fx0 + (lane & 7), pix_y = fy0 + (lane >> 3);
+    const bool inside = pix_x < W && pix_y < H;
+    const float pxf = (float)pix_x, pyf = (float)pix_y;
+    const float foot_x0 = (float)fx0, foot_y0 = (float)fy0;
+    const float tile_x0 = (float)(tile_x * TILE), tile_y0 = (float)(tile_y * TILE);
+
+    const uint2 range = ranges[tile];
+    const int total = (int)(range.y - range.x);
+    if (total == 0) return;
+
+    const size_t pid = (size_t)W * pix_y + pix_x;
+    const size_t plane = (size_t)W * H;
+    const float T_final = inside ? (1.f - out_alpha[pid]) : 0.f;
+    float T = T_final;
+    const int last_contributor = inside ? (int)n_contrib[pid] : 0;
+    float dLp0 = 0.f, dLp1 = 0.f, dLp2 = 0.f, dLd = 0.f, dLa = 0.f;
+    if (inside) {
+        dLp0 = dL_dcolor[pid];
+        dLp1 = dL_dcolor[plane + pid];
+        dLp2 = dL_dcolor[2 * plane + pid];
+        if (HAS_DEPTH) dLd = dL_ddepth[pid];
+        if (HAS_ALPHA) dLa = dL_dalpha[pid];
+    }
+    const float bg_dot = bg[0] * dLp0 + bg[1] * dLp1 + bg[2] * dLp2;
+    float ar0 = 0.f, ar1 = 0.f, ar2 = 0.f, adr = 0.f, aar = 0.f;   // accum_rec colour / depth / alpha
+    float last_alpha = 0.f, lc0 = 0.f, lc1 = 0.f, lc2 = 0.f, last_depth = 0.f;
+    const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
+
+    // entries at list positions >= max(n_contrib) over the tile never contribute: start there
+    __shared__ int s_start;
+    if (threadIdx.x == 0) s_start = 0;
+    __syncthreads();
+    {
+        int m = last_contributor;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
+        if (lane == 0 && m > 0) atomicMax(&s_start, m);
+    }
+    __syncthreads();
+    const int start = s_start;              // process positions start-1 ... 0
+    const int warp_last = __reduce_max_sync(0xffffffffu, last_contributor);
+
+    for (int base = 0; base < start; base += BATCH) {
+        __syncthreads();   // previous flush finished
+        const int n = min(BATCH, start - base);
+        // slot j of this round holds list position (start - 1 - base - j)
+        for (int k = threadIdx.x; k < BATCH * NGRAD / 4; k += BLEND_THREADS)
+            reinterpret_cast<float4*>(&acc[0][0])[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if ((int)threadIdx.x < n) {
+            const uint32_t gid = point_list[range.x + (start - 1 - base - threadIdx.x)];
+            sm_gid[threadIdx.x] = gid;
+            stage_entry(sm, threadIdx.x, gid, g, tile_x0, tile_y0);
+        }
+        __syncthreads();
+
+        for (int c0 = 0; c0 < n; c0 += 32) {
+            // positions of this chunk: pos = start-1-base-(c0+lane) ; whole chunk beyond the warp's last?
+            const int chunk_first_pos = start - 1 - base - c0;   // highest position in the chunk
+            if (chunk_first_pos - 31 >= warp_last) continue;
+            const int e = c0 + lane;
+            bool keep = false;
+            if (e < n && (start - 1 - base - e) < warp_last) {
+                const float thr = sm.thr[e];
+                if (!(thr < 0.f)) {
+                    const float4 r0 = sm.rec0[e];
+                    const float4 r1 = sm.rec1[e];
+                    keep = !reject_rect(r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, thr, foot_x0,
+                                        foot_x0 + (FOOT_W - 1), foot_y0, foot_y0 + (FOOT_H - 1));
+                }
+            }
+            unsigned live = __ballot_sync(0xffffffffu, keep);
+            while (live) {
+                const int j = c0 + __ffs(live) - 1;
+                live &= live - 1;
+                const int pos = start - 1 - base - j;
+                const float4 r0 = sm.rec0[j];
+                const float4 r1 = sm.rec1[j];
+                const float dx = __fadd_rn(r0.x, -pxf), dy = __fadd_rn(r0.y, -pyf);
+                const float power = blend_power(dx, dy, r1.x, r1.y, r1.z);
+                const float G = expf(power);
+                const float alpha = fminf(0.99f, __fmul_rn(r1.w, G));
+                const bool contrib = (pos < last_contributor) && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+                if (!__any_sync(0xffffffffu, contrib)) continue;
+
+                float g_mx = 0.f, g_my = 0.f, g_cx = 0.f, g_cy = 0.f, g_cw = 0.f, g_op = 0.f;
+                float g_c0 = 0.f, g_c1 = 0.f, g_c2 = 0.f, g_d = 0.f;
+                if (contrib) {
+                    const float4 r2 = sm.rec2[j];
+                    const float one_m = __fadd_rn(1.f, -alpha);
+                    T = __fdiv_rn(T, one_m);
+                    const float aT = alpha * T;
+                    float dL_dopa = 0.f;
+                    ar0 = last_alpha * lc0 + (1.f - last_alpha) * ar0; lc0 = r2.x;
+                    dL_dopa += (r2.x - ar0) * dLp0;
+                    ar1 = last_alpha * lc1 + (1.f - last_alpha) * ar1; lc1 = r2.y;
+                    dL_dopa += (r2.y - ar1) * dLp1;
+                    ar2 = last_alpha * lc2 + (1.f - last_alpha) * ar2; lc2 = r2.z;
+                    dL_dopa += (r2.z - ar2) * dLp2;
+                    g_c0 = aT * dLp0; g_c1 = aT * dLp1; g_c2 = aT * dLp2;
+                    if (HAS_DEPTH) {
+                        adr = last_alpha * last_depth + (1.f - last_alpha) * adr;
+                        last_depth = r2.w;
+                        dL_dopa += (r2.w - adr) * dLd;
+                        g_d = aT * dLd;
+                    }
+                    if (HAS_ALPHA) {
+                        aar = last_alpha + (1.f - last_alpha) * aar;
+                        dL_dopa += (1.f - aar) * dLa;
+                    }
+                    dL_dopa *= T;
+                    last_alpha = alpha;
+                    dL_dopa += (-T_final / one_m) * bg_dot;
+                    const float dL_dG = r1.w * dL_dopa;
+                    const float gdx = G * dx, gdy = G * dy;
+                    const float dG_ddelx = -gdx * r1.x - gdy * r1.y;
+                    const float dG_ddely = -gdy * r1.z - gdx * r1.y;
+                    g_mx = dL_dG * dG_ddelx * ddelx_dx;
+                    g_my = dL_dG * dG_ddely * ddely_dy;
+                    g_cx = -0.5f * gdx * dx * dL_dG;
+                    g_cy = -0.5f * gdx * dy * dL_dG;
+                    g_cw = -0.5f * gdy * dy * dL_dG;
+                    g_op = G * dL_dopa;
+                }
+                g_mx = warp_sum(g_mx); g_my = warp_sum(g_my);
+                g_cx = warp_sum(g_cx); g_cy = warp_sum(g_cy); g_cw = warp_sum(g_cw);
+                g_op = warp_sum(g_op);
+                g_c0 = warp_sum(g_c0); g_c1 = warp_sum(g_c1); g_c2 = warp_sum(g_c2);
+                if (HAS_DEPTH) g_d = warp_sum(g_d);
+                // lanes 0..9 each own one component
+                float mine = g_mx;
+                mine = lane == 1 ? g_my : mine;
+                mine = lane == 2 ? g_cx : mine;
+                mine = lane == 3 ? g_cy : mine;
+                mine = lane == 4 ? g_cw : mine;
+                mine = lane == 5 ? g_op : mine;
+                mine = lane == 6 ? g_c0 : mine;
+                mine = lane == 7 ? g_c1 : mine;
+                mine = lane == 8 ? g_c2 : mine;
+                mine = lane == 9 ? g_d : mine;
+                if (lane < 10) atomicAdd(&acc[j][lane], mine);
+            }
+        }
+        __syncthreads();
+        // flush: one record per entry, three 16-byte vector reductions
+        if ((int)threadIdx.x < n) {
+            const float4 a0 = reinterpret_cast<const float4*>(&acc[threadIdx.x][0])[0];
+            const float4 a1 = reinterpret_cast<const float4*>(&acc[threadIdx.x][0])[1];
+            const float4 a2 = reinterpret_cast<const float4*>(&acc[threadIdx.x][0])[2];
+            const bool nz = (a0.x != 0.f) | (a0.y != 0.f) | (a0.z != 0.f) | (a0.w != 0.f) | (a1.x != 0.f) |
+                            (a1.y != 0.f) | (a1.z != 0.f) | (a1.w != 0.f) | (a2.x != 0.f) | (a2.y != 0.f);
+            if (nz) {
+                float4* dst = reinterpret_cast<float4*>(grad + (size_t)sm_gid[threadIdx.x] * NGRAD);
+                atomicAdd(dst, a0);
+                atomicAdd(dst + 1, a1);
+                atomicAdd(dst + 2, a2);
+            }
+        }
+    }
+}
+
+void launch_render_backward(int W, int H, const uint2* ranges, const uint32_t* point_list, const GeomView& g,
+                            const float* bg, const float* out_alpha, const uint32_t* n_contrib,
+                            const float* dL_dcolor, const float* dL_ddepth, const float* dL_dalpha,
+                            float* grad_scratch, cudaStream_t s)
+{
+    const int gx = div_up(W, TILE), gy = div_up(H, TILE);
+    const dim3 grid(gx * gy), block(BLEND_THREADS);
+#define GSR_LAUNCH(D, A)                                                                                        \
+    render_backward_kernel<D, A><<<grid, block, 0, s>>>(W, H, gx, ranges, point_list, g, bg, out_alpha, n_contrib, \
+                                                        dL_dcolor, dL_ddepth, dL_dalpha, grad_scratch)
+    if (dL_ddepth && dL_dalpha) GSR_LAUNCH(true, true);
+    else if (dL_ddepth) GSR_LAUNCH(true, false);
+    else if (dL_dalpha) GSR_LAUNCH(false, true);
+    else GSR_LAUNCH(false, false);
+#undef GSR_LAUNCH
+}
+
+}  // namespace gsr

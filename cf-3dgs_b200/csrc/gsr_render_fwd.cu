@@ -1,0 +1,112 @@
+// Forward tile blend.  Semantics: reference forward.cu:261-381 (renderCUDA): per pixel, front to back,
+//   power > 0 -> skip;  alpha = min(0.99, o*exp(power)) < 1/255 -> skip;  T*(1-alpha) < 1e-4 -> pixel done;
+//   C += c*alpha*T, weight += alpha*T, D += depth*alpha*T;  out = C + T*bg, alpha = weight, depth = D,
+//   n_contrib = 1-based list position of the last blended entry.
+// All per-pair arithmetic uses the reference's rounding sequence (gsr_math.cuh: blend_power; expf is the
+// full-accuracy CUDA expf the reference calls), so the images are bit-identical given identical inputs.
+//
+// What differs is how much work is skipped: entries are staged 256 at a time as packed records (one 16-B
+// gather each for geometry, conic and colour+depth), the staging thread rejects entries that cannot reach
+// alpha >= 1/255 anywhere in the tile, and each warp (8x4 pixels) rejects entries for its own footprint
+// with one lane per entry + a ballot, then walks only the surviving bits.  Rejected pairs are exactly
+// pairs the reference would have skipped at its alpha test.
+#include "gsr_blend.cuh"
+#include "gsr_kernels.h"
+
+namespace gsr {
+
+__global__ void __launch_bounds__(BLEND_THREADS)
+render_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges,
+                      const uint32_t* __restrict__ point_list, GeomView g, const float* __restrict__ bg,
+                      float* __restrict__ out_color, float* __restrict__ out_depth, float* __restrict__ out_alpha,
+                      uint32_t* __restrict__ n_contrib)
+{
+    __shared__ Staged sm;
+    const int tile = blockIdx.x;
+    const int tile_x = tile % grid_x, tile_y = tile / grid_x;
+    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int fx0 = tile_x * TILE + (warp & 1) * FOOT_W, fy0 = tile_y * TILE + (warp >> 1) * FOOT_H;
+    const int pix_x = fx0 + (lane & 7), pix_y = fy0 + (lane >> 3);
+    const bool inside = pix_x < W && pix_y < H;
+    const float pxf = (float)pix_x, pyf = (float)pix_y;
+    const float foot_x0 = (float)fx0, foot_y0 = (float)fy0;
+    const float tile_x0 = (float)(tile_x * TILE), tile_y0 = (float)(tile_y * TILE);
+
+    const uint2 range = ranges[tile];
+    const int total = (int)(range.y - range.x);
+    bool done = !inside;
+    float T = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f, weight = 0.f, Dacc = 0.f;
+    uint32_t last_contributor = 0;
+
+    for (int base = 0; base < total; base += BATCH) {
+        // whole tile finished? (also protects the staging buffers of the previous round)
+        if (__syncthreads_count(done) == BLEND_THREADS) break;
+        const int n = min(BATCH, total - base);
+        if ((int)threadIdx.x < n) stage_entry(sm, threadIdx.x, point_list[range.x + base + threadIdx.x], g, tile_x0, tile_y0);
+        __syncthreads();
+
+        for (int c0 = 0; c0 < n; c0 += 32) {
+            if (__all_sync(0xffffffffu, done)) break;
+            // one lane per entry: can this entry matter anywhere in the warp's footprint?
+            const int e = c0 + lane;
+            bool keep = false;
+            if (e < n) {
+                const float thr = sm.thr[e];
+                if (!(thr < 0.f)) {
+                    const float4 r0 = sm.rec0[e];
+                    const float4 r1 = sm.rec1[e];
+                    keep = !reject_rect(r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, thr, foot_x0,
+                                        foot_x0 + (FOOT_W - 1), foot_y0, foot_y0 + (FOOT_H - 1));
+                }
+            }
+            unsigned live = __ballot_sync(0xffffffffu, keep);
+            while (live) {
+                const int j = c0 + __ffs(live) - 1;
+                live &= live - 1;
+                if (done) continue;
+                const float4 r0 = sm.rec0[j];
+                const float4 r1 = sm.rec1[j];
+                const float dx = __fadd_rn(r0.x, -pxf), dy = __fadd_rn(r0.y, -pyf);
+                const float power = blend_power(dx, dy, r1.x, r1.y, r1.z);
+                if (power > 0.0f) continue;
+                const float alpha = fminf(0.99f, __fmul_rn(r1.w, expf(power)));
+                if (alpha < 1.0f / 255.0f) continue;
+                const float test_T = __fmul_rn(T, __fadd_rn(1.f, -alpha));
+                if (test_T < 0.0001f) {
+                    done = true;
+                    continue;
+                }
+                const float4 r2 = sm.rec2[j];
+                C0 = __fmaf_rn(T, __fmul_rn(alpha, r2.x), C0);
+                C1 = __fmaf_rn(T, __fmul_rn(alpha, r2.y), C1);
+                C2 = __fmaf_rn(T, __fmul_rn(alpha, r2.z), C2);
+                weight = __fmaf_rn(T, alpha, weight);
+                Dacc = __fmaf_rn(T, __fmul_rn(alpha, r2.w), Dacc);
+                T = test_T;
+                last_contributor = (uint32_t)(base + j + 1);
+            }
+        }
+    }
+
+    if (inside) {
+        const size_t pid = (size_t)W * pix_y + pix_x;
+        const size_t plane = (size_t)W * H;
+        n_contrib[pid] = last_contributor;
+        out_color[pid] = __fmaf_rn(bg[0], T, C0);
+        out_color[plane + pid] = __fmaf_rn(bg[1], T, C1);
+        out_color[2 * plane + pid] = __fmaf_rn(bg[2], T, C2);
+        out_alpha[pid] = weight;
+        out_depth[pid] = Dacc;
+    }
+}
+
+void launch_render_forward(int W, int H, const uint2* ranges, const uint32_t* point_list, const GeomView& g,
+                           const float* bg, float* out_color, float* out_depth, float* out_alpha,
+                           uint32_t* n_contrib, cudaStream_t s)
+{
+    const int gx = div_up(W, TILE), gy = div_up(H, TILE);
+    render_forward_kernel<<<gx * gy, BLEND_THREADS, 0, s>>>(W, H, gx, ranges, point_list, g, bg, out_color,
+                                                            out_depth, out_alpha, n_contrib);
+}
+
+}  // namespace gsr

@@ -1,0 +1,291 @@
+// Binning: the (tile|depth) key sort of the reference (rasterizer_impl.cu:70-138,278-319) executed as a
+// split-key LSD radix sort.
+//
+// The reference emits one 64-bit key (tile << 32 | depth bits) per tile instance and runs a stable LSD
+// radix sort over all R instances on 32+bit key bits (CUB, ~6 passes of 24 B/instance each).  Every
+// instance of a Gaussian carries the same low 32 bits, and a stable sort on those bits commutes with
+// the duplication: so the low-32-bit digit passes run here on the P Gaussians BEFORE they are duplicated,
+// instances are then emitted in depth order, and only the tile digits (10-13 bits) are sorted over the R
+// instances.  The 64-bit keys are never materialised in the hot path; the result (order within each tile:
+// depth bits ascending, ties by Gaussian index = emission order) is identical to the reference's stable
+// sort, and gsr_debug_dump() rebuilds the sorted key array for bit-exact comparison.
+//
+// Each radix pass is histogram -> row scan -> stable scatter.  Ranks inside a block come from warp-level
+// multi-split: __match_any_sync groups the lanes holding the same digit, the group's lowest lane bumps a
+// warp-private counter, and popc(mask & lanemask_lt) orders the lanes; warp counters are then scanned
+// across the 8 warps of the block.  No inter-block spinning (safe under any block schedule).
+#include "gsr_kernels.h"
+
+namespace gsr {
+
+// ---------------------------------------------------------------------------------------------
+// pass kernel 1: per-block digit histogram, written digit-major: hist[d * nblk + block]
+__global__ void __launch_bounds__(SORT_THREADS)
+radix_hist_kernel(const uint32_t* __restrict__ keys, int64_t n, int shift, uint32_t mask,
+                  uint32_t* __restrict__ hist, int nblk)
+{
+    __shared__ uint32_t sh[RADIX];
+    sh[threadIdx.x] = 0;
+    __syncthreads();
+    const int64_t base = (int64_t)blockIdx.x * SORT_CHUNK;
+    const unsigned lane = threadIdx.x & 31;
+#pragma unroll
+    for (int i = 0; i < SORT_ITEMS; i++) {
+        const int64_t idx = base + (int64_t)i * SORT_THREADS + threadIdx.x;
+        const bool act = idx < n;
+        const uint32_t d = act ? ((keys[idx] >> shift) & mask) : (uint32_t)RADIX;
+        const unsigned m = __match_any_sync(0xffffffffu, d);
+        if (act && lane == (unsigned)(__ffs(m) - 1)) atomicAdd(&sh[d], (uint32_t)__popc(m));
+    }
+    __syncthreads();
+    hist[(size_t)threadIdx.x * nblk + blockIdx.x] = sh[threadIdx.x];
+}
+
+// pass kernel 2: block d turns row d of hist into its exclusive prefix and records the row total.
+__global__ void __launch_bounds__(SORT_THREADS)
+radix_rowscan_kernel(uint32_t* __restrict__ hist, int nblk, uint32_t* __restrict__ digit_total)
+{
+    __shared__ uint32_t warp_sums[8];
+    uint32_t* row = hist + (size_t)blockIdx.x * nblk;
+    const int per = (nblk + SORT_THREADS - 1) / SORT_THREADS;
+    const int lo = threadIdx.x * per;
+    const int hi = min(nblk, lo + per);
+    uint32_t sum = 0;
+    for (int i = lo; i < hi; i++) sum += row[i];
+    uint32_t total;
+    uint32_t run = block_exclusive_scan_256(sum, warp_sums, &total);
+    for (int i = lo; i < hi; i++) {
+        const uint32_t v = row[i];
+        row[i] = run;
+        run += v;
+    }
+    if (threadIdx.x == 0) digit_total[blockIdx.x] = total;
+}
+
+// pass kernel 3: stable scatter.
+__global__ void __launch_bounds__(SORT_THREADS)
+radix_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+                     uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int64_t n, int shift,
+                     uint32_t mask, const uint32_t* __restrict__ hist, int nblk,
+                     const uint32_t* __restrict__ digit_total)
+{
+    __shared__ uint32_t wcount[SORT_THREADS / 32][RADIX + 1];
+    __shared__ uint32_t gbase[RADIX];
+    __shared__ uint32_t warp_sums[8];
+    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int i = threadIdx.x; i < (SORT_THREADS / 32) * (RADIX + 1); i += SORT_THREADS) (&wcount[0][0])[i] = 0;
+    // global base of each digit for this block = exclusive scan of digit totals + row prefix
+    {
+        const uint32_t tot = digit_total[threadIdx.x];
+        const uint32_t ex = block_exclusive_scan_256(tot, warp_sums, nullptr);  // contains __syncthreads
+        gbase[threadIdx.x] = ex + hist[(size_t)threadIdx.x * nblk + blockIdx.x];
+    }
+    __syncthreads();
+    // each warp owns a contiguous run of SORT_ITEMS*32 items; order inside it is (step, lane)
+    const int64_t wbase = (int64_t)blockIdx.x * SORT_CHUNK + (int64_t)warp * (SORT_ITEMS * 32);
+    uint32_t key[SORT_ITEMS], rank[SORT_ITEMS];
+#pragma unroll
+    for (int i = 0; i < SORT_ITEMS; i++) {
+        const int64_t idx = wbase + i * 32 + lane;
+        const bool act = idx < n;
+        key[i] = act ? keys_in[idx] : 0u;
+        const uint32_t d = act ? ((key[i] >> shift) & mask) : (uint32_t)RADIX;
+        const unsigned m = __match_any_sync(0xffffffffu, d);
+        const int leader = __ffs(m) - 1;
+        uint32_t prev = 0;
+        if (lane == (unsigned)leader) {
+            prev = wcount[warp][d];
+            wcount[warp][d] = prev + (uint32_t)__popc(m);
+        }
+        prev = __shfl_sync(0xffffffffu, prev, leader);
+        rank[i] = prev + (uint32_t)__popc(m & ((1u << lane) - 1u));
+        __syncwarp();
+    }
+    __syncthreads();
+    // exclusive scan of the warp counters across warps, per digit
+    {
+        uint32_t run = 0;
+#pragma unroll
+        for (int w = 0; w < SORT_THREADS / 32; w++) {
+            const uint32_t c = wcount[w][threadIdx.x];
+            wcount[w][threadIdx.x] = run;
+            run += c;
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < SORT_ITEMS; i++) {
+        const int64_t idx = wbase + i * 32 + lane;
+        if (idx < n) {
+            const uint32_t d = (key[i] >> shift) & mask;
+            const uint32_t pos = gbase[d] + wcount[warp][d] + rank[i];
+            keys_out[pos] = key[i];
+            vals_out[pos] = vals_in[idx];
+        }
+    }
+}
+
+int radix_sort_pairs(uint32_t* keys[2], uint32_t* vals[2], int64_t n, int begin_bit, int end_bit,
+                     uint32_t* hist, uint32_t* digit_total, cudaStream_t s)
+{
+    int cur = 0;
+    if (n <= 0) return cur;
+    const int nblk = div_up(n, SORT_CHUNK);
+    for (int shift = begin_bit; shift < end_bit; shift += RADIX_BITS) {
+        const int bits = min(RADIX_BITS, end_bit - shift);
+        const uint32_t mask = (1u << bits) - 1u;
+        radix_hist_kernel<<<nblk, SORT_THREADS, 0, s>>>(keys[cur], n, shift, mask, hist, nblk);
+        radix_rowscan_kernel<<<RADIX, SORT_THREADS, 0, s>>>(hist, nblk, digit_total);
+        radix_scatter_kernel<<<nblk, SORT_THREADS, 0, s>>>(keys[cur], vals[cur], keys[cur ^ 1], vals[cur ^ 1], n,
+                                                           shift, mask, hist, nblk, digit_total);
+        cur ^= 1;
+    }
+    return cur;
+}
+
+// ---------------------------------------------------------------------------------------------
+__global__ void init_sort_input_kernel(const uint32_t* __restrict__ depth_key, uint32_t* __restrict__ keys,
+                                       uint32_t* __restrict__ vals, int P)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < P) {
+        keys[i] = depth_key[i];
+        vals[i] = (uint32_t)i;
+    }
+}
+
+void launch_init_sort_input(const GeomView& g, int P, cudaStream_t s)
+{
+    init_sort_input_kernel<<<div_up(P, 256), 256, 0, s>>>(g.depth_key, g.sort_keys[0], g.sort_vals[0], P);
+}
+
+// ---------------------------------------------------------------------------------------------
+// offsets[i] = exclusive prefix sum over depth order of tiles[order[i]]  (reference: cub InclusiveSum over
+// Gaussian order, rasterizer_impl.cu:278; here over depth order because instances are emitted in depth order)
+__global__ void __launch_bounds__(SORT_THREADS)
+scan_block_sums_kernel(const uint32_t* __restrict__ tiles, const uint32_t* __restrict__ order, int P,
+                       uint32_t* __restrict__ block_sums)
+{
+    __shared__ uint32_t warp_sums[8];
+    const int base = blockIdx.x * SORT_CHUNK + threadIdx.x * SORT_ITEMS;
+    uint32_t sum = 0;
+#pragma unroll
+    for (int i = 0; i < SORT_ITEMS; i++)
+        if (base + i < P) sum += tiles[order[base + i]];
+    uint32_t total;
+    block_exclusive_scan_256(sum, warp_sums, &total);
+    if (threadIdx.x == 0) block_sums[blockIdx.x] = total;
+}
+
+__global__ void __launch_bounds__(SORT_THREADS)
+scan_top_kernel(uint32_t* __restrict__ block_sums, int nblk)
+{
+    __shared__ uint32_t warp_sums[8];
+    const int per = (nblk + SORT_THREADS - 1) / SORT_THREADS;
+    const int lo = threadIdx.x * per, hi = min(nblk, lo + per);
+    uint32_t sum = 0;
+    for (int i = lo; i < hi; i++) sum += block_sums[i];
+    uint32_t run = block_exclusive_scan_256(sum, warp_sums, nullptr);
+    for (int i = lo; i < hi; i++) {
+        const uint32_t v = block_sums[i];
+        block_sums[i] = run;
+        run += v;
+    }
+}
+
+__global__ void __launch_bounds__(SORT_THREADS)
+scan_final_kernel(const uint32_t* __restrict__ tiles, const uint32_t* __restrict__ order, int P,
+                  const uint32_t* __restrict__ block_sums, uint32_t* __restrict__ offsets)
+{
+    __shared__ uint32_t warp_sums[8];
+    const int base = blockIdx.x * SORT_CHUNK + threadIdx.x * SORT_ITEMS;
+    uint32_t v[SORT_ITEMS];
+    uint32_t sum = 0;
+#pragma unroll
+    for (int i = 0; i < SORT_ITEMS; i++) {
+        v[i] = (base + i < P) ? tiles[order[base + i]] : 0u;
+        sum += v[i];
+    }
+    uint32_t run = block_exclusive_scan_256(sum, warp_sums, nullptr) + block_sums[blockIdx.x];
+#pragma unroll
+    for (int i = 0; i < SORT_ITEMS; i++) {
+        if (base + i < P) offsets[base + i] = run;
+        run += v[i];
+    }
+}
+
+void launch_offsets_scan(const uint32_t* tiles, const uint32_t* order, uint32_t* offsets, uint32_t* block_sums,
+                         int P, cudaStream_t s)
+{
+    const int nblk = div_up(P, SORT_CHUNK);
+    scan_block_sums_kernel<<<nblk, SORT_THREADS, 0, s>>>(tiles, order, P, block_sums);
+    scan_top_kernel<<<1, SORT_THREADS, 0, s>>>(block_sums, nblk);
+    scan_final_kernel<<<nblk, SORT_THREADS, 0, s>>>(tiles, order, P, block_sums, offsets);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Instance emit in depth order (reference duplicateWithKeys, rasterizer_impl.cu:70-111, which emits in
+// Gaussian order).  key = tile id only; the depth half of the reference key is implied by the order.
+__global__ void emit_kernel(const uint32_t* __restrict__ order, const uint32_t* __restrict__ tiles,
+                            const uint32_t* __restrict__ offsets, const uint2* __restrict__ rect, int P, int grid_x,
+                            uint32_t* __restrict__ tile_keys, uint32_t* __restrict__ tile_vals)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    const uint32_t gid = order[i];
+    if (tiles[gid] == 0) return;
+    uint32_t off = offsets[i];
+    const uint2 r = rect[gid];
+    const uint32_t x0 = r.x & 0xffffu, x1 = r.x >> 16, y0 = r.y & 0xffffu, y1 = r.y >> 16;
+    for (uint32_t y = y0; y < y1; y++)
+        for (uint32_t x = x0; x < x1; x++) {
+            tile_keys[off] = y * (uint32_t)grid_x + x;
+            tile_vals[off] = gid;
+            off++;
+        }
+}
+
+void launch_emit(const GeomView& g, const uint32_t* order, int P, int grid_x, uint32_t* tile_keys,
+                 uint32_t* tile_vals, cudaStream_t s)
+{
+    emit_kernel<<<div_up(P, 256), 256, 0, s>>>(order, g.tiles, g.offsets, g.rect, P, grid_x, tile_keys, tile_vals);
+}
+
+// ---------------------------------------------------------------------------------------------
+// reference identifyTileRanges (rasterizer_impl.cu:116-138) on the sorted tile ids
+__global__ void tile_ranges_kernel(const uint32_t* __restrict__ sorted_tiles, int64_t R, uint2* __restrict__ ranges)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= R) return;
+    const uint32_t cur = sorted_tiles[i];
+    if (i == 0) ranges[cur].x = 0;
+    else {
+        const uint32_t prev = sorted_tiles[i - 1];
+        if (cur != prev) {
+            ranges[prev].y = (uint32_t)i;
+            ranges[cur].x = (uint32_t)i;
+        }
+    }
+    if (i == R - 1) ranges[cur].y = (uint32_t)R;
+}
+
+void launch_tile_ranges(const uint32_t* sorted_tiles, int64_t R, uint2* ranges, int tiles, cudaStream_t s)
+{
+    cudaMemsetAsync(ranges, 0, sizeof(uint2) * (size_t)tiles, s);
+    if (R > 0) tile_ranges_kernel<<<div_up(R, 256), 256, 0, s>>>(sorted_tiles, R, ranges);
+}
+
+__global__ void build_keys_kernel(const uint32_t* __restrict__ sorted_tiles, const uint32_t* __restrict__ point_list,
+                                  const uint32_t* __restrict__ depth_key, int64_t R, uint64_t* __restrict__ keys_out)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < R) keys_out[i] = ((uint64_t)sorted_tiles[i] << 32) | depth_key[point_list[i]];
+}
+
+void launch_build_keys(const uint32_t* sorted_tiles, const uint32_t* point_list, const uint32_t* depth_key,
+                       int64_t R, uint64_t* keys_out, cudaStream_t s)
+{
+    if (R > 0) build_keys_kernel<<<div_up(R, 256), 256, 0, s>>>(sorted_tiles, point_list, depth_key, R, keys_out);
+}
+
+}  // namespace gsr

@@ -1,0 +1,280 @@
+"""Drop-in replacement for the `diff_gaussian_rasterization` package CF-3DGS imports
+(gaussian_renderer/__init__.py:12, scene/gaussian_model_cf.py:28-31, scene/gaussian_model.py:27-30).
+
+Same public names, argument meaning, return tuple and error behaviour as the reference module
+(submodules/diff-gaussian-rasterization/diff_gaussian_rasterization/__init__.py:17-223); the work is done
+by hand-written sm_100a kernels behind the C ABI of include/gsr.h (libgsr_b200.so) -- no CPU path, no
+PyTorch fallback.  PyTorch is used for device memory, the current stream and autograd plumbing only.
+
+Put `cf-3dgs_b200/` on sys.path (or PYTHONPATH) ahead of any installed reference build and
+`from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer` resolves here.
+"""
+from __future__ import annotations
+
+from typing import NamedTuple, Optional
+
+import torch
+import torch.nn as nn
+
+from . import _cabi
+from ._cabi import check, lib
+
+__all__ = ["GaussianRasterizationSettings", "GaussianRasterizer", "rasterize_gaussians",
+           "cpu_deep_copy_tuple", "rasterizer_state"]
+
+
+def cpu_deep_copy_tuple(input_tuple):
+    return tuple(x.cpu().clone() if isinstance(x, torch.Tensor) else x for x in input_tuple)
+
+
+class GaussianRasterizationSettings(NamedTuple):
+    image_height: int
+    image_width: int
+    tanfovx: float
+    tanfovy: float
+    bg: torch.Tensor
+    scale_modifier: float
+    viewmatrix: torch.Tensor
+    projmatrix: torch.Tensor
+    sh_degree: int
+    campos: torch.Tensor
+    prefiltered: bool
+    debug: bool
+
+
+# ---------------------------------------------------------------------------------------------------
+_pinned_counts = {}
+
+
+def _count_word(device: torch.device) -> torch.Tensor:
+    """One pinned int64 per device: the landing spot of num_rendered (rasterizer_impl.cu:282)."""
+    key = device.index if device.index is not None else torch.cuda.current_device()
+    w = _pinned_counts.get(key)
+    if w is None:
+        w = torch.zeros(2, dtype=torch.int64).pin_memory()
+        _pinned_counts[key] = w
+    return w
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    """Device pointer or NULL for the reference's "empty CPU tensor" sentinels."""
+    if t is None or t.numel() == 0:
+        return None
+    return t.data_ptr()
+
+
+def _dense(t: torch.Tensor, name: str) -> torch.Tensor:
+    if t.numel() == 0:
+        return t
+    if not t.is_cuda:
+        raise RuntimeError(f"{name} must be a CUDA tensor")
+    if t.dtype != torch.float32:
+        raise RuntimeError(f"{name} must be float32")
+    return t.contiguous()
+
+
+def _forward_impl(bg, means3D, colors_precomp, opacities, scales, rotations, scale_modifier, cov3Ds_precomp,
+                  viewmatrix, projmatrix, tanfovx, tanfovy, H, W, sh, degree, campos, prefiltered, debug):
+    """Counterpart of _C.rasterize_gaussians (rasterize_points.cu:35-119); same return tuple."""
+    if means3D.ndim != 2 or means3D.shape[1] != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")
+    dev = means3D.device
+    P = means3D.shape[0]
+    means3D = _dense(means3D, "means3D"); colors_precomp = _dense(colors_precomp, "colors_precomp")
+    opacities = _dense(opacities, "opacities"); scales = _dense(scales, "scales")
+    rotations = _dense(rotations, "rotations"); cov3Ds_precomp = _dense(cov3Ds_precomp, "cov3D_precomp")
+    sh = _dense(sh, "sh"); bg = _dense(bg, "bg"); viewmatrix = _dense(viewmatrix, "viewmatrix")
+    projmatrix = _dense(projmatrix, "projmatrix"); campos = _dense(campos, "campos")
+    M = sh.shape[1] if sh.numel() != 0 else 0
+    f32 = dict(dtype=torch.float32, device=dev)
+    u8 = dict(dtype=torch.uint8, device=dev)
+    color = torch.empty((3, H, W), **f32)
+    depth = torch.empty((1, H, W), **f32)
+    alpha = torch.empty((1, H, W), **f32)
+    radii = torch.empty((P,), dtype=torch.int32, device=dev)
+    if P == 0:
+        color.zero_(); depth.zero_(); alpha.zero_()
+        e = torch.empty(0, **u8)
+        return 0, color, depth, alpha, radii, e, e.clone(), e.clone()
+    with torch.cuda.device(dev):
+        stream = torch.cuda.current_stream().cuda_stream
+        geom = torch.empty(lib.gsr_geometry_bytes(P), **u8)
+        img = torch.empty(lib.gsr_image_bytes(W, H), **u8)
+        word = _count_word(dev)
+        check(lib.gsr_forward_prepare(
+            P, int(degree), int(M), _ptr(means3D), _ptr(scales), float(scale_modifier), _ptr(rotations),
+            _ptr(opacities), _ptr(sh), _ptr(cov3Ds_precomp), _ptr(colors_precomp), _ptr(viewmatrix),
+            _ptr(projmatrix), _ptr(campos), int(W), int(H), float(tanfovx), float(tanfovy), int(bool(prefiltered)),
+            radii.data_ptr(), geom.data_ptr(), geom.numel(), word.data_ptr(), stream, int(bool(debug))))
+        R = int(word[0])
+        binning = torch.empty(lib.gsr_binning_bytes(R, W, H), **u8)
+        check(lib.gsr_forward_render(
+            P, int(W), int(H), R, _ptr(bg), _ptr(colors_precomp), geom.data_ptr(), binning.data_ptr(),
+            binning.numel(), img.data_ptr(), color.data_ptr(), depth.data_ptr(), alpha.data_ptr(), stream,
+            int(bool(debug))))
+    return R, color, depth, alpha, radii, geom, binning, img
+
+
+def _backward_impl(bg, means3D, radii, colors_precomp, scales, rotations, scale_modifier, cov3Ds_precomp,
+                   viewmatrix, projmatrix, tanfovx, tanfovy, grad_color, grad_depth, grad_alpha, sh, degree,
+                   campos, geom, R, binning, img, alpha, debug, want_pose_grad=False):
+    """Counterpart of _C.rasterize_gaussians_backward (rasterize_points.cu:121-208).  Returns the same eight
+    gradients (None where the matching input was absent) plus the optional fused pose gradient."""
+    dev = means3D.device
+    P = means3D.shape[0]
+    H, W = grad_color.shape[1], grad_color.shape[2]
+    M = sh.shape[1] if sh.numel() != 0 else 0
+    f32 = dict(dtype=torch.float32, device=dev)
+    dmeans3D = torch.empty((P, 3), **f32)
+    dmeans2D = torch.empty((P, 3), **f32)
+    dopacity = torch.empty((P, 1), **f32)
+    dcolors = torch.empty((P, 3), **f32) if colors_precomp.numel() else None
+    dsh = torch.empty((P, M, 3), **f32) if sh.numel() else None
+    dscales = torch.empty((P, 3), **f32) if scales.numel() else None
+    drots = torch.empty((P, 4), **f32) if scales.numel() else None
+    dcov3D = torch.empty((P, 6), **f32) if cov3Ds_precomp.numel() else None
+    dpose = torch.empty((6,), **f32) if want_pose_grad else None
+    if P == 0:
+        if dpose is not None:
+            dpose.zero_()
+        return dmeans2D, dcolors, dopacity, dmeans3D, dcov3D, dsh, dscales, drots, dpose
+    grad_color = _dense(grad_color, "grad_color")
+    grad_depth = None if grad_depth is None else _dense(grad_depth, "grad_depth")
+    grad_alpha = None if grad_alpha is None else _dense(grad_alpha, "grad_alpha")
+    with torch.cuda.device(dev):
+        stream = torch.cuda.current_stream().cuda_stream
+        scratch = torch.empty(P * 12, **f32)
+        pose_scratch = torch.empty(lib.gsr_pose_scratch_bytes(P) // 4, **f32) if want_pose_grad else None
+        check(lib.gsr_backward(
+            P, int(degree), int(M), int(W), int(H), int(R), _ptr(bg), _ptr(means3D), radii.data_ptr(),
+            _ptr(colors_precomp), _ptr(scales), _ptr(rotations), float(scale_modifier), _ptr(cov3Ds_precomp),
+            _ptr(viewmatrix), _ptr(projmatrix), _ptr(campos), float(tanfovx), float(tanfovy), _ptr(sh),
+            alpha.data_ptr(), grad_color.data_ptr(), _ptr(grad_depth), _ptr(grad_alpha), geom.data_ptr(),
+            binning.data_ptr(), img.data_ptr(), scratch.data_ptr(), dmeans2D.data_ptr(), _ptr(dcolors),
+            dopacity.data_ptr(), dmeans3D.data_ptr(), _ptr(dcov3D), _ptr(dsh), _ptr(dscales), _ptr(drots),
+            _ptr(dpose), _ptr(pose_scratch), stream, int(bool(debug))))
+    return dmeans2D, dcolors, dopacity, dmeans3D, dcov3D, dsh, dscales, drots, dpose
+
+
+class _RasterizeGaussians(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
+                raster_settings):
+        rs = raster_settings
+        args = (rs.bg, means3D, colors_precomp, opacities, scales, rotations, rs.scale_modifier, cov3Ds_precomp,
+                rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, rs.image_height, rs.image_width, sh,
+                rs.sh_degree, rs.campos, rs.prefiltered, rs.debug)
+        if rs.debug:
+            cpu_args = cpu_deep_copy_tuple(args)  # snapshot before anything can be corrupted
+            try:
+                out = _forward_impl(*args)
+            except Exception:
+                torch.save(cpu_args, "snapshot_fw.dump")
+                print("\nAn error occured in forward. Please forward snapshot_fw.dump for debugging.")
+                raise
+        else:
+            out = _forward_impl(*args)
+        num_rendered, color, depth, alpha, radii, geom, binning, img = out
+        ctx.raster_settings = rs
+        ctx.num_rendered = num_rendered
+        ctx.set_materialize_grads(False)   # absent depth/alpha cotangents arrive as None, not zeros
+        ctx.mark_non_differentiable(radii)
+        ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, geom,
+                              binning, img, alpha)
+        return color, radii, depth, alpha
+
+    @staticmethod
+    def backward(ctx, grad_color, grad_radii, grad_depth, grad_alpha):
+        rs = ctx.raster_settings
+        colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, geom, binning, img, alpha = \
+            ctx.saved_tensors
+        if grad_color is None:
+            grad_color = torch.zeros((3, rs.image_height, rs.image_width), dtype=torch.float32,
+                                     device=means3D.device)
+        args = (rs.bg, means3D, radii, colors_precomp, scales, rotations, rs.scale_modifier, cov3Ds_precomp,
+                rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, grad_color, grad_depth, grad_alpha, sh,
+                rs.sh_degree, rs.campos, geom, ctx.num_rendered, binning, img, alpha, rs.debug)
+        if rs.debug:
+            cpu_args = cpu_deep_copy_tuple(args)
+            try:
+                res = _backward_impl(*args)
+            except Exception:
+                torch.save(cpu_args, "snapshot_bw.dump")
+                print("\nAn error occured in backward. Writing snapshot_bw.dump for debugging.\n")
+                raise
+        else:
+            res = _backward_impl(*args)
+        dmeans2D, dcolors, dopacity, dmeans3D, dcov3D, dsh, dscales, drots, _ = res
+        return dmeans3D, dmeans2D, dsh, dcolors, dopacity, dscales, drots, dcov3D, None
+
+
+def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
+                        raster_settings):
+    return _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
+                                     cov3Ds_precomp, raster_settings)
+
+
+class GaussianRasterizer(nn.Module):
+    def __init__(self, raster_settings):
+        super().__init__()
+        self.raster_settings = raster_settings
+
+    def markVisible(self, positions):
+        """Boolean mask of points in front of the near cull plane (view z > 0.2)."""
+        with torch.no_grad():
+            rs = self.raster_settings
+            positions = _dense(positions, "positions")
+            P = positions.shape[0]
+            visible = torch.zeros((P,), dtype=torch.bool, device=positions.device)
+            if P:
+                with torch.cuda.device(positions.device):
+                    check(lib.gsr_mark_visible(P, positions.data_ptr(), _dense(rs.viewmatrix, "viewmatrix").data_ptr(),
+                                               _dense(rs.projmatrix, "projmatrix").data_ptr(), visible.data_ptr(),
+                                               torch.cuda.current_stream().cuda_stream))
+        return visible
+
+    def forward(self, means3D, means2D, opacities, shs=None, colors_precomp=None, scales=None, rotations=None,
+                cov3D_precomp=None):
+        rs = self.raster_settings
+        if (shs is None) == (colors_precomp is None):
+            raise Exception('Please provide excatly one of either SHs or precomputed colors!')
+        have_sr = scales is not None or rotations is not None
+        if ((scales is None or rotations is None) and cov3D_precomp is None) or (have_sr and cov3D_precomp is not None):
+            raise Exception('Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!')
+        empty = torch.Tensor([])
+        shs = empty if shs is None else shs
+        colors_precomp = empty if colors_precomp is None else colors_precomp
+        scales = empty if scales is None else scales
+        rotations = empty if rotations is None else rotations
+        cov3D_precomp = empty if cov3D_precomp is None else cov3D_precomp
+        return rasterize_gaussians(means3D, means2D, shs, colors_precomp, opacities, scales, rotations,
+                                   cov3D_precomp, rs)
+
+
+def rasterizer_state(P, W, H, num_rendered, geom, binning, img):
+    """Parity accessor (not in the reference API): the reference-visible contents of the three workspaces --
+    sorted 64-bit keys, point list, tile ranges, n_contrib and the per-Gaussian intermediates -- as tensors."""
+    dev = geom.device
+    R = int(num_rendered)
+    tiles = ((W + 15) // 16) * ((H + 15) // 16)
+    out = dict(
+        keys_sorted=torch.zeros(R, dtype=torch.int64, device=dev),
+        point_list=torch.zeros(R, dtype=torch.int32, device=dev),
+        ranges=torch.zeros((tiles, 2), dtype=torch.int32, device=dev),
+        n_contrib=torch.zeros((H, W), dtype=torch.int32, device=dev),
+        depths=torch.zeros(P, dtype=torch.float32, device=dev),
+        means2D=torch.zeros((P, 2), dtype=torch.float32, device=dev),
+        conic_opacity=torch.zeros((P, 4), dtype=torch.float32, device=dev),
+        rgb=torch.zeros((P, 3), dtype=torch.float32, device=dev),
+        tiles_touched=torch.zeros(P, dtype=torch.int32, device=dev),
+        clamped=torch.zeros((P, 3), dtype=torch.uint8, device=dev),
+    )
+    if P:
+        with torch.cuda.device(dev):
+            check(lib.gsr_debug_dump(P, W, H, R, geom.data_ptr(), binning.data_ptr(), img.data_ptr(),
+                                     _ptr(out["keys_sorted"]), _ptr(out["point_list"]), out["ranges"].data_ptr(),
+                                     out["n_contrib"].data_ptr(), out["depths"].data_ptr(), out["means2D"].data_ptr(),
+                                     out["conic_opacity"].data_ptr(), out["rgb"].data_ptr(),
+                                     out["tiles_touched"].data_ptr(), out["clamped"].data_ptr(),
+                                     torch.cuda.current_stream().cuda_stream))
+    return out

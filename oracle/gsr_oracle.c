@@ -215,7 +215,7 @@ int64_t gsro_preprocess(int P, int D, int M, const float* means, const float* sc
         rects[4 * i] = rects[4 * i + 1] = rects[4 * i + 2] = rects[4 * i + 3] = 0;
         const float* p = means + 3 * i;
         const float depth = xform_row(V, 2, p[0], p[1], p[2]);
-        if (!(depth > 0.2f)) continue; /* auxiliary.h:154 */
+        if (depth <= 0.2f) continue; /* auxiliary.h:154 */
         const float hw = xform_row(Pm, 3, p[0], p[1], p[2]);
         const float hx = xform_row(Pm, 0, p[0], p[1], p[2]);
         const float hy = xform_row(Pm, 1, p[0], p[1], p[2]);
@@ -688,7 +688,7 @@ void gsro_mark_visible(int P, const float* means, const float* V, uint8_t* prese
 {
     for (int i = 0; i < P; i++) {
         const float* p = means + 3 * i;
-        present[i] = xform_row(V, 2, p[0], p[1], p[2]) > 0.2f;
+        present[i] = !(xform_row(V, 2, p[0], p[1], p[2]) <= 0.2f);
     }
 }
 
