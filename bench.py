@@ -1,0 +1,395 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the B200 Gaussian-splatting rasterizer hot path.
+
+Metric (BASELINE.json): forward+backward rendered frames/s at 1920x1080.
+Workload at N=1: `gvol_1M_1080p_sh3` -- synthetic G-vol scene, 1,000,000 Gaussians, SH degree 3,
+one fwd+bwd rasterization per step through the reference-shaped API (GaussianRasterizer autograd Function ->
+C ABI -> sm_100a kernels), colour cotangent only (CF-3DGS default: depth/alpha losses off).
+N>1: every rank holds a replica of the scene, renders its own view, then the flat 59-float/Gaussian gradient is
+summed with one NCCL all-reduce; weak scaling, value = N * frames / max-over-ranks time.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+`--impl reference` times the UNMODIFIED reference rasterizer: its own CUDA build from oracle/_ref (compiled by
+oracle/build_ref.py from the sources under /root/reference) when that exists and a GPU is present, otherwise the
+CPU oracle port on a bounded sample.  The oracle is only ever the checker / baseline here, never the product path.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import math
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(ROOT, "cf-3dgs_b200"))
+sys.path.insert(0, ROOT)
+
+import numpy as np
+import torch
+
+WORKLOAD = dict(name="gvol_1M_1080p_sh3", P=1_000_000, W=1920, H=1080, seed=5, sh_degree=3)
+PARAM_KEYS = ["means3D", "opacities", "shs", "scales", "rotations"]
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return float(d.get("hbm_gbs", 6650.0)), "measured"
+    return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index = index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return None
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            parts = [x.strip() for x in r.split(",")]
+            if len(parts) < 7:
+                continue
+            try:
+                sm.append(float(parts[0])); mx.append(float(parts[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, parts[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        if not sm:
+            return None
+        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def dist_setup(n_gpus):
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29500")
+        backend = "nccl" if torch.cuda.is_available() else "gloo"
+        dist.init_process_group(backend=backend, rank=rank, world_size=world)
+    return world, rank, local
+
+
+def rank_camera(S, W, H, rank, world):
+    """View of rank r: yaw offset around the canonical camera so every rank renders different pixels."""
+    if world == 1:
+        return S.make_camera(W, H)
+    yaw = (rank - (world - 1) / 2.0) * 1.5
+    a = math.radians(yaw)
+    R = np.array([[math.cos(a), 0, math.sin(a)], [0, 1, 0], [-math.sin(a), 0, math.cos(a)]])
+    return S.make_camera(W, H, R=R, t=np.array([0.02 * (rank - (world - 1) / 2.0), 0.0, 0.0]))
+
+
+def timed(step, K, warm, world, dev, clock_index=None):
+    import torch.distributed as dist
+    for _ in range(warm):
+        step()
+    sampler = ClockSampler(clock_index) if clock_index is not None else None
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize(dev)
+    if sampler:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(K):
+        step()
+    e1.record()
+    torch.cuda.synchronize(dev)
+    if world > 1:
+        dist.barrier()
+    ms = e0.elapsed_time(e1)
+    clocks = sampler.stop() if sampler else None
+    if world > 1:
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    return ms, clocks
+
+
+def cpu_oracle_baseline(S, wl, cam, sample_frac=1.0):
+    """C oracle port, OpenMP over all host cores, one fwd+bwd frame of the same workload."""
+    from oracle import oracle as O
+    sc = S.make_gvol(wl["P"], wl["W"], wl["H"], seed=wl["seed"], sh_degree=wl["sh_degree"])
+    ct = S.cotangents(wl["W"], wl["H"], seed=1, dense=False)
+    cores = os.cpu_count() or 1
+    t0 = time.time()
+    st = O.forward(sc["means3D"].numpy(), sc["opacities"].numpy(), shs=sc["shs"].numpy(), scales=sc["scales"].numpy(),
+                   rotations=sc["rotations"].numpy(), viewmatrix=cam["viewmatrix"].numpy(),
+                   projmatrix=cam["projmatrix"].numpy(), campos=cam["campos"].numpy(), bg=np.zeros(3, np.float32),
+                   W=wl["W"], H=wl["H"], tanfovx=cam["tanfovx"], tanfovy=cam["tanfovy"], sh_degree=wl["sh_degree"])
+    O.backward(st, ct["grad_color"].numpy())
+    dt = time.time() - t0
+    return {"value": 1.0 / dt, "unit": "frames/s", "cores": cores, "kind": "port",
+            "sample": f"1 full fwd+bwd frame of {wl['name']} (C oracle, OpenMP {cores} threads, {dt:.2f} s)"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    world, rank, local = dist_setup(args.gpus)
+    import gsr_synth as S
+    wl = dict(WORKLOAD)
+    W, H, P = wl["W"], wl["H"], wl["P"]
+
+    have_gpu = torch.cuda.is_available()
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        from oracle import ref_cuda as RC
+        if not (have_gpu and RC.available()):
+            cam = S.make_camera(W, H)
+            cb = cpu_oracle_baseline(S, wl, cam)
+            line = {"impl": "reference", "metric": "fwd+bwd rendered frames/s at 1080p", "value": cb["value"],
+                    "unit": "frames/s", "n_gpus": args.gpus, "steps": 1, "warmup": 0, "ms_per_step": 1000.0 / cb["value"],
+                    "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                    "config": {"workload": wl["name"], "P": P, "W": W, "H": H, "sh_degree": wl["sh_degree"]},
+                    "cpu_baseline": cb, "gpu_launches": 0,
+                    "e2e": {"value": cb["value"], "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+            print(json.dumps(line))
+            return 0
+
+    if not have_gpu:
+        raise SystemExit("bench.py needs a CUDA device: the product path has no CPU fallback")
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    cam = rank_camera(S, W, H, rank, world)
+    sc = S.make_gvol(P, W, H, seed=wl["seed"], sh_degree=wl["sh_degree"])
+    params = {k: sc[k].to(dev) for k in PARAM_KEYS}
+    bg = torch.zeros(3, device=dev)
+    view, proj, campos = cam["viewmatrix"].to(dev), cam["projmatrix"].to(dev), cam["campos"].to(dev)
+    gc = S.cotangents(W, H, seed=1, dense=False)["grad_color"].to(dev)
+    flat_grad = torch.empty(P * 59, device=dev) if world > 1 else None
+    state = {}
+
+    if args.impl == "ours":
+        import diff_gaussian_rasterization as D
+        lib = D.lib
+        rs = D.GaussianRasterizationSettings(image_height=H, image_width=W, tanfovx=cam["tanfovx"], tanfovy=cam["tanfovy"],
+                                             bg=bg, scale_modifier=1.0, viewmatrix=view, projmatrix=proj,
+                                             sh_degree=wl["sh_degree"], campos=campos, prefiltered=False, debug=False)
+
+        def render(leaves, m2d, settings=rs):
+            return D.GaussianRasterizer(settings)(leaves["means3D"], m2d, leaves["opacities"], shs=leaves["shs"],
+                                                  scales=leaves["scales"], rotations=leaves["rotations"])
+    else:
+        from oracle import ref_cuda as RC
+
+        class _RefFn(torch.autograd.Function):
+            @staticmethod
+            def forward(ctx, means3D, opac, shs, scales, rots, v, pj, cp):
+                st = RC.forward(means3D, opac, shs=shs, scales=scales, rotations=rots, viewmatrix=v, projmatrix=pj,
+                                campos=cp, bg=bg, W=W, H=H, tanfovx=cam["tanfovx"], tanfovy=cam["tanfovy"],
+                                sh_degree=wl["sh_degree"])
+                ctx.st = st
+                return st["color"], st["depth"], st["alpha"]
+
+            @staticmethod
+            def backward(ctx, gcol, gdep, galp):
+                g = RC.backward(ctx.st, gcol.contiguous(), gdep.contiguous(), galp.contiguous())
+                return g["means3D"], g["opacities"], g["sh"], g["scales"], g["rotations"], None, None, None
+
+        def render(leaves, m2d, settings=None):
+            v, pj, cp = (view, proj, campos) if settings is None else settings
+            c, d, a = _RefFn.apply(leaves["means3D"], leaves["opacities"], leaves["shs"], leaves["scales"],
+                                   leaves["rotations"], v, pj, cp)
+            return c, None, d, a
+
+    def step():
+        leaves = {k: v.detach().requires_grad_(True) for k, v in params.items()}
+        m2d = torch.zeros_like(leaves["means3D"], requires_grad=True) if args.impl == "ours" else None
+        out = render(leaves, m2d)
+        out[0].backward(gc)
+        if world > 1:
+            import torch.distributed as dist
+            off = 0
+            for k in PARAM_KEYS:
+                g = leaves[k].grad
+                flat_grad[off:off + g.numel()].copy_(g.reshape(-1))
+                off += g.numel()
+            dist.all_reduce(flat_grad)
+        state["leaves"] = leaves
+
+    # ---- device-resident throughput ----
+    ms, clocks = timed(step, args.steps, args.warmup, world, dev, clock_index=local if rank == 0 else None)
+    value = world * args.steps / (ms / 1000.0)
+
+    # ---- end to end: per step the camera + target image come from pinned host memory, the loss goes back ----
+    tgt_host = torch.rand(3, H, W).pin_memory()
+    view_h, proj_h, cam_h = cam["viewmatrix"].pin_memory(), cam["projmatrix"].pin_memory(), cam["campos"].pin_memory()
+    tgt_dev = torch.empty(3, H, W, device=dev)
+    view_d, proj_d, cam_d = torch.empty_like(view), torch.empty_like(proj), torch.empty_like(campos)
+    loss_host = torch.zeros(1).pin_memory()
+    h2d = tgt_host.numel() * 4 + (view_h.numel() + proj_h.numel() + cam_h.numel()) * 4
+    d2h = 4
+
+    def e2e_step():
+        tgt_dev.copy_(tgt_host, non_blocking=True)
+        view_d.copy_(view_h, non_blocking=True); proj_d.copy_(proj_h, non_blocking=True); cam_d.copy_(cam_h, non_blocking=True)
+        leaves = {k: v.detach().requires_grad_(True) for k, v in params.items()}
+        if args.impl == "ours":
+            st2 = rs._replace(viewmatrix=view_d, projmatrix=proj_d, campos=cam_d)
+            m2d = torch.zeros_like(leaves["means3D"], requires_grad=True)
+        else:
+            st2, m2d = (view_d, proj_d, cam_d), None
+        color = render(leaves, m2d, st2)[0]
+        loss = (color - tgt_dev).abs().mean()
+        loss.backward()
+        if world > 1:
+            import torch.distributed as dist
+            off = 0
+            for k in PARAM_KEYS:
+                g = leaves[k].grad
+                flat_grad[off:off + g.numel()].copy_(g.reshape(-1))
+                off += g.numel()
+            dist.all_reduce(flat_grad)
+        loss_host.copy_(loss.detach().reshape(1), non_blocking=True)
+        torch.cuda.current_stream().synchronize()   # the caller reads the loss every step
+
+    e2e_ms, _ = timed(e2e_step, args.steps, 3, world, dev)
+    e2e_value = world * args.steps / (e2e_ms / 1000.0)
+
+    if rank != 0:
+        return 0
+    line = {"metric": "fwd+bwd rendered frames/s at 1080p", "value": value, "unit": "frames/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": wl["name"], "P": P, "W": W, "H": H, "sh_degree": wl["sh_degree"],
+                       "cotangents": "colour only (CF-3DGS default)", "parallelism": f"dp{world}",
+                       "l2": "per-step working set ~0.9 GB > 126 MB L2, no explicit flush"},
+            "gaussians_per_s": value * P, "clocks": clocks,
+            "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "what": "camera + target image H2D from pinned memory, L1 loss, backward, loss D2H, per step"}}
+    if args.impl == "reference":
+        line["impl"] = "reference"
+        line["gpu_launches"] = 0
+        line["cpu_baseline"] = {"value": value, "unit": "frames/s", "cores": 0, "kind": "reference",
+                                "sample": "the reference's own CUDA rasterizer (oracle/_ref, unmodified sources, sm_100a) "
+                                          "on this GPU: it has no CPU implementation"}
+        print(json.dumps(line))
+        return 0
+
+    # ---- per-stage timing, work counters, roofline of the dominant kernel ----
+    hbm_peak, peak_kind = load_peaks()
+    n_st = lib.gsr_profile_count()
+    names = [lib.gsr_profile_name(i).decode() for i in range(n_st)]
+    import ctypes
+    acc = np.zeros(n_st)
+    reps = 5
+    lib.gsr_profile_enable(1)
+    for _ in range(reps):
+        step()
+        buf = (ctypes.c_float * n_st)()
+        lib.gsr_profile_read(buf, n_st)
+        acc += np.maximum(np.array(buf[:]), 0.0)
+    lib.gsr_profile_enable(0)
+    stage_ms = {n: float(a / reps) for n, a in zip(names, acc)}
+    # work counters from one more forward
+    leaves = {k: v.detach().requires_grad_(True) for k, v in params.items()}
+    out = render(leaves, torch.zeros_like(leaves["means3D"], requires_grad=True))
+    fn = out[0].grad_fn
+    geom, binning, img = fn.saved_tensors[7], fn.saved_tensors[8], fn.saved_tensors[9]
+    R = fn.num_rendered
+    counts = torch.zeros(4, dtype=torch.int64, device=dev)
+    lib.gsr_debug_pair_counts(P, W, H, R, geom.data_ptr(), binning.data_ptr(), img.data_ptr(), counts.data_ptr(),
+                              torch.cuda.current_stream().cuda_stream)
+    in_range, blended, ref_pairs, tile_rej = [int(x) for x in counts.tolist()]
+    P_vis = int((out[1] > 0).sum())
+    tiles = ((W + 15) // 16) * ((H + 15) // 16)
+    sm_mhz = (clocks or {}).get("sm_mhz") or 1500.0
+    n_sm = torch.cuda.get_device_properties(dev).multi_processor_count
+    fp32_peak = n_sm * 128 * 2 * sm_mhz * 1e6 / 1e12
+    # algorithmic work: bytes for the HBM-bound stages, flops for the blend kernels
+    alg = {
+        "preprocess": ("hbm", (P_vis * 311 + (P - P_vis) * 20) / 1e9),
+        "depth_sort": ("hbm", P * 16 / 1e9),
+        "offsets_scan": ("hbm", P * 8 / 1e9),
+        "emit": ("hbm", (P * 20 + R * 12) / 1e9),
+        "tile_sort": ("hbm", R * 24 / 1e9),
+        "tile_ranges": ("hbm", (R * 8 + tiles * 8) / 1e9),
+        "render_forward": ("fp32", (in_range * 24 + blended * 16) / 1e12),
+        "render_backward": ("fp32", (blended * 75 + (in_range - blended) * 24) / 1e12),
+        "preprocess_backward": ("hbm", P_vis * 627 / 1e9),
+    }
+    stages = {}
+    for n, (bound, work) in alg.items():
+        t = stage_ms.get(n, 0.0)
+        if t <= 0:
+            continue
+        ach = work / (t / 1000.0)
+        peak = hbm_peak if bound == "hbm" else fp32_peak
+        stages[n] = {"ms": t, "bound": bound, "achieved": ach, "unit": "GB/s" if bound == "hbm" else "TFLOP/s",
+                     "frac": ach / peak}
+    dom = max(stages, key=lambda k: stages[k]["ms"])
+    d = stages[dom]
+    line["roofline"] = {"kernel": dom, "bound": d["bound"], "achieved": d["achieved"],
+                        "peak": hbm_peak if d["bound"] == "hbm" else fp32_peak, "unit": d["unit"], "frac": d["frac"],
+                        "traffic": None, "ms": d["ms"],
+                        "peak_source": (f"{peak_kind} HBM copy" if d["bound"] == "hbm" else
+                                        f"derived FP32 FMA peak {n_sm} SMs x 128 lanes x 2 x {sm_mhz:.0f} MHz (median SM clock "
+                                        "under load); MEASURED_PEAKS.json holds no FP32 figure")}
+    line["stages"] = stages
+    line["work"] = {"num_rendered": R, "visible": P_vis, "pairs_in_range": in_range, "pairs_blended": blended,
+                    "reference_pairs_no_early_exit": ref_pairs, "tile_rejected_entries": tile_rej}
+    depth_passes, tile_passes = 4, (max(1, (tiles - 1).bit_length()) + 7) // 8
+    line["gpu_launches"] = args.steps * (1 + 1 + 3 * depth_passes + 3 + 1 + 3 * tile_passes + 1 + 1 + 1 + 1)
+    if world == 1 and not args.no_cpu_baseline:
+        try:
+            line["cpu_baseline"] = cpu_oracle_baseline(S, wl, S.make_camera(W, H))
+        except Exception as ex:  # the CPU checker must never take the GPU number down with it
+            line["cpu_baseline"] = {"error": str(ex)}
+    print(json.dumps(line))
+    return 0
+
+
+if __name__ == "__main__":
+    rc = main()
+    if torch.distributed.is_available() and torch.distributed.is_initialized():
+        torch.distributed.destroy_process_group()
+    sys.exit(rc)

@@ -30,6 +30,23 @@ int fail(int code, const char* fmt, ...)
         if (e_ != cudaSuccess) return fail(GSR_ERR_CUDA, "%s: %s", name, cudaGetErrorString(e_)); \
     } while (0)
 
+// ---- stage timing ------------------------------------------------------------------------------
+enum Stage { ST_PREPROCESS, ST_DEPTH_SORT, ST_OFFSETS, ST_EMIT, ST_TILE_SORT, ST_RANGES, ST_RENDER_FWD,
+             ST_GRAD_ZERO, ST_RENDER_BWD, ST_PREPROCESS_BWD, ST_COUNT };
+const char* const kStageNames[ST_COUNT] = {"preprocess", "depth_sort", "offsets_scan", "emit", "tile_sort",
+                                           "tile_ranges", "render_forward", "grad_zero", "render_backward",
+                                           "preprocess_backward"};
+bool g_prof_on = false;
+cudaEvent_t g_ev[ST_COUNT][2];
+bool g_ev_made = false;
+bool g_ev_used[ST_COUNT];
+
+struct StageTimer {
+    int st; cudaStream_t s;
+    StageTimer(int st_, cudaStream_t s_) : st(st_), s(s_) { if (g_prof_on) cudaEventRecord(g_ev[st][0], s); }
+    ~StageTimer() { if (g_prof_on) { cudaEventRecord(g_ev[st][1], s); g_ev_used[st] = true; } }
+};
+
 int tile_bits(int tiles)
 {
     int bits = 0;
@@ -100,7 +117,7 @@ int gsr_forward_prepare(int P, int sh_degree, int M, const float* means3D, const
     a.opacities = opacities; a.shs = shs; a.cov3D_precomp = cov3D_precomp; a.colors_precomp = colors_precomp;
     a.viewmatrix = viewmatrix; a.projmatrix = projmatrix; a.campos = campos ? campos : viewmatrix;
     a.W = W; a.H = H; a.tanfovx = tanfovx; a.tanfovy = tanfovy; a.prefiltered = prefiltered; a.radii = radii;
-    launch_preprocess(a, g, s);
+    { StageTimer t(ST_PREPROCESS, s); launch_preprocess(a, g, s); }
     GSR_STAGE("preprocess");
 
     // "how many instances?" travels to the host (8 bytes, into the caller's -- ideally pinned -- word) while
@@ -112,12 +129,15 @@ int gsr_forward_prepare(int P, int sh_degree, int M, const float* means3D, const
     cudaEventRecord(ev, s);
 
     // low 32 key bits (depth) sorted over Gaussians, before duplication
-    launch_init_sort_input(g, P, s);
-    const int cur = radix_sort_pairs(g.sort_keys, g.sort_vals, P, 0, 32, g.hist, g.digit_total, s);
-    if (cur != 0) {  // keep the invariant "sort_vals[0] holds the depth order"
-        cudaMemcpyAsync(g.sort_vals[0], g.sort_vals[1], sizeof(uint32_t) * (size_t)P, cudaMemcpyDeviceToDevice, s);
+    {
+        StageTimer t(ST_DEPTH_SORT, s);
+        launch_init_sort_input(g, P, s);
+        const int cur = radix_sort_pairs(g.sort_keys, g.sort_vals, P, 0, 32, g.hist, g.digit_total, s);
+        if (cur != 0) {  // keep the invariant "sort_vals[0] holds the depth order"
+            cudaMemcpyAsync(g.sort_vals[0], g.sort_vals[1], sizeof(uint32_t) * (size_t)P, cudaMemcpyDeviceToDevice, s);
+        }
     }
-    launch_offsets_scan(g.tiles, g.sort_vals[0], g.offsets, g.block_sums, P, s);
+    { StageTimer t(ST_OFFSETS, s); launch_offsets_scan(g.tiles, g.sort_vals[0], g.offsets, g.block_sums, P, s); }
 
     e = cudaEventSynchronize(ev);
     cudaEventDestroy(ev);
@@ -159,18 +179,24 @@ int gsr_forward_render(int P, int W, int H, int64_t num_rendered, const float* b
     const int gx = div_up(W, TILE), gy = div_up(H, TILE), tiles = gx * gy;
 
     if (num_rendered > 0) {
-        launch_emit(g, g.sort_vals[0], P, gx, b.keys[0], b.vals[0], s);
+        { StageTimer t(ST_EMIT, s); launch_emit(g, g.sort_vals[0], P, gx, b.keys[0], b.vals[0], s); }
         GSR_STAGE("emit");
-        const int cur = radix_sort_pairs(b.keys, b.vals, num_rendered, 0, tile_bits(tiles), b.hist, b.digit_total, s);
-        if (cur != 0) {  // invariant: keys[0]/vals[0] hold the sorted list
-            cudaMemcpyAsync(b.keys[0], b.keys[1], sizeof(uint32_t) * (size_t)num_rendered, cudaMemcpyDeviceToDevice, s);
-            cudaMemcpyAsync(b.vals[0], b.vals[1], sizeof(uint32_t) * (size_t)num_rendered, cudaMemcpyDeviceToDevice, s);
+        {
+            StageTimer t(ST_TILE_SORT, s);
+            const int cur = radix_sort_pairs(b.keys, b.vals, num_rendered, 0, tile_bits(tiles), b.hist, b.digit_total, s);
+            if (cur != 0) {  // invariant: keys[0]/vals[0] hold the sorted list
+                cudaMemcpyAsync(b.keys[0], b.keys[1], sizeof(uint32_t) * (size_t)num_rendered, cudaMemcpyDeviceToDevice, s);
+                cudaMemcpyAsync(b.vals[0], b.vals[1], sizeof(uint32_t) * (size_t)num_rendered, cudaMemcpyDeviceToDevice, s);
+            }
         }
         GSR_STAGE("tile sort");
     }
-    launch_tile_ranges(b.keys[0], num_rendered, iv.ranges, tiles, s);
+    { StageTimer t(ST_RANGES, s); launch_tile_ranges(b.keys[0], num_rendered, iv.ranges, tiles, s); }
     GSR_STAGE("tile ranges");
-    launch_render_forward(W, H, iv.ranges, b.vals[0], g, background, out_color, out_depth, out_alpha, iv.n_contrib, s);
+    {
+        StageTimer t(ST_RENDER_FWD, s);
+        launch_render_forward(W, H, iv.ranges, b.vals[0], g, background, out_color, out_depth, out_alpha, iv.n_contrib, s);
+    }
     GSR_STAGE("render");
     return GSR_OK;
 }
@@ -208,12 +234,13 @@ int gsr_backward(int P, int sh_degree, int M, int W, int H, int64_t num_rendered
     BinView b;
     bin_layout((char*)binning, num_rendered, b);
 
-    cudaMemsetAsync(grad_scratch, 0, (size_t)P * 12 * sizeof(float), s);
+    { StageTimer t(ST_GRAD_ZERO, s); cudaMemsetAsync(grad_scratch, 0, (size_t)P * 12 * sizeof(float), s); }
     if (num_rendered > 0) {
+        StageTimer t(ST_RENDER_BWD, s);
         launch_render_backward(W, H, iv.ranges, b.vals[0], g, background, out_alpha, iv.n_contrib, dL_dout_color,
                                dL_dout_depth, dL_dout_alpha, (float*)grad_scratch, s);
-        GSR_STAGE("render backward");
     }
+    GSR_STAGE("render backward");
     PreprocessBwdArgs a;
     a.P = P; a.D = sh_degree; a.M = M;
     a.means3D = means3D; a.radii = radii; a.shs = shs; a.scales = scales; a.rotations = rotations;
@@ -225,7 +252,7 @@ int gsr_backward(int P, int sh_degree, int M, int W, int H, int64_t num_rendered
     a.dL_dmeans3D = dL_dmeans3D; a.dL_dcov3D = dL_dcov3D; a.dL_dsh = shs ? dL_dsh : nullptr;
     a.dL_dscales = scales ? dL_dscales : nullptr; a.dL_drotations = scales ? dL_drotations : nullptr;
     a.dL_dpose = dL_dpose; a.pose_scratch = (float*)pose_scratch;
-    launch_preprocess_backward(a, g, s);
+    { StageTimer t(ST_PREPROCESS_BWD, s); launch_preprocess_backward(a, g, s); }
     GSR_STAGE("preprocess backward");
     return GSR_OK;
 }
@@ -294,6 +321,56 @@ int gsr_debug_dump(int P, int W, int H, int64_t num_rendered, const void* geomet
     if (n_contrib) cudaMemcpyAsync(n_contrib, iv.n_contrib, sizeof(uint32_t) * (size_t)W * H, cudaMemcpyDeviceToDevice, s);
     unpack_geom_kernel<<<div_up(P, 256), 256, 0, s>>>(P, g, depths, means2D, conic_opacity, rgb, tiles_touched, clamped);
     GSR_STAGE("debug dump");
+    return GSR_OK;
+}
+
+int gsr_profile_enable(int on)
+{
+    if (on && !g_ev_made) {
+        for (int i = 0; i < ST_COUNT; i++)
+            for (int k = 0; k < 2; k++) {
+                cudaError_t e = cudaEventCreate(&g_ev[i][k]);
+                if (e != cudaSuccess) return fail(GSR_ERR_CUDA, "event: %s", cudaGetErrorString(e));
+            }
+        g_ev_made = true;
+    }
+    for (int i = 0; i < ST_COUNT; i++) g_ev_used[i] = false;
+    g_prof_on = on != 0;
+    return GSR_OK;
+}
+
+int gsr_profile_count(void) { return ST_COUNT; }
+
+const char* gsr_profile_name(int i) { return (i >= 0 && i < ST_COUNT) ? kStageNames[i] : ""; }
+
+int gsr_profile_read(float* ms_out, int capacity)
+{
+    if (!ms_out) return fail(GSR_ERR_INVALID, "ms_out is NULL");
+    for (int i = 0; i < ST_COUNT && i < capacity; i++) {
+        ms_out[i] = -1.f;
+        if (!g_ev_made || !g_ev_used[i]) continue;
+        cudaError_t e = cudaEventSynchronize(g_ev[i][1]);
+        if (e == cudaSuccess) e = cudaEventElapsedTime(&ms_out[i], g_ev[i][0], g_ev[i][1]);
+        if (e != cudaSuccess) return fail(GSR_ERR_CUDA, "profile read: %s", cudaGetErrorString(e));
+    }
+    return GSR_OK;
+}
+
+int gsr_debug_pair_counts(int P, int W, int H, int64_t num_rendered, const void* geometry, const void* binning,
+                          const void* image, uint64_t* counts, void* stream)
+{
+    cudaStream_t s = (cudaStream_t)stream;
+    const int debug = 1;
+    if (!counts) return fail(GSR_ERR_INVALID, "counts is NULL");
+    if (P == 0) { cudaMemsetAsync(counts, 0, 4 * sizeof(uint64_t), s); return GSR_OK; }
+    GeomView g;
+    geom_layout((char*)geometry, P, g);
+    ImageView iv;
+    image_layout((char*)image, W, H, iv);
+    BinView b;
+    bin_layout((char*)binning, num_rendered, b);
+    launch_pair_counts(W, H, iv.ranges, b.vals[0], g, iv.n_contrib, (unsigned long long*)counts, s);
+    GSR_STAGE("pair counts");
     return GSR_OK;
 }
 

@@ -46,7 +46,9 @@ void launch_render_forward(int W, int H, const uint2* ranges, const uint32_t* po
                            const float* bg, float* out_color, float* out_depth, float* out_alpha,
                            uint32_t* n_contrib, cudaStream_t s);
 
-struct RasterGrad;  // 12 floats per Gaussian, see gsr_render_bwd.cu
+void launch_pair_counts(int W, int H, const uint2* ranges, const uint32_t* point_list, const GeomView& g,
+                        const uint32_t* n_contrib, unsigned long long* counts, cudaStream_t s);
+
 void launch_render_backward(int W, int H, const uint2* ranges, const uint32_t* point_list, const GeomView& g,
                             const float* bg, const float* out_alpha, const uint32_t* n_contrib,
                             const float* dL_dcolor, const float* dL_ddepth, const float* dL_dalpha,

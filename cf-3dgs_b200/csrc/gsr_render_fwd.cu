@@ -100,6 +100,56 @@ render_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges
     }
 }
 
+// Work counters for roofline accounting (see gsr_debug_pair_counts in include/gsr.h).
+__global__ void __launch_bounds__(BLEND_THREADS)
+pair_counts_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
+                   GeomView g, const uint32_t* __restrict__ n_contrib, unsigned long long* __restrict__ counts)
+{
+    __shared__ Staged sm;
+    const int tile = blockIdx.x;
+    const int tile_x = tile % grid_x, tile_y = tile / grid_x;
+    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int pix_x = tile_x * TILE + (warp & 1) * FOOT_W + (lane & 7), pix_y = tile_y * TILE + (warp >> 1) * FOOT_H + (lane >> 3);
+    const bool inside = pix_x < W && pix_y < H;
+    const float pxf = (float)pix_x, pyf = (float)pix_y;
+    const uint2 range = ranges[tile];
+    const int total = (int)(range.y - range.x);
+    const int last = inside ? (int)n_contrib[(size_t)W * pix_y + pix_x] : 0;
+    unsigned long long in_range = 0, blended = 0, tile_rej = 0;
+    for (int base = 0; base < total; base += BATCH) {
+        __syncthreads();
+        const int n = min(BATCH, total - base);
+        if ((int)threadIdx.x < n) {
+            stage_entry(sm, threadIdx.x, point_list[range.x + base + threadIdx.x], g, (float)(tile_x * TILE), (float)(tile_y * TILE));
+            if (sm.thr[threadIdx.x] < 0.f) tile_rej++;
+        }
+        __syncthreads();
+        for (int j = 0; j < n; j++) {
+            if (base + j + 1 > last) break;
+            in_range++;
+            const float4 r0 = sm.rec0[j];
+            const float4 r1 = sm.rec1[j];
+            const float power = blend_power(__fadd_rn(r0.x, -pxf), __fadd_rn(r0.y, -pyf), r1.x, r1.y, r1.z);
+            if (power > 0.0f) continue;
+            const float alpha = fminf(0.99f, __fmul_rn(r1.w, expf(power)));
+            if (alpha < 1.0f / 255.0f) continue;
+            blended++;
+        }
+    }
+    atomicAdd(&counts[0], in_range);
+    atomicAdd(&counts[1], blended);
+    if (threadIdx.x == 0) atomicAdd(&counts[2], (unsigned long long)total * TILE_PIX);
+    atomicAdd(&counts[3], tile_rej);
+}
+
+void launch_pair_counts(int W, int H, const uint2* ranges, const uint32_t* point_list, const GeomView& g,
+                        const uint32_t* n_contrib, unsigned long long* counts, cudaStream_t s)
+{
+    const int gx = div_up(W, TILE), gy = div_up(H, TILE);
+    cudaMemsetAsync(counts, 0, 4 * sizeof(unsigned long long), s);
+    pair_counts_kernel<<<gx * gy, BLEND_THREADS, 0, s>>>(W, H, gx, ranges, point_list, g, n_contrib, counts);
+}
+
 void launch_render_forward(int W, int H, const uint2* ranges, const uint32_t* point_list, const GeomView& g,
                            const float* bg, float* out_color, float* out_depth, float* out_alpha,
                            uint32_t* n_contrib, cudaStream_t s)

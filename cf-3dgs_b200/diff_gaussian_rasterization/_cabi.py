@@ -29,6 +29,11 @@ SIGNATURES = {
                              _P, _P, _P, _P, _P, c_int]),
     "gsr_mark_visible": (c_int, [c_int, _P, _P, _P, _P, _P]),
     "gsr_debug_dump": (c_int, [c_int, c_int, c_int, c_int64, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "gsr_profile_enable": (c_int, [c_int]),
+    "gsr_profile_count": (c_int, []),
+    "gsr_profile_name": (c_char_p, [c_int]),
+    "gsr_profile_read": (c_int, [_P, c_int]),
+    "gsr_debug_pair_counts": (c_int, [c_int, c_int, c_int, c_int64, _P, _P, _P, _P, _P]),
 }
 
 

@@ -1,0 +1,64 @@
+"""CPU: host-side behaviour of the drop-in module mirrors the reference wrapper
+(submodules/diff-gaussian-rasterization/diff_gaussian_rasterization/__init__.py:160-223)."""
+import pytest
+import torch
+
+import diff_gaussian_rasterization as D
+
+
+def test_public_names():
+    for n in ["GaussianRasterizationSettings", "GaussianRasterizer", "rasterize_gaussians", "_RasterizeGaussians",
+              "cpu_deep_copy_tuple"]:
+        assert hasattr(D, n)
+
+
+def test_settings_fields_match_reference():
+    assert D.GaussianRasterizationSettings._fields == (
+        "image_height", "image_width", "tanfovx", "tanfovy", "bg", "scale_modifier", "viewmatrix", "projmatrix",
+        "sh_degree", "campos", "prefiltered", "debug")
+
+
+def _rast():
+    e = torch.eye(4)
+    rs = D.GaussianRasterizationSettings(16, 16, 1.0, 1.0, torch.zeros(3), 1.0, e, e, 0, torch.zeros(3), False, False)
+    return D.GaussianRasterizer(rs)
+
+
+def test_exactly_one_colour_source():
+    r = _rast()
+    x = torch.zeros(4, 3)
+    with pytest.raises(Exception, match="SHs or precomputed colors"):
+        r(x, x, torch.zeros(4, 1), scales=x, rotations=torch.zeros(4, 4))
+    with pytest.raises(Exception, match="SHs or precomputed colors"):
+        r(x, x, torch.zeros(4, 1), shs=torch.zeros(4, 16, 3), colors_precomp=x, scales=x, rotations=torch.zeros(4, 4))
+
+
+def test_exactly_one_covariance_source():
+    r = _rast()
+    x = torch.zeros(4, 3)
+    with pytest.raises(Exception, match="scale/rotation pair or precomputed 3D covariance"):
+        r(x, x, torch.zeros(4, 1), colors_precomp=x)
+    with pytest.raises(Exception, match="scale/rotation pair or precomputed 3D covariance"):
+        r(x, x, torch.zeros(4, 1), colors_precomp=x, scales=x)
+    with pytest.raises(Exception, match="scale/rotation pair or precomputed 3D covariance"):
+        r(x, x, torch.zeros(4, 1), colors_precomp=x, scales=x, rotations=torch.zeros(4, 4), cov3D_precomp=torch.zeros(4, 6))
+
+
+def test_bad_means_shape_is_a_runtime_error():
+    r = _rast()
+    with pytest.raises(RuntimeError, match="means3D must have dimensions"):
+        r(torch.zeros(4, 2), torch.zeros(4, 2), torch.zeros(4, 1), colors_precomp=torch.zeros(4, 3),
+          scales=torch.zeros(4, 3), rotations=torch.zeros(4, 4))
+
+
+def test_cpu_inputs_are_rejected_not_silently_computed():
+    r = _rast()
+    x = torch.rand(4, 3)
+    with pytest.raises(RuntimeError, match="CUDA tensor"):
+        r(x, x, torch.zeros(4, 1), colors_precomp=x, scales=x, rotations=torch.zeros(4, 4))
+
+
+def test_cpu_deep_copy_tuple():
+    t = (torch.ones(2), 3, "s")
+    c = D.cpu_deep_copy_tuple(t)
+    assert c[1] == 3 and c[2] == "s" and torch.equal(c[0], t[0]) and c[0] is not t[0]

@@ -1,0 +1,57 @@
+"""CPU: the C-ABI library loads and exports every symbol include/gsr.h declares (no compute calls)."""
+import ctypes
+import os
+import re
+
+from helpers import ROOT
+
+
+def _header_decls():
+    src = open(os.path.join(ROOT, "include", "gsr.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return re.findall(r"GSR_API\s+([\w\s\*]+?)\s*(gsr_\w+)\s*\(([^;]*?)\)\s*;", src, flags=re.S)
+
+
+def test_header_declares_entry_points():
+    names = [n for _, n, _ in _header_decls()]
+    for must in ["gsr_forward_prepare", "gsr_forward_render", "gsr_backward", "gsr_mark_visible", "gsr_debug_dump",
+                 "gsr_geometry_bytes", "gsr_image_bytes", "gsr_binning_bytes", "gsr_last_error", "gsr_version"]:
+        assert must in names
+
+
+def test_library_exports_every_declared_symbol():
+    from diff_gaussian_rasterization import _cabi
+    lib = ctypes.CDLL(_cabi.LIB_PATH)
+    for _, name, _ in _header_decls():
+        assert hasattr(lib, name), f"{name} declared in gsr.h but not exported"
+
+
+def test_ctypes_signatures_match_header():
+    from diff_gaussian_rasterization import _cabi
+
+    def ctype_of(a):
+        a = a.strip()
+        if a in ("void", ""):
+            return None
+        if "*" in a:
+            return ctypes.c_void_p
+        t = " ".join(a.split()[:-1])
+        return {"int": ctypes.c_int, "float": ctypes.c_float, "int64_t": ctypes.c_int64, "size_t": ctypes.c_size_t}[t]
+
+    decls = _header_decls()
+    assert {n for _, n, _ in decls} == set(_cabi.SIGNATURES), "binding and header list different entry points"
+    for _, name, args in decls:
+        want = [c for c in (ctype_of(a) for a in args.split(",")) if c is not None]
+        assert want == _cabi.SIGNATURES[name][1], name
+
+
+def test_size_queries_need_no_gpu():
+    from diff_gaussian_rasterization import _cabi
+    lib = _cabi.lib
+    assert lib.gsr_version() >= 1000
+    g1, g2 = lib.gsr_geometry_bytes(1000), lib.gsr_geometry_bytes(2000)
+    assert 0 < g1 < g2
+    assert lib.gsr_image_bytes(640, 360) >= 640 * 360 * 4 + 40 * 23 * 8
+    assert lib.gsr_binning_bytes(1000, 640, 360) >= 16 * 1000
+    assert lib.gsr_profile_count() == 10
+    assert lib.gsr_profile_name(0) == b"preprocess"

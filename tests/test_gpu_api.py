@@ -1,0 +1,120 @@
+"""GPU: API-surface behaviour of the drop-in module (edge cases the reference handles in rasterize_points.cu)."""
+import numpy as np
+import pytest
+import torch
+
+import gsr_synth as S
+from helpers import cuda_forward, cuda_settings
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def test_mark_visible_matches_oracle():
+    import diff_gaussian_rasterization as D
+    from oracle import oracle as O
+    cam = S.second_view(320, 180)
+    sc = S.make_gvol(50000, 320, 180, seed=31)
+    r = D.GaussianRasterizer(cuda_settings(D, cam, (0, 0, 0), 3, DEV))
+    vis = r.markVisible(sc["means3D"].to(DEV))
+    assert vis.dtype == torch.bool and vis.shape == (50000,)
+    assert np.array_equal(vis.cpu().numpy(), O.mark_visible(sc["means3D"].numpy(), cam["viewmatrix"].numpy()))
+
+
+def test_zero_gaussians_returns_zero_images():
+    import diff_gaussian_rasterization as D
+    cam = S.make_camera(64, 48)
+    r = D.GaussianRasterizer(cuda_settings(D, cam, (1, 1, 1), 3, DEV))
+    z = lambda *s: torch.zeros(*s, device=DEV, requires_grad=True)
+    color, radii, depth, alpha = r(z(0, 3), z(0, 3), z(0, 1), shs=z(0, 16, 3), scales=z(0, 3), rotations=z(0, 4))
+    assert color.shape == (3, 48, 64) and float(color.abs().max()) == 0.0      # rasterize_points.cu:68-71,83
+    assert radii.numel() == 0 and float(depth.abs().max()) == 0.0 and float(alpha.abs().max()) == 0.0
+    color.sum().backward()
+
+
+def test_everything_culled_gives_background_and_zero_grads():
+    cam = S.make_camera(100, 60)
+    sc = S.make_gvol(500, 100, 60, seed=32)
+    sc["means3D"][:, 2] = -2.0
+    out, leaves, m2d = cuda_forward(sc, cam, (0.25, 0.5, 0.75))
+    assert out["num_rendered"] == 0 and int(out["radii"].abs().sum()) == 0
+    assert torch.allclose(out["color"], torch.tensor([0.25, 0.5, 0.75], device=DEV)[:, None, None].expand(3, 60, 100))
+    out["color"].sum().backward()
+    assert all(float(v.grad.abs().sum()) == 0.0 for v in leaves.values())
+
+
+def test_single_gaussian_and_debug_mode():
+    cam = S.make_camera(48, 32)
+    sc = S.make_gvol(1, 48, 32, seed=33, s0=0.05)
+    sc["means3D"][0] = torch.tensor([0.0, 0.0, 2.0])
+    out, leaves, _ = cuda_forward(sc, cam, (0, 0, 0), debug=True)
+    assert int(out["radii"][0]) > 0 and out["num_rendered"] == int(out["state"]["tiles_touched"][0])
+    assert float(out["alpha"].max()) > 0.0
+    out["color"].sum().backward()
+    assert float(leaves["means3D"].grad.abs().sum()) > 0.0
+
+
+def test_forward_is_deterministic_bit_for_bit():
+    cam = S.make_camera(320, 180)
+    sc = S.make_gvol(20000, 320, 180, seed=34)
+    a, _, _ = cuda_forward(sc, cam, (0, 0, 0))
+    b, _, _ = cuda_forward(sc, cam, (0, 0, 0))
+    for k in ["color", "depth", "alpha"]:
+        assert torch.equal(a[k], b[k])
+    assert torch.equal(a["state"]["point_list"], b["state"]["point_list"])
+
+
+def test_scale_modifier_and_depth_alpha_cotangents_absent():
+    """scale_modifier scales the splats; with no depth/alpha cotangent the backward takes its colour-only path."""
+    from oracle import oracle as O
+    from helpers import oracle_forward, rel_to_max
+    cam = S.make_camera(160, 96)
+    sc = S.make_gvol(4000, 160, 96, seed=35, s0=0.02)
+    out, leaves, m2d = cuda_forward(sc, cam, (0, 0, 0), scale_modifier=1.7)
+    st = oracle_forward(sc, cam, (0, 0, 0), scale_modifier=1.7)
+    assert np.array_equal(out["radii"].cpu().numpy(), st["radii"])
+    assert np.array_equal(out["state"]["point_list"].cpu().numpy().view(np.uint32), st["point_list"])
+    gc = S.cotangents(160, 96, seed=36, dense=False)["grad_color"]
+    out["color"].backward(gc.to(DEV))
+    st["alpha"] = out["alpha"].detach().cpu().numpy()
+    st["n_contrib"] = out["state"]["n_contrib"].cpu().numpy().view(np.uint32)
+    go = O.backward(st, gc.numpy())
+    for name, key in [("means3D", "means3D"), ("scales", "scales"), ("shs", "sh")]:
+        assert rel_to_max(leaves[name].grad.cpu().numpy(), go[key]) <= 1e-4
+
+
+def test_non_contiguous_inputs_are_accepted_like_the_reference():
+    """rasterize_points.cu:96-115 calls .contiguous() on everything."""
+    import diff_gaussian_rasterization as D
+    cam = S.make_camera(96, 64)
+    sc = S.make_gvol(1000, 96, 64, seed=37, s0=0.03)
+    wide = torch.zeros(1000, 6, device=DEV)
+    wide[:, ::2] = sc["means3D"].to(DEV)
+    means_nc = wide[:, ::2]
+    assert not means_nc.is_contiguous()
+    r = D.GaussianRasterizer(cuda_settings(D, cam, (0, 0, 0), 3, DEV))
+    kw = dict(shs=sc["shs"].to(DEV), scales=sc["scales"].to(DEV), rotations=sc["rotations"].to(DEV))
+    a = r(means_nc, None, sc["opacities"].to(DEV), **kw)[0]
+    b = r(sc["means3D"].to(DEV), None, sc["opacities"].to(DEV), **kw)[0]
+    assert torch.equal(a, b)
+
+
+def test_prefiltered_violation_raises():
+    import diff_gaussian_rasterization as D
+    cam = S.make_camera(96, 64)
+    sc = S.make_gvol(1000, 96, 64, seed=38)       # 2 % of G-vol lies behind the near plane
+    rs = cuda_settings(D, cam, (0, 0, 0), 3, DEV, prefiltered=True)
+    with pytest.raises(RuntimeError, match="filtered although prefiltered"):
+        D.GaussianRasterizer(rs)(sc["means3D"].to(DEV), None, sc["opacities"].to(DEV), shs=sc["shs"].to(DEV),
+                                 scales=sc["scales"].to(DEV), rotations=sc["rotations"].to(DEV))
+
+
+def test_runs_on_a_side_stream():
+    cam = S.make_camera(160, 96)
+    sc = S.make_gvol(4000, 160, 96, seed=39, s0=0.02)
+    ref, _, _ = cuda_forward(sc, cam, (0, 0, 0))
+    s = torch.cuda.Stream()
+    with torch.cuda.stream(s):
+        out, _, _ = cuda_forward(sc, cam, (0, 0, 0))
+    s.synchronize()
+    assert torch.equal(out["color"], ref["color"])
