@@ -26,11 +26,11 @@ def needs_build() -> bool:
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build(force: bool = False, verbose: bool = False, extra=()) -> str:
-    if not force and not needs_build():
+def build(force: bool = False, verbose: bool = False, extra=(), out: str = OUT) -> str:
+    if not force and not needs_build() and out == OUT:
         return OUT
     objs = []
-    obj_dir = os.path.join(HERE, "build")
+    obj_dir = os.path.join(HERE, "build", os.path.basename(out))
     os.makedirs(obj_dir, exist_ok=True)
     procs = []
     for src in _sources():
@@ -43,11 +43,11 @@ def build(force: bool = False, verbose: bool = False, extra=()) -> str:
     for cmd, p in procs:
         if p.wait() != 0:
             raise RuntimeError("nvcc failed: " + " ".join(cmd))
-    link = ["nvcc", "-shared", "-o", OUT] + objs + ["-gencode", "arch=compute_100a,code=sm_100a"]
+    link = ["nvcc", "-shared", "-o", out] + objs + ["-gencode", "arch=compute_100a,code=sm_100a"]
     if verbose:
         print(" ".join(link))
     subprocess.check_call(link)
-    return OUT
+    return out
 
 
 if __name__ == "__main__":

@@ -12,12 +12,14 @@ constexpr int BATCH = 256;          // tile-list entries staged per round
 constexpr int FOOT_W = 8, FOOT_H = 4;
 
 // Per-entry staged record (shared memory).  rec0/rec1 are read by every pixel test, rec2 only when blending.
-struct Staged {
-    float4 rec0[BATCH];  // x, y, -B/C, -B/A
-    float4 rec1[BATCH];  // conic A, B, C, opacity
-    float4 rec2[BATCH];  // r, g, b, depth
-    float thr[BATCH];    // ln(255*opacity): alpha < 1/255 <=> q > thr ;  -1 = rejected for the whole tile
+template <int N>
+struct StagedT {
+    float4 rec0[N];  // x, y, -B/C, -B/A
+    float4 rec1[N];  // conic A, B, C, opacity
+    float4 rec2[N];  // r, g, b, depth
+    float thr[N];    // ln(255*opacity): alpha < 1/255 <=> q > thr ;  -1 = rejected for the whole tile
 };
+using Staged = StagedT<BATCH>;
 
 // Conservative rejection: true only if alpha < 1/255 is guaranteed for EVERY pixel centre inside
 // [x_lo,x_hi] x [y_lo,y_hi].  The reference skips such pairs one by one (forward.cu:347-349), so skipping
@@ -47,7 +49,8 @@ __device__ __forceinline__ bool reject_rect(float X, float Y, float nBoC, float 
 }
 
 // Stage one tile-list entry.  Also applies the rejection test for the whole tile.
-__device__ __forceinline__ void stage_entry(Staged& sm, int slot, uint32_t gid, const GeomView& g, float tile_x0,
+template <int N>
+__device__ __forceinline__ void stage_entry(StagedT<N>& sm, int slot, uint32_t gid, const GeomView& g, float tile_x0,
                                             float tile_y0)
 {
     const float2 xy = g.xy[gid];

@@ -3,10 +3,16 @@
 // recurrence, not an algebraic equivalent, so nearly opaque pixels behave like the reference.
 //
 // The reference issues 10 global float atomics per blended (pixel, Gaussian) pair.  Here the 32 lanes of a
-// warp always look at the same Gaussian, so the 10 partials are summed across the warp with shuffles, the 8
-// warps of the CTA accumulate into a per-batch shared-memory table, and each CTA flushes one 48-byte record
-// per touched Gaussian with three 16-byte vector reductions (red.global.add.v4.f32).  Entries that cannot
-// reach alpha >= 1/255 in the tile / in the warp's 8x4 footprint are rejected exactly as in the forward.
+// warp always look at the same Gaussian, so the partials are summed across the warp first: every lane drops
+// its 9 (10 with a depth cotangent) partials into a warp-private shared-memory slab ([value][lane], rows padded
+// to 36 floats so both the scalar stores and the 128-bit loads are bank-conflict free); once three entries are
+// parked, lane L sums slab row L (eight LDS.128) and adds it into the table -- ~25 issue slots per entry
+// instead of the ~100 a 5-step shuffle butterfly over 10 values costs (ncu: the butterfly was 70 % of this
+// kernel's instructions; same-address shared atomics from the contributing lanes measured slower still).
+// The 8 warps of the CTA accumulate into a
+// per-batch shared-memory table, and each CTA flushes one 48-byte record per touched Gaussian with three
+// 16-byte vector reductions (red.global.add.v4.f32).  Entries that cannot reach alpha >= 1/255 in the tile / in
+// the warp's 8x4 footprint are rejected exactly as in the forward.
 //
 // Gradient record per Gaussian (grad_scratch, 12 floats):
 //   0 mean2D.x  1 mean2D.y  2 conic.x  3 conic.y | 4 conic.w  5 opacity  6 colour.r  7 colour.g |
@@ -16,26 +22,35 @@
 
 namespace gsr {
 
+#ifndef GSR_BWD_MIN_BLOCKS
+#define GSR_BWD_MIN_BLOCKS 4
+#endif
+#ifndef GSR_BWD_BATCH
+#define GSR_BWD_BATCH 128      // tile-list entries staged per round
+#endif
+#ifndef GSR_BWD_GROUP
+#define GSR_BWD_GROUP 3        // entries whose partials share one slab reduction
+#endif
 constexpr int NGRAD = 12;
-
-__device__ __forceinline__ float warp_sum(float v)
-{
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    return v;
-}
+constexpr int BWD_BATCH = GSR_BWD_BATCH;
+constexpr int GROUP = GSR_BWD_GROUP;
+constexpr int RED_STRIDE = 36;  // floats per value row of the warp slab (32 lanes + pad; 144 B keeps LDS.128 aligned)
 
 template <bool HAS_DEPTH, bool HAS_ALPHA>
-__global__ void __launch_bounds__(BLEND_THREADS)
+__global__ void __launch_bounds__(BLEND_THREADS, GSR_BWD_MIN_BLOCKS)
 render_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges,
                        const uint32_t* __restrict__ point_list, GeomView g, const float* __restrict__ bg,
                        const float* __restrict__ out_alpha, const uint32_t* __restrict__ n_contrib,
                        const float* __restrict__ dL_dcolor, const float* __restrict__ dL_ddepth,
                        const float* __restrict__ dL_dalpha, float* __restrict__ grad)
 {
-    __shared__ Staged sm;
-    __shared__ uint32_t sm_gid[BATCH];
-    __shared__ __align__(16) float acc[BATCH][NGRAD];
+    constexpr int NV = HAS_DEPTH ? 10 : 9;   // partials per (pixel, Gaussian) pair
+    constexpr int ROWS = GROUP * NV;         // one slab row per (pending entry, partial); ROWS <= 32
+    static_assert(ROWS <= 32, "one lane sums one slab row");
+    __shared__ StagedT<BWD_BATCH> sm;
+    __shared__ uint32_t sm_gid[BWD_BATCH];
+    __shared__ __align__(16) float acc[BWD_BATCH][NGRAD];
+    __shared__ __align__(16) float red[BLEND_THREADS / 32][ROWS * RED_STRIDE];
 
     const int tile = blockIdx.x;
     const int tile_x = tile % grid_x, tile_y = tile / grid_x;
@@ -65,6 +80,7 @@ render_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ range
         if (HAS_ALPHA) dLa = dL_dalpha[pid];
     }
     const float bg_dot = bg[0] * dLp0 + bg[1] * dLp1 + bg[2] * dLp2;
+    const bool has_bg = (bg[0] != 0.f) || (bg[1] != 0.f) || (bg[2] != 0.f);   // uniform: black background skips a divide
     float ar0 = 0.f, ar1 = 0.f, ar2 = 0.f, adr = 0.f, aar = 0.f;   // accum_rec colour / depth / alpha
     float last_alpha = 0.f, lc0 = 0.f, lc1 = 0.f, lc2 = 0.f, last_depth = 0.f;
     const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
@@ -83,11 +99,34 @@ render_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ range
     const int start = s_start;              // process positions start-1 ... 0
     const int warp_last = __reduce_max_sync(0xffffffffu, last_contributor);
 
-    for (int base = 0; base < start; base += BATCH) {
+    // slab bookkeeping: lane L sums slab row L = (pending entry L / NV, partial L % NV)
+    float* const slab = red[warp];
+    const int my_grp = (int)lane / NV, my_comp = (int)lane - my_grp * NV;
+    const float4* const my_row = reinterpret_cast<const float4*>(slab + lane * RED_STRIDE);
+    int pending = 0, pj0 = 0, pj1 = 0, pj2 = 0;
+
+    // sums the rows of the pending entries and adds them into the per-batch table
+    auto flush_slab = [&]() {
+        __syncwarp();
+        if ((int)lane < pending * NV) {
+            float sacc = 0.f;
+#pragma unroll
+            for (int q = 0; q < 8; q += 2) {
+                const float4 a = my_row[q], b = my_row[q + 1];
+                sacc += ((a.x + a.y) + (a.z + a.w)) + ((b.x + b.y) + (b.z + b.w));
+            }
+            const int jj = my_grp == 0 ? pj0 : (my_grp == 1 ? pj1 : pj2);
+            atomicAdd(&acc[jj][my_comp], sacc);
+        }
+        __syncwarp();
+        pending = 0;
+    };
+
+    for (int base = 0; base < start; base += BWD_BATCH) {
         __syncthreads();   // previous flush finished
-        const int n = min(BATCH, start - base);
+        const int n = min(BWD_BATCH, start - base);
         // slot j of this round holds list position (start - 1 - base - j)
-        for (int k = threadIdx.x; k < BATCH * NGRAD / 4; k += BLEND_THREADS)
+        for (int k = threadIdx.x; k < BWD_BATCH * NGRAD / 4; k += BLEND_THREADS)
             reinterpret_cast<float4*>(&acc[0][0])[k] = make_float4(0.f, 0.f, 0.f, 0.f);
         if ((int)threadIdx.x < n) {
             const uint32_t gid = point_list[range.x + (start - 1 - base - threadIdx.x)];
@@ -125,8 +164,9 @@ render_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ range
                 const bool contrib = (pos < last_contributor) && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
                 if (!__any_sync(0xffffffffu, contrib)) continue;
 
-                float g_mx = 0.f, g_my = 0.f, g_cx = 0.f, g_cy = 0.f, g_cw = 0.f, g_op = 0.f;
-                float g_c0 = 0.f, g_c1 = 0.f, g_c2 = 0.f, g_d = 0.f;
+                float v[10];
+#pragma unroll
+                for (int k = 0; k < 10; k++) v[k] = 0.f;
                 if (contrib) {
                     const float4 r2 = sm.rec2[j];
                     const float one_m = __fadd_rn(1.f, -alpha);
@@ -139,12 +179,12 @@ render_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ range
                     dL_dopa += (r2.y - ar1) * dLp1;
                     ar2 = last_alpha * lc2 + (1.f - last_alpha) * ar2; lc2 = r2.z;
                     dL_dopa += (r2.z - ar2) * dLp2;
-                    g_c0 = aT * dLp0; g_c1 = aT * dLp1; g_c2 = aT * dLp2;
+                    v[6] = aT * dLp0; v[7] = aT * dLp1; v[8] = aT * dLp2;
                     if (HAS_DEPTH) {
                         adr = last_alpha * last_depth + (1.f - last_alpha) * adr;
                         last_depth = r2.w;
                         dL_dopa += (r2.w - adr) * dLd;
-                        g_d = aT * dLd;
+                        v[9] = aT * dLd;
                     }
                     if (HAS_ALPHA) {
                         aar = last_alpha + (1.f - last_alpha) * aar;
@@ -152,37 +192,30 @@ render_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ range
                     }
                     dL_dopa *= T;
                     last_alpha = alpha;
-                    dL_dopa += (-T_final / one_m) * bg_dot;
+                    if (has_bg) dL_dopa += (-T_final / one_m) * bg_dot;
                     const float dL_dG = r1.w * dL_dopa;
                     const float gdx = G * dx, gdy = G * dy;
                     const float dG_ddelx = -gdx * r1.x - gdy * r1.y;
                     const float dG_ddely = -gdy * r1.z - gdx * r1.y;
-                    g_mx = dL_dG * dG_ddelx * ddelx_dx;
-                    g_my = dL_dG * dG_ddely * ddely_dy;
-                    g_cx = -0.5f * gdx * dx * dL_dG;
-                    g_cy = -0.5f * gdx * dy * dL_dG;
-                    g_cw = -0.5f * gdy * dy * dL_dG;
-                    g_op = G * dL_dopa;
+                    v[0] = dL_dG * dG_ddelx * ddelx_dx;
+                    v[1] = dL_dG * dG_ddely * ddely_dy;
+                    v[2] = -0.5f * gdx * dx * dL_dG;
+                    v[3] = -0.5f * gdx * dy * dL_dG;
+                    v[4] = -0.5f * gdy * dy * dL_dG;
+                    v[5] = G * dL_dopa;
                 }
-                g_mx = warp_sum(g_mx); g_my = warp_sum(g_my);
-                g_cx = warp_sum(g_cx); g_cy = warp_sum(g_cy); g_cw = warp_sum(g_cw);
-                g_op = warp_sum(g_op);
-                g_c0 = warp_sum(g_c0); g_c1 = warp_sum(g_c1); g_c2 = warp_sum(g_c2);
-                if (HAS_DEPTH) g_d = warp_sum(g_d);
-                // lanes 0..9 each own one component
-                float mine = g_mx;
-                mine = lane == 1 ? g_my : mine;
-                mine = lane == 2 ? g_cx : mine;
-                mine = lane == 3 ? g_cy : mine;
-                mine = lane == 4 ? g_cw : mine;
-                mine = lane == 5 ? g_op : mine;
-                mine = lane == 6 ? g_c0 : mine;
-                mine = lane == 7 ? g_c1 : mine;
-                mine = lane == 8 ? g_c2 : mine;
-                mine = lane == 9 ? g_d : mine;
-                if (lane < 10) atomicAdd(&acc[j][lane], mine);
+                // park this entry's partials in the slab; reduce once GROUP entries are pending
+                {
+                    float* dst = slab + pending * (NV * RED_STRIDE) + lane;
+#pragma unroll
+                    for (int k = 0; k < NV; k++) dst[k * RED_STRIDE] = v[k];
+                    if (pending == 0) pj0 = j; else if (pending == 1) pj1 = j; else pj2 = j;
+                    pending++;
+                    if (pending == GROUP) flush_slab();
+                }
             }
         }
+        if (pending) flush_slab();
         __syncthreads();
         // flush: one record per entry, three 16-byte vector reductions
         if ((int)threadIdx.x < n) {
