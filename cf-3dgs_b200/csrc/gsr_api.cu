@@ -56,6 +56,11 @@ int tile_bits(int tiles)
 
 }  // namespace
 
+namespace gsr {
+// lets other translation units of the library report through gsr_last_error()
+void set_last_error(const char* msg) { snprintf(g_err, sizeof(g_err), "%s", msg ? msg : ""); }
+}  // namespace gsr
+
 extern "C" {
 
 int gsr_version(void) { return 1000; }

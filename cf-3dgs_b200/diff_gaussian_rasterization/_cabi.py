@@ -27,6 +27,7 @@ SIGNATURES = {
     "gsr_backward": (c_int, [c_int, c_int, c_int, c_int, c_int, c_int64, _P, _P, _P, _P, _P, _P, c_float, _P, _P,
                              _P, _P, c_float, c_float, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P,
                              _P, _P, _P, _P, _P, c_int]),
+    "gsr_pose_gradient_static": (c_int, [c_int, _P, _P, _P, _P]),
     "gsr_mark_visible": (c_int, [c_int, _P, _P, _P, _P, _P]),
     "gsr_debug_dump": (c_int, [c_int, c_int, c_int, c_int64, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "gsr_profile_enable": (c_int, [c_int]),
