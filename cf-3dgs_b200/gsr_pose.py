@@ -1,0 +1,73 @@
+"""Rigid-pose optimisation on top of the rasterizer, without lietorch.
+
+CF-3DGS fits a relative camera pose by rendering `SE3.retr(P).act(xyz)` and letting lietorch's backward turn
+dL/dmeans3D into a 6-vector (scene/gaussian_model_cf.py:123-133, 303-373).  Here the same quantity comes out of the
+rasterizer's backward kernel directly (gsr_backward's dL_dpose): for the left perturbation  p'(xi) = Exp(xi) * T * x
+at xi = 0,
+        dL/dxi = [ sum_i g_i ,  sum_i p'_i x g_i ],      g_i = dL/dmeans3D_i,   xi = (translation, rotation),
+which is lietorch's SE3 tangent ordering.  lietorch is not vendored with the reference and cannot be installed
+offline, so this convention is checked against float64 autograd through a matrix-exponential SE3, not against
+lietorch itself.
+"""
+from __future__ import annotations
+
+import torch
+
+import diff_gaussian_rasterization as D
+
+
+def hat(w: torch.Tensor) -> torch.Tensor:
+    z = torch.zeros((), dtype=w.dtype, device=w.device)
+    return torch.stack([torch.stack([z, -w[2], w[1]]), torch.stack([w[2], z, -w[0]]), torch.stack([-w[1], w[0], z])])
+
+
+def se3_exp(xi: torch.Tensor) -> torch.Tensor:
+    """4x4 matrix exponential of the twist xi = (v, w)."""
+    A = torch.zeros(4, 4, dtype=xi.dtype, device=xi.device)
+    A = A.clone()
+    A[:3, :3] = hat(xi[3:])
+    A[:3, 3] = xi[:3]
+    return torch.linalg.matrix_exp(A)
+
+
+class _PoseRasterize(torch.autograd.Function):
+    """means3D = T[:3,:3] @ xyz + T[:3,3]; gradient w.r.t. the twist `xi` (evaluated at xi = 0) is the fused
+    dL_dpose; gradients w.r.t. the Gaussian parameters flow as in the plain rasterizer."""
+
+    @staticmethod
+    def forward(ctx, xi, xyz, T, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, rs):
+        means3D = (xyz @ T[:3, :3].t() + T[:3, 3]).contiguous()
+        out = D._forward_impl(rs.bg, means3D, colors_precomp, opacities, scales, rotations, rs.scale_modifier,
+                              cov3Ds_precomp, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, rs.image_height,
+                              rs.image_width, sh, rs.sh_degree, rs.campos, rs.prefiltered, rs.debug)
+        R, color, depth, alpha, radii, geom, binning, img = out
+        ctx.rs, ctx.R = rs, R
+        ctx.set_materialize_grads(False)
+        ctx.mark_non_differentiable(radii)
+        ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, geom, binning, img,
+                              alpha, T)
+        return color, radii, depth, alpha
+
+    @staticmethod
+    def backward(ctx, grad_color, grad_radii, grad_depth, grad_alpha):
+        rs = ctx.rs
+        colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, geom, binning, img, alpha, T = ctx.saved_tensors
+        if grad_color is None:
+            grad_color = torch.zeros((3, rs.image_height, rs.image_width), dtype=torch.float32, device=means3D.device)
+        res = D._backward_impl(rs.bg, means3D, radii, colors_precomp, scales, rotations, rs.scale_modifier, cov3Ds_precomp,
+                               rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, grad_color, grad_depth, grad_alpha,
+                               sh, rs.sh_degree, rs.campos, geom, ctx.R, binning, img, alpha, rs.debug, want_pose_grad=True)
+        dmeans2D, dcolors, dopacity, dmeans3D, dcov3D, dsh, dscales, drots, dpose = res
+        dxyz = dmeans3D @ T[:3, :3] if ctx.needs_input_grad[1] else None
+        return dpose, dxyz, None, dsh, dcolors, dopacity, dscales, drots, dcov3D, None
+
+
+def rasterize_with_pose(raster_settings, xi, xyz, T, opacities, shs=None, colors_precomp=None, scales=None,
+                        rotations=None, cov3D_precomp=None):
+    """Render the Gaussians `xyz` moved by the rigid transform T (4x4, float32, CUDA).  `xi` is a 6-vector of zeros
+    with requires_grad=True; after backward xi.grad holds the pose gradient (translation first).  Update the pose with
+    T <- se3_exp(-lr * xi.grad) @ T (or any optimiser on xi followed by re-centring)."""
+    e = torch.Tensor([])
+    return _PoseRasterize.apply(xi, xyz, T, e if shs is None else shs, e if colors_precomp is None else colors_precomp,
+                                opacities, e if scales is None else scales, e if rotations is None else rotations,
+                                e if cov3D_precomp is None else cov3D_precomp, raster_settings)

@@ -1,0 +1,84 @@
+"""GPU: the fused pose gradient (row N1) against autograd through a matrix-exponential SE3."""
+import numpy as np
+import pytest
+import torch
+
+import gsr_synth as S
+from helpers import cuda_settings
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def test_fused_pose_gradient_matches_autograd_through_se3_exp():
+    import diff_gaussian_rasterization as D
+    import gsr_pose as GP
+    W, H, P = 200, 120, 12000
+    cam = S.make_camera(W, H)
+    sc = S.make_gvol(P, W, H, seed=61, s0=0.02)
+    rs = cuda_settings(D, cam, (0.1, 0.1, 0.1), 3, DEV)
+    t = {k: sc[k].to(DEV) for k in ["means3D", "opacities", "shs", "scales", "rotations"]}
+    a = np.deg2rad(3.0)
+    T = torch.tensor([[np.cos(a), 0, np.sin(a), 0.03], [0, 1, 0, -0.02], [-np.sin(a), 0, np.cos(a), 0.05], [0, 0, 0, 1]],
+                     dtype=torch.float32, device=DEV)
+    ct = S.cotangents(W, H, seed=62, dense=True)
+    gc, gd, ga = ct["grad_color"].to(DEV), ct["grad_depth"].to(DEV), ct["grad_alpha"].to(DEV)
+
+    # fused: dL/dxi straight from the backward kernel
+    xi = torch.zeros(6, device=DEV, requires_grad=True)
+    xyz = t["means3D"].clone().requires_grad_(True)
+    color, radii, depth, alpha = GP.rasterize_with_pose(rs, xi, xyz, T, t["opacities"], shs=t["shs"], scales=t["scales"],
+                                                        rotations=t["rotations"])
+    ((color * gc).sum() + (depth * gd).sum() + (alpha * ga).sum()).backward()
+
+    # reference: autograd through p' = Exp(xi) T x with the plain operator
+    xi2 = torch.zeros(6, device=DEV, requires_grad=True)
+    xyz2 = t["means3D"].clone().requires_grad_(True)
+    M = GP.se3_exp(xi2) @ T
+    means = (xyz2 @ M[:3, :3].t() + M[:3, 3]).contiguous()
+    c2, r2, d2, a2 = D.GaussianRasterizer(rs)(means, torch.zeros_like(means), t["opacities"], shs=t["shs"],
+                                              scales=t["scales"], rotations=t["rotations"])
+    ((c2 * gc).sum() + (d2 * gd).sum() + (a2 * ga).sum()).backward()
+
+    assert torch.equal(color, c2) and torch.equal(radii, r2)
+    want, got = xi2.grad.double().cpu().numpy(), xi.grad.double().cpu().numpy()
+    assert np.abs(want).max() > 0
+    assert np.abs(got - want).max() <= 1e-4 * np.abs(want).max(), (got, want)
+    # gradient w.r.t. the untransformed points is R^T g
+    assert float((xyz.grad - xyz2.grad).abs().max()) <= 1e-4 * float(xyz2.grad.abs().max())
+
+
+def test_pose_descent_recovers_a_known_offset():
+    """Pose-only fit (CF-3DGS local pose fit, trainer/cf3dgs_trainer.py:262-285) on a G-pix frame pair."""
+    import diff_gaussian_rasterization as D
+    import gsr_pose as GP
+    W, H = 240, 136
+    cam = S.make_camera(W, H)
+    sc = S.make_gpix(W, H, seed=2, target_P=20000)
+    rs = cuda_settings(D, cam, (0, 0, 0), 0, DEV)
+    t = {k: sc[k].to(DEV) for k in ["means3D", "opacities", "shs", "scales", "rotations"]}
+    t["opacities"] = torch.full_like(t["opacities"], 0.9)
+    a = np.deg2rad(0.8)
+    T_true = torch.tensor([[np.cos(a), 0, np.sin(a), 0.02], [0, 1, 0, 0.01], [-np.sin(a), 0, np.cos(a), -0.015], [0, 0, 0, 1]],
+                          dtype=torch.float32, device=DEV)
+    with torch.no_grad():
+        tgt = GP.rasterize_with_pose(rs, torch.zeros(6, device=DEV), t["means3D"], T_true, t["opacities"], shs=t["shs"],
+                                     scales=t["scales"], rotations=t["rotations"])[0]
+    T = torch.eye(4, device=DEV)
+    m = torch.zeros(6, device=DEV); v = torch.zeros(6, device=DEV)
+    first = None
+    for it in range(150):
+        xi = torch.zeros(6, device=DEV, requires_grad=True)
+        img = GP.rasterize_with_pose(rs, xi, t["means3D"], T, t["opacities"], shs=t["shs"], scales=t["scales"],
+                                     rotations=t["rotations"])[0]
+        loss = (img - tgt).abs().mean()
+        loss.backward()
+        first = float(loss) if first is None else first
+        g = xi.grad
+        m = 0.9 * m + 0.1 * g; v = 0.999 * v + 0.001 * g * g
+        step = -2e-3 * (m / (1 - 0.9 ** (it + 1))) / ((v / (1 - 0.999 ** (it + 1))).sqrt() + 1e-8)
+        T = (GP.se3_exp(step.double()) @ T.double()).float()
+    err_t = float((T[:3, 3] - T_true[:3, 3]).norm())
+    err_R = float((T[:3, :3] - T_true[:3, :3]).norm())
+    assert float(loss) < 0.25 * first, (first, float(loss))
+    assert err_t < 0.01 and err_R < 0.01, (err_t, err_R)
