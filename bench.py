@@ -97,16 +97,19 @@ class ClockSampler:
         return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def dist_setup(n_gpus):
+def dist_setup(n_gpus, init=True):
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not init:      # the reference arm runs on rank 0 alone and never communicates
+        return 1, rank, local
     if world > 1:
         import torch.distributed as dist
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         os.environ.setdefault("MASTER_PORT", "29500")
         backend = "nccl" if torch.cuda.is_available() else "gloo"
-        dist.init_process_group(backend=backend, rank=rank, world_size=world)
+        import datetime
+        dist.init_process_group(backend=backend, rank=rank, world_size=world, timeout=datetime.timedelta(seconds=120))
     return world, rank, local
 
 
@@ -164,7 +167,24 @@ def cpu_oracle_baseline(S, wl, cam, sample_frac=1.0):
             "sample": f"1 full fwd+bwd frame of {wl['name']} (C oracle, OpenMP {cores} threads, {dt:.2f} s)"}
 
 
+_REAL_STDOUT = None
+
+
+def emit(line: dict) -> None:
+    """The ONE JSON line goes to the process's original stdout; everything else (NCCL banners, warnings) was
+    re-routed to stderr at start-up so it cannot pollute it."""
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 def main():
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=30)
@@ -173,7 +193,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
-    world, rank, local = dist_setup(args.gpus)
+    world, rank, local = dist_setup(args.gpus, init=(args.impl == "ours"))
     import gsr_synth as S
     wl = dict(WORKLOAD)
     W, H, P = wl["W"], wl["H"], wl["P"]
@@ -192,7 +212,7 @@ def main():
                     "config": {"workload": wl["name"], "P": P, "W": W, "H": H, "sh_degree": wl["sh_degree"]},
                     "cpu_baseline": cb, "gpu_launches": 0,
                     "e2e": {"value": cb["value"], "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-            print(json.dumps(line))
+            emit(line)
             return 0
 
     if not have_gpu:
@@ -241,12 +261,12 @@ def main():
                                    leaves["rotations"], v, pj, cp)
             return c, None, d, a
 
-    def step():
+    def step(comm=True):
         leaves = {k: v.detach().requires_grad_(True) for k, v in params.items()}
         m2d = torch.zeros_like(leaves["means3D"], requires_grad=True) if args.impl == "ours" else None
         out = render(leaves, m2d)
         out[0].backward(gc)
-        if world > 1:
+        if world > 1 and comm:
             import torch.distributed as dist
             off = 0
             for k in PARAM_KEYS:
@@ -312,7 +332,7 @@ def main():
         line["cpu_baseline"] = {"value": value, "unit": "frames/s", "cores": 0, "kind": "reference",
                                 "sample": "the reference's own CUDA rasterizer (oracle/_ref, unmodified sources, sm_100a) "
                                           "on this GPU: it has no CPU implementation"}
-        print(json.dumps(line))
+        emit(line)
         return 0
 
     # ---- per-stage timing, work counters, roofline of the dominant kernel ----
@@ -324,7 +344,7 @@ def main():
     reps = 5
     lib.gsr_profile_enable(1)
     for _ in range(reps):
-        step()
+        step(comm=False)   # rank 0 only from here on: no collective
         buf = (ctypes.c_float * n_st)()
         lib.gsr_profile_read(buf, n_st)
         acc += np.maximum(np.array(buf[:]), 0.0)
@@ -384,7 +404,7 @@ def main():
             line["cpu_baseline"] = cpu_oracle_baseline(S, wl, S.make_camera(W, H))
         except Exception as ex:  # the CPU checker must never take the GPU number down with it
             line["cpu_baseline"] = {"error": str(ex)}
-    print(json.dumps(line))
+    emit(line)
     return 0
 
 
