@@ -9,13 +9,25 @@
 
 namespace gsr {
 
-constexpr int PRE_THREADS = 256;
+constexpr int PRE_THREADS = 128;
+// SH rows are staged through shared memory when M == 16 and the active degree needs more than the DC term: the block's
+// rows are one contiguous 24 KB span, moved with coalesced 128-bit loads; rows padded to 13 float4 keep the per-thread
+// LDS.128 conflict free (same layout as the backward kernel).
+constexpr int PRE_ROW4 = 13;
 
+template <bool SLAB>
 __global__ void __launch_bounds__(PRE_THREADS)
 preprocess_kernel(PreprocessArgs a, GeomView g)
 {
     __shared__ float sV[16], sP[16], sCam[3];
     __shared__ uint32_t warp_sums[PRE_THREADS / 32];
+    __shared__ float4 slab[SLAB ? PRE_THREADS * PRE_ROW4 : 1];
+    if (SLAB) {
+        const int first = blockIdx.x * PRE_THREADS;
+        const int rows = min(PRE_THREADS, a.P - first);
+        const float4* src = reinterpret_cast<const float4*>(a.shs + (size_t)first * 48);
+        for (int q = threadIdx.x; q < rows * 12; q += PRE_THREADS) slab[(q / 12) * PRE_ROW4 + (q % 12)] = src[q];
+    }
     if (threadIdx.x < 16) {
         sV[threadIdx.x] = a.viewmatrix[threadIdx.x];
         sP[threadIdx.x] = a.projmatrix[threadIdx.x];
@@ -84,14 +96,31 @@ preprocess_kernel(PreprocessArgs a, GeomView g)
                         float basis[16];
                         sh_basis(a.D, dx, dy, dz, basis);
                         const int ncoef = (a.D + 1) * (a.D + 1);
-                        const float* sh = a.shs + (size_t)idx * a.M * 3;
                         float r = 0.f, gg = 0.f, b = 0.f;
+                        if (SLAB) {
 #pragma unroll
-                        for (int k = 0; k < 16; k++) {
-                            if (k < ncoef) {
-                                r += basis[k] * sh[3 * k];
-                                gg += basis[k] * sh[3 * k + 1];
-                                b += basis[k] * sh[3 * k + 2];
+                            for (int k = 0; k < 16; k++)
+                                if (k >= ncoef) basis[k] = 0.f;
+                            float acc3[3] = {0.f, 0.f, 0.f};
+                            const float4* row = slab + threadIdx.x * PRE_ROW4;
+#pragma unroll
+                            for (int c = 0; c < 12; c++) {
+                                const float4 v = row[c];
+                                acc3[(4 * c) % 3] += basis[(4 * c) / 3] * v.x;
+                                acc3[(4 * c + 1) % 3] += basis[(4 * c + 1) / 3] * v.y;
+                                acc3[(4 * c + 2) % 3] += basis[(4 * c + 2) / 3] * v.z;
+                                acc3[(4 * c + 3) % 3] += basis[(4 * c + 3) / 3] * v.w;
+                            }
+                            r = acc3[0]; gg = acc3[1]; b = acc3[2];
+                        } else {
+                            const float* sh = a.shs + (size_t)idx * a.M * 3;
+#pragma unroll
+                            for (int k = 0; k < 16; k++) {
+                                if (k < ncoef) {
+                                    r += basis[k] * sh[3 * k];
+                                    gg += basis[k] * sh[3 * k + 1];
+                                    b += basis[k] * sh[3 * k + 2];
+                                }
                             }
                         }
                         r += 0.5f; gg += 0.5f; b += 0.5f;
@@ -133,7 +162,9 @@ preprocess_kernel(PreprocessArgs a, GeomView g)
 void launch_preprocess(const PreprocessArgs& a, const GeomView& g, cudaStream_t s)
 {
     cudaMemsetAsync(g.counters, 0, 4 * sizeof(unsigned long long), s);
-    preprocess_kernel<<<div_up(a.P, PRE_THREADS), PRE_THREADS, 0, s>>>(a, g);
+    const bool slab = a.shs && !a.colors_precomp && a.M == 16 && a.D >= 1 && (((uintptr_t)a.shs) & 15) == 0;
+    if (slab) preprocess_kernel<true><<<div_up(a.P, PRE_THREADS), PRE_THREADS, 0, s>>>(a, g);
+    else preprocess_kernel<false><<<div_up(a.P, PRE_THREADS), PRE_THREADS, 0, s>>>(a, g);
 }
 
 __global__ void mark_visible_kernel(int P, const float* __restrict__ means, const float* __restrict__ view,

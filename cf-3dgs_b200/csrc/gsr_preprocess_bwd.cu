@@ -12,7 +12,12 @@
 
 namespace gsr {
 
-constexpr int PB_THREADS = 256;
+constexpr int PB_THREADS = 128;
+// SH rows of a block are staged through shared memory when M == 16 (48 floats = 12 float4 per Gaussian): the block's
+// slab is one contiguous 24 KB span in global memory, so it is moved with coalesced 128-bit loads/stores instead of
+// 192-byte-strided per-thread accesses.  Rows are padded to 13 float4 (208 B): a quarter warp's LDS.128/STS.128 then
+// hit 8 distinct 16-byte bank groups.
+constexpr int SLAB_ROW4 = 13;
 
 int pose_blocks(int P) { return div_up(P, PB_THREADS); }
 
@@ -29,11 +34,20 @@ __device__ __forceinline__ float block_sum_256(float v, float* red)
     return t;
 }
 
+template <bool SLAB>
 __global__ void __launch_bounds__(PB_THREADS)
 preprocess_backward_kernel(PreprocessBwdArgs a, GeomView g)
 {
     __shared__ float sV[16], sP[16], sCam[3];
     __shared__ float red[PB_THREADS / 32];
+    __shared__ float4 slab[SLAB ? PB_THREADS * SLAB_ROW4 : 1];
+    if (SLAB) {
+        // coalesced copy-in of this block's SH rows
+        const int first = blockIdx.x * PB_THREADS;
+        const int rows = min(PB_THREADS, a.P - first);
+        const float4* src = reinterpret_cast<const float4*>(a.shs + (size_t)first * 48);
+        for (int q = threadIdx.x; q < rows * 12; q += PB_THREADS) slab[(q / 12) * SLAB_ROW4 + (q % 12)] = src[q];
+    }
     if (threadIdx.x < 16) {
         sV[threadIdx.x] = a.viewmatrix[threadIdx.x];
         sP[threadIdx.x] = a.projmatrix[threadIdx.x];
@@ -44,6 +58,12 @@ preprocess_backward_kernel(PreprocessBwdArgs a, GeomView g)
     const int idx = blockIdx.x * PB_THREADS + threadIdx.x;
     float gmx = 0.f, gmy = 0.f, gmz = 0.f;   // dL/dmeans3D
     float px = 0.f, py = 0.f, pz = 0.f;
+    float sh_out[16];                         // SLAB: basis (0 above the active degree / for culled Gaussians)
+    float sh_dR = 0.f, sh_dG = 0.f, sh_dB = 0.f;
+    if (SLAB) {
+#pragma unroll
+        for (int k = 0; k < 16; k++) sh_out[k] = 0.f;
+    }
     if (idx < a.P) {
         const bool vis = a.radii[idx] > 0;
         float dmean2x = 0.f, dmean2y = 0.f, dopac = 0.f, dcol0 = 0.f, dcol1 = 0.f, dcol2 = 0.f;
@@ -141,16 +161,42 @@ preprocess_backward_kernel(PreprocessBwdArgs a, GeomView g)
                 const float x = ox / len, y = oy / len, z = oz / len;
                 float basis[16];
                 sh_basis(a.D, x, y, z, basis);
+                // shd[k] = <sh[k], dL/dRGB>: what the direction gradient needs from the coefficients
+                float shd[16];
+                if (SLAB) {
+                    const float dch[3] = {dR, dG, dB};
 #pragma unroll
-                for (int k = 0; k < 16; k++) {
-                    if (k < ncoef) {
-                        dsh[3 * k] = basis[k] * dR;
-                        dsh[3 * k + 1] = basis[k] * dG;
-                        dsh[3 * k + 2] = basis[k] * dB;
+                    for (int k = 0; k < 16; k++) shd[k] = 0.f;
+                    const float4* row = slab + threadIdx.x * SLAB_ROW4;
+#pragma unroll
+                    for (int c = 0; c < 12; c++) {
+                        const float4 v = row[c];
+                        shd[(4 * c) / 3] += v.x * dch[(4 * c) % 3];
+                        shd[(4 * c + 1) / 3] += v.y * dch[(4 * c + 1) % 3];
+                        shd[(4 * c + 2) / 3] += v.z * dch[(4 * c + 2) % 3];
+                        shd[(4 * c + 3) / 3] += v.w * dch[(4 * c + 3) % 3];
+                    }
+                } else {
+#pragma unroll
+                    for (int k = 0; k < 16; k++)
+                        shd[k] = (k < ncoef) ? (sh[3 * k] * dR + sh[3 * k + 1] * dG + sh[3 * k + 2] * dB) : 0.f;
+#pragma unroll
+                    for (int k = 0; k < 16; k++) {
+                        if (k < ncoef) {
+                            dsh[3 * k] = basis[k] * dR;
+                            dsh[3 * k + 1] = basis[k] * dG;
+                            dsh[3 * k + 2] = basis[k] * dB;
+                        }
                     }
                 }
-                // d colour / d direction, summed over channels with the channel gradient
-#define SHD(k) (sh[3 * (k)] * dR + sh[3 * (k) + 1] * dG + sh[3 * (k) + 2] * dB)
+                if (SLAB) {
+                    // every thread of the block has passed the copy-in barrier below before reading; writes to the slab
+                    // happen after a second barrier (see the end of the kernel), so keep dRGB and basis for later
+#pragma unroll
+                    for (int k = 0; k < 16; k++) sh_out[k] = (k < ncoef) ? basis[k] : 0.f;
+                    sh_dR = dR; sh_dG = dG; sh_dB = dB;
+                }
+#define SHD(k) shd[k]
                 float ddx = 0.f, ddy = 0.f, ddz = 0.f;
                 if (a.D > 0) {
                     const float s1 = SHD(1), s2 = SHD(2), s3 = SHD(3);
@@ -214,7 +260,7 @@ preprocess_backward_kernel(PreprocessBwdArgs a, GeomView g)
             }
         }
         // ---- write every output exactly once ----
-        if (dsh) {
+        if (dsh && !SLAB) {
             const int first_zero = vis ? ncoef : 0;
             for (int k = first_zero * 3; k < a.M * 3; k++) dsh[k] = 0.f;
         }
@@ -240,6 +286,20 @@ preprocess_backward_kernel(PreprocessBwdArgs a, GeomView g)
             a.dL_dscales[3 * idx + 2] = dscale[2];
         }
         if (a.dL_drotations) reinterpret_cast<float4*>(a.dL_drotations)[idx] = drot;
+    }
+    if (SLAB) {
+        __syncthreads();   // everyone has finished reading the coefficients
+        const float dch[3] = {sh_dR, sh_dG, sh_dB};
+        float4* row = slab + threadIdx.x * SLAB_ROW4;
+#pragma unroll
+        for (int c = 0; c < 12; c++)
+            row[c] = make_float4(sh_out[(4 * c) / 3] * dch[(4 * c) % 3], sh_out[(4 * c + 1) / 3] * dch[(4 * c + 1) % 3],
+                                 sh_out[(4 * c + 2) / 3] * dch[(4 * c + 2) % 3], sh_out[(4 * c + 3) / 3] * dch[(4 * c + 3) % 3]);
+        __syncthreads();
+        const int first = blockIdx.x * PB_THREADS;
+        const int rows = min(PB_THREADS, a.P - first);
+        float4* dst = reinterpret_cast<float4*>(a.dL_dsh + (size_t)first * 48);
+        for (int q = threadIdx.x; q < rows * 12; q += PB_THREADS) dst[q] = slab[(q / 12) * SLAB_ROW4 + (q % 12)];
     }
     if (a.dL_dpose) {
         // rigid pose gradient at xi = 0 for p' = Exp(xi) p:  d/dnu = g,  d/domega = p x g
@@ -277,7 +337,10 @@ __global__ void __launch_bounds__(256) pose_reduce_kernel(const float* __restric
 void launch_preprocess_backward(const PreprocessBwdArgs& a, const GeomView& g, cudaStream_t s)
 {
     const int nblk = div_up(a.P, PB_THREADS);
-    preprocess_backward_kernel<<<nblk, PB_THREADS, 0, s>>>(a, g);
+    // slab path: (P,16,3) coefficients with 16-byte aligned base pointers
+    const bool slab = a.shs && a.dL_dsh && a.M == 16 && (((uintptr_t)a.shs | (uintptr_t)a.dL_dsh) & 15) == 0;
+    if (slab) preprocess_backward_kernel<true><<<nblk, PB_THREADS, 0, s>>>(a, g);
+    else preprocess_backward_kernel<false><<<nblk, PB_THREADS, 0, s>>>(a, g);
     if (a.dL_dpose) pose_reduce_kernel<<<1, 256, 0, s>>>(a.pose_scratch, nblk, a.dL_dpose);
 }
 
