@@ -170,7 +170,14 @@ render_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ range
                 if (contrib) {
                     const float4 r2 = sm.rec2[j];
                     const float one_m = __fadd_rn(1.f, -alpha);
-                    T = __fdiv_rn(T, one_m);
+                    // T / (1 - alpha): reciprocal seed + one residual correction (<= 1 ulp from the IEEE quotient for
+                    // these operand ranges; saves the slow-path checks of the full divide)
+                    {
+                        float rcp;
+                        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rcp) : "f"(one_m));
+                        const float q = T * rcp;
+                        T = __fmaf_rn(__fmaf_rn(-one_m, q, T), rcp, q);
+                    }
                     const float aT = alpha * T;
                     float dL_dopa = 0.f;
                     ar0 = last_alpha * lc0 + (1.f - last_alpha) * ar0; lc0 = r2.x;

@@ -15,7 +15,10 @@
 
 namespace gsr {
 
-__global__ void __launch_bounds__(BLEND_THREADS)
+#ifndef GSR_FWD_MIN_BLOCKS
+#define GSR_FWD_MIN_BLOCKS 6
+#endif
+__global__ void __launch_bounds__(BLEND_THREADS, GSR_FWD_MIN_BLOCKS)
 render_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges,
                       const uint32_t* __restrict__ point_list, GeomView g, const float* __restrict__ bg,
                       float* __restrict__ out_color, float* __restrict__ out_depth, float* __restrict__ out_alpha,
@@ -140,6 +143,40 @@ pair_counts_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges, c
     atomicAdd(&counts[1], blended);
     if (threadIdx.x == 0) atomicAdd(&counts[2], (unsigned long long)total * TILE_PIX);
     atomicAdd(&counts[3], tile_rej);
+#ifdef GSR_FOOTPRINT_STATS
+    // experiment: warp iterations with one entry stream per warp (8x4) vs one per half-warp (two 4x4) vs per quarter (4x2)
+    {
+        const int wfx = tile_x * TILE + (warp & 1) * FOOT_W, wfy = tile_y * TILE + (warp >> 1) * FOOT_H;
+        unsigned long long u = 0, h = 0, qd = 0;
+        const int wl = __reduce_max_sync(0xffffffffu, last);
+        for (int base = 0; base < total; base += BATCH) {
+            __syncthreads();
+            const int n = min(BATCH, total - base);
+            if ((int)threadIdx.x < n)
+                stage_entry(sm, threadIdx.x, point_list[range.x + base + threadIdx.x], g, (float)(tile_x * TILE), (float)(tile_y * TILE));
+            __syncthreads();
+            for (int c0 = 0; c0 < n; c0 += 32) {
+                const int e = c0 + lane;
+                bool k8 = false, ka = false, kb = false, q0 = false, q1 = false, q2 = false, q3 = false;
+                if (e < n && base + e < wl && !(sm.thr[e] < 0.f)) {
+                    const float4 r0 = sm.rec0[e]; const float4 r1 = sm.rec1[e]; const float thr = sm.thr[e];
+                    auto rj = [&](float x0, float x1, float y0, float y1) {
+                        return !reject_rect(r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, thr, x0, x1, y0, y1); };
+                    k8 = rj(wfx, wfx + 7, wfy, wfy + 3);
+                    ka = rj(wfx, wfx + 3, wfy, wfy + 3); kb = rj(wfx + 4, wfx + 7, wfy, wfy + 3);
+                    q0 = rj(wfx, wfx + 3, wfy, wfy + 1); q1 = rj(wfx + 4, wfx + 7, wfy, wfy + 1);
+                    q2 = rj(wfx, wfx + 3, wfy + 2, wfy + 3); q3 = rj(wfx + 4, wfx + 7, wfy + 2, wfy + 3);
+                }
+                const int pu = __popc(__ballot_sync(0xffffffffu, k8));
+                const int pa = __popc(__ballot_sync(0xffffffffu, ka)), pb = __popc(__ballot_sync(0xffffffffu, kb));
+                const int p0 = __popc(__ballot_sync(0xffffffffu, q0)), p1 = __popc(__ballot_sync(0xffffffffu, q1));
+                const int p2 = __popc(__ballot_sync(0xffffffffu, q2)), p3 = __popc(__ballot_sync(0xffffffffu, q3));
+                u += pu; h += max(pa, pb); qd += max(max(p0, p1), max(p2, p3));
+            }
+        }
+        if (lane == 0) { atomicAdd(&counts[4], u); atomicAdd(&counts[5], h); atomicAdd(&counts[6], qd); }
+    }
+#endif
 }
 
 void launch_pair_counts(int W, int H, const uint2* ranges, const uint32_t* point_list, const GeomView& g,
@@ -147,6 +184,9 @@ void launch_pair_counts(int W, int H, const uint2* ranges, const uint32_t* point
 {
     const int gx = div_up(W, TILE), gy = div_up(H, TILE);
     cudaMemsetAsync(counts, 0, 4 * sizeof(unsigned long long), s);
+#ifdef GSR_FOOTPRINT_STATS
+    cudaMemsetAsync(counts, 0, 8 * sizeof(unsigned long long), s);
+#endif
     pair_counts_kernel<<<gx * gy, BLEND_THREADS, 0, s>>>(W, H, gx, ranges, point_list, g, n_contrib, counts);
 }
 

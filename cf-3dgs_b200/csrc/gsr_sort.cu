@@ -34,8 +34,14 @@ radix_hist_kernel(const uint32_t* __restrict__ keys, int64_t n, int shift, uint3
         const int64_t idx = base + (int64_t)i * SORT_THREADS + threadIdx.x;
         const bool act = idx < n;
         const uint32_t d = act ? ((keys[idx] >> shift) & mask) : (uint32_t)RADIX;
-        const unsigned m = __match_any_sync(0xffffffffu, d);
-        if (act && lane == (unsigned)(__ffs(m) - 1)) atomicAdd(&sh[d], (uint32_t)__popc(m));
+        // high digits (tile rows, float exponents) are often identical across a warp: count those with one atomic,
+        // everything else with plain shared atomics (few same-address collisions for mixed digits)
+        const uint32_t d0 = __shfl_sync(0xffffffffu, d, 0);
+        if (__all_sync(0xffffffffu, d == d0)) {
+            if (lane == 0 && d0 < (uint32_t)RADIX) atomicAdd(&sh[d0], 32u);
+        } else if (act) {
+            atomicAdd(&sh[d], 1u);
+        }
     }
     __syncthreads();
     hist[(size_t)threadIdx.x * nblk + blockIdx.x] = sh[threadIdx.x];
@@ -62,7 +68,8 @@ radix_rowscan_kernel(uint32_t* __restrict__ hist, int nblk, uint32_t* __restrict
     if (threadIdx.x == 0) digit_total[blockIdx.x] = total;
 }
 
-// pass kernel 3: stable scatter.
+// pass kernel 3: stable scatter.  Items are first placed at their block-local sorted position in shared memory, then
+// written out in that order, so a warp's stores fall into a few contiguous runs (one per digit) instead of 32 sectors.
 __global__ void __launch_bounds__(SORT_THREADS)
 radix_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                      uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int64_t n, int shift,
@@ -70,25 +77,32 @@ radix_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __res
                      const uint32_t* __restrict__ digit_total)
 {
     __shared__ uint32_t wcount[SORT_THREADS / 32][RADIX + 1];
-    __shared__ uint32_t gbase[RADIX];
+    __shared__ uint32_t goff[RADIX];   // global base of digit d for this block minus its block-local start
     __shared__ uint32_t warp_sums[8];
+    __shared__ uint32_t skey[SORT_CHUNK], sval[SORT_CHUNK];
     const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (int i = threadIdx.x; i < (SORT_THREADS / 32) * (RADIX + 1); i += SORT_THREADS) (&wcount[0][0])[i] = 0;
     // global base of each digit for this block = exclusive scan of digit totals + row prefix
+    uint32_t my_gbase;
     {
         const uint32_t tot = digit_total[threadIdx.x];
         const uint32_t ex = block_exclusive_scan_256(tot, warp_sums, nullptr);  // contains __syncthreads
-        gbase[threadIdx.x] = ex + hist[(size_t)threadIdx.x * nblk + blockIdx.x];
+        my_gbase = ex + hist[(size_t)threadIdx.x * nblk + blockIdx.x];
     }
-    __syncthreads();
     // each warp owns a contiguous run of SORT_ITEMS*32 items; order inside it is (step, lane)
-    const int64_t wbase = (int64_t)blockIdx.x * SORT_CHUNK + (int64_t)warp * (SORT_ITEMS * 32);
-    uint32_t key[SORT_ITEMS], rank[SORT_ITEMS];
+    const int64_t block_base = (int64_t)blockIdx.x * SORT_CHUNK;
+    const int64_t wbase = block_base + (int64_t)warp * (SORT_ITEMS * 32);
+    uint32_t key[SORT_ITEMS], val[SORT_ITEMS], rank[SORT_ITEMS];
 #pragma unroll
     for (int i = 0; i < SORT_ITEMS; i++) {
         const int64_t idx = wbase + i * 32 + lane;
         const bool act = idx < n;
         key[i] = act ? keys_in[idx] : 0u;
+        val[i] = act ? vals_in[idx] : 0u;
+    }
+#pragma unroll
+    for (int i = 0; i < SORT_ITEMS; i++) {
+        const bool act = (wbase + i * 32 + lane) < n;
         const uint32_t d = act ? ((key[i] >> shift) & mask) : (uint32_t)RADIX;
         const unsigned m = __match_any_sync(0xffffffffu, d);
         const int leader = __ffs(m) - 1;
@@ -102,9 +116,13 @@ radix_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __res
         __syncwarp();
     }
     __syncthreads();
-    // exclusive scan of the warp counters across warps, per digit
+    // per digit: total over the block, its block-local start (scan over digits), then warp bases
     {
-        uint32_t run = 0;
+        uint32_t total = 0;
+#pragma unroll
+        for (int w = 0; w < SORT_THREADS / 32; w++) total += wcount[w][threadIdx.x];
+        uint32_t run = block_exclusive_scan_256(total, warp_sums, nullptr);
+        goff[threadIdx.x] = my_gbase - run;
 #pragma unroll
         for (int w = 0; w < SORT_THREADS / 32; w++) {
             const uint32_t c = wcount[w][threadIdx.x];
@@ -115,12 +133,23 @@ radix_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __res
     __syncthreads();
 #pragma unroll
     for (int i = 0; i < SORT_ITEMS; i++) {
-        const int64_t idx = wbase + i * 32 + lane;
-        if (idx < n) {
+        if ((wbase + i * 32 + lane) < n) {
             const uint32_t d = (key[i] >> shift) & mask;
-            const uint32_t pos = gbase[d] + wcount[warp][d] + rank[i];
-            keys_out[pos] = key[i];
-            vals_out[pos] = vals_in[idx];
+            const uint32_t lp = wcount[warp][d] + rank[i];
+            skey[lp] = key[i];
+            sval[lp] = val[i];
+        }
+    }
+    __syncthreads();
+    const int count = (int)min((int64_t)SORT_CHUNK, n - block_base);
+#pragma unroll
+    for (int i = 0; i < SORT_ITEMS; i++) {
+        const int t = i * SORT_THREADS + threadIdx.x;
+        if (t < count) {
+            const uint32_t k = skey[t];
+            const uint32_t pos = goff[(k >> shift) & mask] + (uint32_t)t;
+            keys_out[pos] = k;
+            vals_out[pos] = sval[t];
         }
     }
 }
