@@ -12,10 +12,15 @@ constexpr uint32_t CULLED_KEY = 0xFFFFFFFFu;  // depth key of an invisible Gauss
 
 // ---- radix sort geometry -------------------------------------------------------------------
 constexpr int SORT_THREADS = 256;
-constexpr int SORT_ITEMS = 8;                       // items per thread
+#ifndef GSR_SORT_ITEMS
+#define GSR_SORT_ITEMS 8
+#endif
+constexpr int SORT_ITEMS = GSR_SORT_ITEMS;              // items per thread
 constexpr int SORT_CHUNK = SORT_THREADS * SORT_ITEMS;  // items per block
 constexpr int RADIX_BITS = 8;
 constexpr int RADIX = 1 << RADIX_BITS;
+constexpr int SORT_MAX_PASSES = 4;
+constexpr int SORT_AUX_WORDS = RADIX * SORT_MAX_PASSES + 64;  // per-pass global digit histograms + block tickets
 
 inline int div_up(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
@@ -34,7 +39,7 @@ struct GeomView {
     uint32_t* sort_vals[2];  // [P] ping-pong Gaussian ids; sort_vals[0] ends up holding the depth order
     uint32_t* offsets;     // [P] exclusive scan of tiles[] in depth order
     uint32_t* hist;        // [RADIX * nblk(P)] per-block digit counts
-    uint32_t* digit_total; // [RADIX]
+    uint32_t* digit_total; // [SORT_AUX_WORDS] per-pass global digit histograms, block tickets
     uint32_t* block_sums;  // [nblk(P)+1]
     unsigned long long* counters;  // [4] 0: total instances (bit 62: prefilter violation)
 };
@@ -48,7 +53,7 @@ struct BinView {
     uint32_t* keys[2];  // [R] tile ids (ping-pong)
     uint32_t* vals[2];  // [R] Gaussian ids (ping-pong); vals[0] ends up as the sorted point list
     uint32_t* hist;     // [RADIX * nblk(R)]
-    uint32_t* digit_total;  // [RADIX]
+    uint32_t* digit_total;  // [SORT_AUX_WORDS]
 };
 
 template <typename T>
@@ -77,7 +82,7 @@ inline size_t geom_layout(char* base, int P, GeomView& g)
     carve(p, g.sort_vals[1], n);
     carve(p, g.offsets, n);
     carve(p, g.hist, (size_t)RADIX * nblk);
-    carve(p, g.digit_total, RADIX);
+    carve(p, g.digit_total, SORT_AUX_WORDS);
     carve(p, g.block_sums, nblk + 1);
     carve(p, g.counters, 4);
     return (size_t)(p - base) + 256;
@@ -102,7 +107,7 @@ inline size_t bin_layout(char* base, int64_t R, BinView& b)
     carve(p, b.vals[0], n);
     carve(p, b.vals[1], n);
     carve(p, b.hist, (size_t)RADIX * nblk);
-    carve(p, b.digit_total, RADIX);
+    carve(p, b.digit_total, SORT_AUX_WORDS);
     return (size_t)(p - base) + 256;
 }
 
