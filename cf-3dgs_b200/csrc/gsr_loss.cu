@@ -1,0 +1,237 @@
+// Fused photometric loss of the CF-3DGS training step:
+//     loss = (1 - lambda) * mean|x - gt|  +  lambda * (1 - mean(SSIM_11x11(x, gt)))
+// Semantics: reference trainer/losses.py:98-136 with utils/loss_utils.py:14-62 (l1_loss, gaussian window sigma 1.5,
+// conv2d zero padding 5, C1 = 0.01^2, C2 = 0.03^2) and the image.clamp(0,1) CF-3DGS applies just before
+// (scene/gaussian_model_cf.py:885).  In PyTorch this is 5 grouped convolutions + ~20 element-wise kernels forward and
+// their backward; here it is one forward and one backward kernel, both separable convolutions in shared memory.
+//
+// forward : per pixel  mu1, mu2, E[x^2], E[y^2], E[xy]  ->  SSIM value and the three maps the backward needs
+//             A = dS/dmu1 (total, through sigma1^2 and sigma12 as well),  B = dS/dsigma1^2,  C = dS/dsigma12
+//           block sums of |x - gt| and SSIM -> two double accumulators
+// backward: dL/dx(p) = gL * [ (1-lambda)/N * sign(x-gt)  -  lambda/N * ( G*A + 2 x G*B + gt G*C )(p) ] * clamp mask
+#include <cmath>
+
+#include "../../include/gsr.h"
+#include "gsr_kernels.h"
+
+namespace gsr {
+void set_last_error(const char* msg);
+
+namespace {
+
+constexpr int LT = 16;            // output tile
+constexpr int HALO = 5;
+constexpr int LW = LT + 2 * HALO; // 26
+__constant__ float c_gw[11];
+bool g_gw_ready[64] = {false};
+
+__device__ __forceinline__ float clamp01(float v, bool on) { return on ? fminf(fmaxf(v, 0.f), 1.f) : v; }
+
+__global__ void __launch_bounds__(LT * LT)
+photo_loss_forward_kernel(int H, int W, const float* __restrict__ img, const float* __restrict__ gt, int clamp_img,
+                          float* __restrict__ maps, double* __restrict__ sums)
+{
+    __shared__ float sx[LW][LW + 1], sy[LW][LW + 1];
+    __shared__ float hq[5][LW][LT];
+    __shared__ float red[2][LT * LT / 32];
+    const int ch = blockIdx.z;
+    const size_t plane = (size_t)H * W;
+    const float* x = img + ch * plane;
+    const float* y = gt + ch * plane;
+    const int x0 = blockIdx.x * LT - HALO, y0 = blockIdx.y * LT - HALO;
+    for (int i = threadIdx.x; i < LW * LW; i += LT * LT) {
+        const int r = i / LW, c = i % LW;
+        const int gy = y0 + r, gx = x0 + c;
+        float vx = 0.f, vy = 0.f;
+        if (gy >= 0 && gy < H && gx >= 0 && gx < W) {
+            vx = clamp01(x[(size_t)gy * W + gx], clamp_img);
+            vy = y[(size_t)gy * W + gx];
+        }
+        sx[r][c] = vx; sy[r][c] = vy;
+    }
+    __syncthreads();
+    // horizontal pass: 26 rows x 16 columns, 5 quantities
+    for (int i = threadIdx.x; i < LW * LT; i += LT * LT) {
+        const int r = i / LT, c = i % LT;
+        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, a4 = 0.f;
+#pragma unroll
+        for (int k = 0; k < 11; k++) {
+            const float w = c_gw[k], vx = sx[r][c + k], vy = sy[r][c + k];
+            a0 += w * vx; a1 += w * vy; a2 += w * vx * vx; a3 += w * vy * vy; a4 += w * vx * vy;
+        }
+        hq[0][r][c] = a0; hq[1][r][c] = a1; hq[2][r][c] = a2; hq[3][r][c] = a3; hq[4][r][c] = a4;
+    }
+    __syncthreads();
+    const int lx = threadIdx.x % LT, ly = threadIdx.x / LT;
+    const int px = blockIdx.x * LT + lx, py = blockIdx.y * LT + ly;
+    float l1 = 0.f, ss = 0.f;
+    if (px < W && py < H) {
+        float mu1 = 0.f, mu2 = 0.f, e11 = 0.f, e22 = 0.f, e12 = 0.f;
+#pragma unroll
+        for (int k = 0; k < 11; k++) {
+            const float w = c_gw[k];
+            mu1 += w * hq[0][ly + k][lx]; mu2 += w * hq[1][ly + k][lx]; e11 += w * hq[2][ly + k][lx];
+            e22 += w * hq[3][ly + k][lx]; e12 += w * hq[4][ly + k][lx];
+        }
+        const float C1 = 0.01f * 0.01f, C2 = 0.03f * 0.03f;
+        const float mu1_sq = mu1 * mu1, mu2_sq = mu2 * mu2, mu12 = mu1 * mu2;
+        const float s1 = e11 - mu1_sq, s2 = e22 - mu2_sq, s12 = e12 - mu12;
+        const float n1 = 2.f * mu12 + C1, n2 = 2.f * s12 + C2;
+        const float d1 = mu1_sq + mu2_sq + C1, d2 = s1 + s2 + C2;
+        const float inv = 1.f / (d1 * d2);
+        const float S = n1 * n2 * inv;
+        // partials of S
+        const float dS_dmu1_direct = (2.f * mu2 * n2 * d1 - n1 * n2 * 2.f * mu1) / (d1 * d1 * d2);
+        const float dS_ds1 = -n1 * n2 / (d1 * d2 * d2);
+        const float dS_ds12 = 2.f * n1 * inv;
+        const float A = dS_dmu1_direct + dS_ds1 * (-2.f * mu1) + dS_ds12 * (-mu2);
+        const size_t o = (size_t)py * W + px;
+        maps[ch * plane + o] = A;
+        maps[((size_t)gridDim.z + ch) * plane + o] = dS_ds1;
+        maps[((size_t)2 * gridDim.z + ch) * plane + o] = dS_ds12;
+        ss = S;
+        l1 = fabsf(sx[ly + HALO][lx + HALO] - sy[ly + HALO][lx + HALO]);
+    }
+    // block sums -> two double atomics
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        l1 += __shfl_xor_sync(0xffffffffu, l1, o);
+        ss += __shfl_xor_sync(0xffffffffu, ss, o);
+    }
+    if ((threadIdx.x & 31) == 0) { red[0][threadIdx.x >> 5] = l1; red[1][threadIdx.x >> 5] = ss; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double a = 0.0, b = 0.0;
+        for (int w = 0; w < LT * LT / 32; w++) { a += red[0][w]; b += red[1][w]; }
+        atomicAdd(&sums[0], a);
+        atomicAdd(&sums[1], b);
+    }
+}
+
+__global__ void photo_loss_finalize_kernel(const double* __restrict__ sums, double n, float lambda, float* __restrict__ out)
+{
+    const double l1 = sums[0] / n, ssim = sums[1] / n;
+    out[0] = (float)((1.0 - (double)lambda) * l1 + (double)lambda * (1.0 - ssim));
+    out[1] = (float)l1;
+    out[2] = (float)ssim;
+}
+
+__global__ void __launch_bounds__(LT * LT)
+photo_loss_backward_kernel(int H, int W, const float* __restrict__ img, const float* __restrict__ gt, int clamp_img,
+                           const float* __restrict__ maps, float lambda, const float* __restrict__ grad_loss,
+                           float* __restrict__ dL_dimg)
+{
+    __shared__ float sm[3][LW][LW + 1];
+    __shared__ float hq[3][LW][LT];
+    const int ch = blockIdx.z, C = gridDim.z;
+    const size_t plane = (size_t)H * W;
+    const int x0 = blockIdx.x * LT - HALO, y0 = blockIdx.y * LT - HALO;
+    for (int i = threadIdx.x; i < LW * LW; i += LT * LT) {
+        const int r = i / LW, c = i % LW;
+        const int gy = y0 + r, gx = x0 + c;
+        float a = 0.f, b = 0.f, cc = 0.f;
+        if (gy >= 0 && gy < H && gx >= 0 && gx < W) {
+            const size_t o = (size_t)gy * W + gx;
+            a = maps[ch * plane + o];
+            b = maps[((size_t)C + ch) * plane + o];
+            cc = maps[((size_t)2 * C + ch) * plane + o];
+        }
+        sm[0][r][c] = a; sm[1][r][c] = b; sm[2][r][c] = cc;
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < LW * LT; i += LT * LT) {
+        const int r = i / LT, c = i % LT;
+        float a0 = 0.f, a1 = 0.f, a2 = 0.f;
+#pragma unroll
+        for (int k = 0; k < 11; k++) {
+            const float w = c_gw[k];
+            a0 += w * sm[0][r][c + k]; a1 += w * sm[1][r][c + k]; a2 += w * sm[2][r][c + k];
+        }
+        hq[0][r][c] = a0; hq[1][r][c] = a1; hq[2][r][c] = a2;
+    }
+    __syncthreads();
+    const int lx = threadIdx.x % LT, ly = threadIdx.x / LT;
+    const int px = blockIdx.x * LT + lx, py = blockIdx.y * LT + ly;
+    if (px < W && py < H) {
+        float ga = 0.f, gb = 0.f, gc = 0.f;
+#pragma unroll
+        for (int k = 0; k < 11; k++) {
+            const float w = c_gw[k];
+            ga += w * hq[0][ly + k][lx]; gb += w * hq[1][ly + k][lx]; gc += w * hq[2][ly + k][lx];
+        }
+        const size_t o = ch * plane + (size_t)py * W + px;
+        const float raw = img[o];
+        const float xv = clamp01(raw, clamp_img), yv = gt[o];
+        const float n = (float)((double)C * (double)plane);
+        const float diff = xv - yv;
+        const float sgn = diff > 0.f ? 1.f : (diff < 0.f ? -1.f : 0.f);
+        float gval = (1.f - lambda) / n * sgn - lambda / n * (ga + 2.f * xv * gb + yv * gc);
+        if (clamp_img && (raw < 0.f || raw > 1.f)) gval = 0.f;
+        dL_dimg[o] = gval * grad_loss[0];
+    }
+}
+
+int ensure_window()
+{
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return -1;
+    if (g_gw_ready[dev]) return 0;
+    // utils/loss_utils.py:21-23: exp(-(x-5)^2 / (2*1.5^2)) / sum, float32
+    double g[11], sum = 0.0;
+    for (int i = 0; i < 11; i++) { g[i] = exp(-(double)((i - 5) * (i - 5)) / (2.0 * 1.5 * 1.5)); }
+    float gf[11], fsum = 0.f;
+    for (int i = 0; i < 11; i++) { gf[i] = (float)g[i]; fsum += gf[i]; sum += g[i]; }
+    for (int i = 0; i < 11; i++) gf[i] = gf[i] / fsum;
+    if (cudaMemcpyToSymbol(c_gw, gf, sizeof(gf)) != cudaSuccess) return -1;
+    g_gw_ready[dev] = true;
+    return 0;
+}
+
+}  // namespace
+}  // namespace gsr
+
+using namespace gsr;
+
+extern "C" size_t gsr_photo_loss_scratch_bytes(int C, int H, int W)
+{
+    return (size_t)3 * C * H * W * sizeof(float) + 256;
+}
+
+extern "C" int gsr_photo_loss_forward(int C, int H, int W, const float* img, const float* gt, float lambda_dssim,
+                                      int clamp_img, void* scratch, float* loss_out, void* stream)
+{
+    cudaStream_t s = (cudaStream_t)stream;
+    if (C <= 0 || H <= 0 || W <= 0 || !img || !gt || !scratch || !loss_out) {
+        set_last_error("gsr_photo_loss_forward: bad argument");
+        return GSR_ERR_INVALID;
+    }
+    if (ensure_window() != 0) { set_last_error("gsr_photo_loss_forward: cannot upload the window"); return GSR_ERR_CUDA; }
+    float* maps = (float*)scratch;
+    double* sums = (double*)((char*)scratch + (size_t)3 * C * H * W * sizeof(float));
+    sums = (double*)(((uintptr_t)sums + 15) & ~(uintptr_t)15);
+    cudaMemsetAsync(sums, 0, 2 * sizeof(double), s);
+    const dim3 grid((W + LT - 1) / LT, (H + LT - 1) / LT, C);
+    photo_loss_forward_kernel<<<grid, LT * LT, 0, s>>>(H, W, img, gt, clamp_img, maps, sums);
+    photo_loss_finalize_kernel<<<1, 1, 0, s>>>(sums, (double)C * H * W, lambda_dssim, loss_out);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { set_last_error(cudaGetErrorString(e)); return GSR_ERR_CUDA; }
+    return GSR_OK;
+}
+
+extern "C" int gsr_photo_loss_backward(int C, int H, int W, const float* img, const float* gt, float lambda_dssim,
+                                       int clamp_img, const void* scratch, const float* grad_loss, float* dL_dimg,
+                                       void* stream)
+{
+    cudaStream_t s = (cudaStream_t)stream;
+    if (C <= 0 || H <= 0 || W <= 0 || !img || !gt || !scratch || !grad_loss || !dL_dimg) {
+        set_last_error("gsr_photo_loss_backward: bad argument");
+        return GSR_ERR_INVALID;
+    }
+    if (ensure_window() != 0) { set_last_error("gsr_photo_loss_backward: cannot upload the window"); return GSR_ERR_CUDA; }
+    const dim3 grid((W + LT - 1) / LT, (H + LT - 1) / LT, C);
+    photo_loss_backward_kernel<<<grid, LT * LT, 0, s>>>(H, W, img, gt, clamp_img, (const float*)scratch, lambda_dssim,
+                                                        grad_loss, dL_dimg);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { set_last_error(cudaGetErrorString(e)); return GSR_ERR_CUDA; }
+    return GSR_OK;
+}

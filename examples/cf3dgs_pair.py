@@ -56,7 +56,16 @@ def ssim(img1, img2, window):
 
 
 def photometric_loss(img, gt, window, lam=0.2):
+    """PyTorch formulation (what the reference trainer runs): expects the clamped image."""
+    img = img.clamp(0, 1)
     return (1.0 - lam) * (img - gt).abs().mean() + lam * (1.0 - ssim(img.unsqueeze(0), gt.unsqueeze(0), window))
+
+
+def make_loss(kind):
+    if kind == "fused":
+        import gsr_loss
+        return lambda img, gt, window: gsr_loss.photometric_loss(img, gt, 0.2, clamp=True)
+    return photometric_loss
 
 
 def true_offset(p):
@@ -67,6 +76,7 @@ def true_offset(p):
 
 def run_pair(p, args, dev, backend):
     import gsr_pose as GP
+    loss_fn = make_loss(args.loss)
     W, H = args.width, args.height
     cam = S.make_camera(W, H)
     sc = S.make_gpix(W, H, seed=2 + p, target_P=args.points)
@@ -97,8 +107,8 @@ def run_pair(p, args, dev, backend):
     t0 = time.time()
     for it in range(args.fit_iters):
         img = backend["render"](rs, zero6, xyz, eye, torch.sigmoid(opa_raw), shs=torch.cat([f_dc, f_rest], 1),
-                                scales=torch.exp(log_s), rotations=F.normalize(rot))[0].clamp(0, 1)
-        loss = photometric_loss(img, frame0, window)
+                                scales=torch.exp(log_s), rotations=F.normalize(rot))[0]
+        loss = loss_fn(img, frame0, window)
         loss.backward()
         opt.step(); opt.zero_grad(set_to_none=True)
     torch.cuda.synchronize(dev)
@@ -118,8 +128,8 @@ def run_pair(p, args, dev, backend):
     t0 = time.time()
     for it in range(args.pose_iters):
         xi = torch.zeros(6, device=dev, requires_grad=True)
-        img = backend["render"](rs, xi, xyz_f, T, opa, **fr)[0].clamp(0, 1)
-        loss = photometric_loss(img, frame1, window)
+        img = backend["render"](rs, xi, xyz_f, T, opa, **fr)[0]
+        loss = loss_fn(img, frame1, window)
         loss.backward()
         g = xi.grad
         m = b1 * m + (1 - b1) * g; v = b2 * v + (1 - b2) * g * g
@@ -185,7 +195,11 @@ def main():
     ap.add_argument("--height", type=int, default=540)
     ap.add_argument("--pose-lr", type=float, default=1e-3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--loss", default=None, choices=["fused", "torch"],
+                    help="fused CUDA L1+SSIM (default for --impl ours) or the PyTorch formulation (default for reference)")
     args = ap.parse_args()
+    if args.loss is None:
+        args.loss = "fused" if args.impl == "ours" else "torch"
     world = int(os.environ.get("WORLD_SIZE", "1")); rank = int(os.environ.get("RANK", "0")); local = int(os.environ.get("LOCAL_RANK", "0"))
     real_stdout = os.dup(1); os.dup2(2, 1)
     if world > 1:
@@ -220,7 +234,7 @@ def main():
         err_t, err_r = max(r["err_t"] for r in res), max(r["err_r_deg"] for r in res)
     if rank == 0:
         n_local = len(GPar.shard_pairs(args.pairs, 0, world))
-        line = {"workload": "cf3dgs_local_pair", "impl": args.impl, "n_gpus": world, "pairs": args.pairs, "P": res[0]["P"] if res else 0,
+        line = {"workload": "cf3dgs_local_pair", "impl": args.impl, "loss": args.loss, "n_gpus": world, "pairs": args.pairs, "P": res[0]["P"] if res else 0,
                 "W": args.width, "H": args.height, "fit_iters": args.fit_iters, "pose_iters": args.pose_iters,
                 "wall_s": wall, "pairs_per_s": args.pairs / wall,
                 "pose_opt_iters_per_s": args.pairs * args.pose_iters / (pose_s * world) * world if pose_s > 0 else None,

@@ -1,0 +1,80 @@
+"""GPU: the fused L1 + SSIM loss against the reference's PyTorch formulation (utils/loss_utils.py, trainer/losses.py)."""
+import math
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def _window(device, dtype):
+    g = torch.tensor([math.exp(-(x - 5) ** 2 / float(2 * 1.5 ** 2)) for x in range(11)])
+    g = (g / g.sum()).unsqueeze(1)
+    return g.mm(g.t()).float().unsqueeze(0).unsqueeze(0).expand(3, 1, 11, 11).contiguous().to(device=device, dtype=dtype)
+
+
+def _ref_loss(img, gt, lam, clamp):
+    """utils/loss_utils.py:_ssim + l1_loss, combined as trainer/losses.py:113-123."""
+    x = img.clamp(0, 1) if clamp else img
+    w = _window(x.device, x.dtype)
+    x4, y4 = x.unsqueeze(0), gt.unsqueeze(0)
+    mu1 = F.conv2d(x4, w, padding=5, groups=3); mu2 = F.conv2d(y4, w, padding=5, groups=3)
+    mu1_sq, mu2_sq, mu12 = mu1.pow(2), mu2.pow(2), mu1 * mu2
+    s1 = F.conv2d(x4 * x4, w, padding=5, groups=3) - mu1_sq
+    s2 = F.conv2d(y4 * y4, w, padding=5, groups=3) - mu2_sq
+    s12 = F.conv2d(x4 * y4, w, padding=5, groups=3) - mu12
+    C1, C2 = 0.01 ** 2, 0.03 ** 2
+    ssim = (((2 * mu12 + C1) * (2 * s12 + C2)) / ((mu1_sq + mu2_sq + C1) * (s1 + s2 + C2))).mean()
+    l1 = (x - gt).abs().mean()
+    return (1 - lam) * l1 + lam * (1 - ssim), l1, ssim
+
+
+@pytest.mark.parametrize("shape", [(3, 540, 960), (3, 67, 93), (3, 16, 16)])
+@pytest.mark.parametrize("clamp", [False, True])
+def test_fused_loss_matches_reference_formulation(shape, clamp):
+    import gsr_loss
+    g = torch.Generator().manual_seed(5)
+    img = (torch.rand(shape, generator=g) * (1.4 if clamp else 1.0) - (0.2 if clamp else 0.0)).to(DEV)
+    # smooth-ish target so SSIM is not degenerate
+    gt = F.avg_pool2d(torch.rand(1, *shape, generator=g), 5, 1, 2)[0].to(DEV)
+    a = img.clone().requires_grad_(True)
+    loss, parts = gsr_loss.photometric_loss(a, gt, 0.2, clamp=clamp, return_parts=True)
+    (loss * 3.0).backward()
+    b = img.double().clone().requires_grad_(True)
+    ref, l1, ssim = _ref_loss(b, gt.double(), 0.2, clamp)
+    (ref * 3.0).backward()
+    assert abs(float(loss) - float(ref)) <= 1e-5 * max(1.0, abs(float(ref)))
+    assert abs(float(parts[1]) - float(l1)) <= 1e-5 and abs(float(parts[2]) - float(ssim)) <= 1e-5
+    err = float((a.grad.double() - b.grad).abs().max()) / float(b.grad.abs().max())
+    assert err <= 1e-4, err
+
+
+def test_fused_loss_is_faster_than_the_torch_formulation():
+    import gsr_loss
+    img = torch.rand(3, 540, 960, device=DEV)
+    gt = torch.rand(3, 540, 960, device=DEV)
+
+    def run(fn, n=20):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(n):
+            fn()
+        e1.record(); torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / n
+
+    def fused():
+        a = img.clone().requires_grad_(True)
+        gsr_loss.photometric_loss(a, gt, 0.2, clamp=True).backward()
+
+    def plain():
+        a = img.clone().requires_grad_(True)
+        _ref_loss(a, gt, 0.2, True)[0].backward()
+
+    tf, tp = run(fused), run(plain)
+    print(f"fused {tf:.3f} ms  torch {tp:.3f} ms")
+    assert tf < tp
