@@ -88,18 +88,15 @@ size_t gsr_binning_bytes(int64_t num_rendered, int W, int H)
 
 size_t gsr_pose_scratch_bytes(int P) { return (size_t)pose_blocks(P > 0 ? P : 1) * 6 * sizeof(float); }
 
-int gsr_forward_prepare(int P, int sh_degree, int M, const float* means3D, const float* scales,
-                        float scale_modifier, const float* rotations, const float* opacities,
-                        const float* shs, const float* cov3D_precomp, const float* colors_precomp,
-                        const float* viewmatrix, const float* projmatrix, const float* campos, int W, int H,
-                        float tanfovx, float tanfovy, int prefiltered, int* radii, void* geometry,
-                        size_t geometry_bytes, int64_t* num_rendered_host, void* stream, int debug)
+// ---- shared pieces of the two forward flavours --------------------------------------------------------
+static int check_forward_args(int P, int sh_degree, int M, const float* means3D, const float* scales,
+                              const float* rotations, const float* opacities, const float* shs,
+                              const float* cov3D_precomp, const float* colors_precomp, const float* viewmatrix,
+                              const float* projmatrix, const float* campos, int W, int H, const int* radii,
+                              const void* geometry, size_t geometry_bytes)
 {
-    cudaStream_t s = (cudaStream_t)stream;
-    if (!num_rendered_host) return fail(GSR_ERR_INVALID, "num_rendered_host is NULL");
-    *num_rendered_host = 0;
     if (P < 0 || W <= 0 || H <= 0) return fail(GSR_ERR_INVALID, "bad sizes P=%d W=%d H=%d", P, W, H);
-    if (P == 0) return GSR_OK;  // rasterize_points.cu:83 -- nothing launched
+    if (P == 0) return GSR_OK;
     if (!means3D || !opacities || !viewmatrix || !projmatrix || !radii || !geometry)
         return fail(GSR_ERR_INVALID, "means3D, opacities, matrices, radii and geometry workspace are required");
     if ((shs == nullptr) == (colors_precomp == nullptr))
@@ -111,9 +108,84 @@ int gsr_forward_prepare(int P, int sh_degree, int M, const float* means3D, const
                     (sh_degree + 1) * (sh_degree + 1), M);
     if (shs && !campos) return fail(GSR_ERR_INVALID, "campos is required with SHs");
     if (div_up(W, TILE) > 65535 || div_up(H, TILE) > 65535) return fail(GSR_ERR_INVALID, "image too large");
-    GeomView g;
     if (gsr_geometry_bytes(P) > geometry_bytes)
         return fail(GSR_ERR_WORKSPACE, "geometry workspace too small: %zu < %zu", geometry_bytes, gsr_geometry_bytes(P));
+    return GSR_OK;
+}
+
+// depth-digit passes of the key sort + instance offsets (stages 2-3)
+static int depth_sort_and_offsets(int P, const GeomView& g, cudaStream_t s)
+{
+    {
+        StageTimer t(ST_DEPTH_SORT, s);
+        launch_init_sort_input(g, P, s);
+        uint32_t* keys[2] = {g.sort_keys[0], g.sort_keys[1]};
+        uint32_t* vals[2] = {g.sort_vals[0], g.sort_vals[1]};
+        const int cur = radix_sort_pairs(keys, vals, P, 0, 32, g.hist, g.digit_total, s);
+        if (cur != 0)  // keep the invariant "sort_vals[0] holds the depth order"
+            cudaMemcpyAsync(g.sort_vals[0], g.sort_vals[1], sizeof(uint32_t) * (size_t)P, cudaMemcpyDeviceToDevice, s);
+    }
+    { StageTimer t(ST_OFFSETS, s); launch_offsets_scan(g.tiles, g.sort_vals[0], g.offsets, g.block_sums, P, s); }
+    return GSR_OK;
+}
+
+// stages 4-7.  n_layout sizes the binning workspace; with n_dev != nullptr the real count is read on the device.
+static int bin_and_render(int P, int W, int H, int64_t n_layout, const unsigned long long* n_dev, const float* background,
+                          void* geometry, void* binning, void* image, float* out_color, float* out_depth,
+                          float* out_alpha, cudaStream_t s, int debug)
+{
+    GeomView g;
+    geom_layout((char*)geometry, P, g);
+    ImageView iv;
+    image_layout((char*)image, W, H, iv);
+    BinView b;
+    bin_layout((char*)binning, n_layout, b);
+    const int gx = div_up(W, TILE), gy = div_up(H, TILE), tiles = gx * gy;
+    if (n_layout > 0) {
+        { StageTimer t(ST_EMIT, s); launch_emit(g, g.sort_vals[0], P, gx, b.keys[0], b.vals[0], n_layout, s); }
+        GSR_STAGE("emit");
+        {
+            StageTimer t(ST_TILE_SORT, s);
+            const int cur = radix_sort_pairs(b.keys, b.vals, n_layout, 0, tile_bits(tiles), b.hist, b.digit_total, s, n_dev);
+            if (cur != 0) {  // invariant: keys[0]/vals[0] hold the sorted list
+                cudaMemcpyAsync(b.keys[0], b.keys[1], sizeof(uint32_t) * (size_t)n_layout, cudaMemcpyDeviceToDevice, s);
+                cudaMemcpyAsync(b.vals[0], b.vals[1], sizeof(uint32_t) * (size_t)n_layout, cudaMemcpyDeviceToDevice, s);
+            }
+        }
+        GSR_STAGE("tile sort");
+    }
+    { StageTimer t(ST_RANGES, s); launch_tile_ranges(b.keys[0], n_layout, iv.ranges, tiles, s, n_dev); }
+    GSR_STAGE("tile ranges");
+    {
+        StageTimer t(ST_RENDER_FWD, s);
+        launch_render_forward(W, H, iv.ranges, b.vals[0], g, background, out_color, out_depth, out_alpha, iv.n_contrib, s);
+    }
+    GSR_STAGE("render");
+    return GSR_OK;
+}
+
+static void zero_images(int W, int H, float* out_color, float* out_depth, float* out_alpha, cudaStream_t s)
+{
+    cudaMemsetAsync(out_color, 0, sizeof(float) * 3 * (size_t)W * H, s);
+    cudaMemsetAsync(out_depth, 0, sizeof(float) * (size_t)W * H, s);
+    cudaMemsetAsync(out_alpha, 0, sizeof(float) * (size_t)W * H, s);
+}
+
+int gsr_forward_prepare(int P, int sh_degree, int M, const float* means3D, const float* scales,
+                        float scale_modifier, const float* rotations, const float* opacities,
+                        const float* shs, const float* cov3D_precomp, const float* colors_precomp,
+                        const float* viewmatrix, const float* projmatrix, const float* campos, int W, int H,
+                        float tanfovx, float tanfovy, int prefiltered, int* radii, void* geometry,
+                        size_t geometry_bytes, int64_t* num_rendered_host, void* stream, int debug)
+{
+    cudaStream_t s = (cudaStream_t)stream;
+    if (!num_rendered_host) return fail(GSR_ERR_INVALID, "num_rendered_host is NULL");
+    *num_rendered_host = 0;
+    const int rc = check_forward_args(P, sh_degree, M, means3D, scales, rotations, opacities, shs, cov3D_precomp,
+                                      colors_precomp, viewmatrix, projmatrix, campos, W, H, radii, geometry, geometry_bytes);
+    if (rc != GSR_OK) return rc;
+    if (P == 0) return GSR_OK;  // rasterize_points.cu:83 -- nothing launched
+    GeomView g;
     geom_layout((char*)geometry, P, g);
 
     PreprocessArgs a;
@@ -133,16 +205,7 @@ int gsr_forward_prepare(int P, int sh_degree, int M, const float* means3D, const
     cudaMemcpyAsync(num_rendered_host, g.counters, sizeof(int64_t), cudaMemcpyDeviceToHost, s);
     cudaEventRecord(ev, s);
 
-    // low 32 key bits (depth) sorted over Gaussians, before duplication
-    {
-        StageTimer t(ST_DEPTH_SORT, s);
-        launch_init_sort_input(g, P, s);
-        const int cur = radix_sort_pairs(g.sort_keys, g.sort_vals, P, 0, 32, g.hist, g.digit_total, s);
-        if (cur != 0) {  // keep the invariant "sort_vals[0] holds the depth order"
-            cudaMemcpyAsync(g.sort_vals[0], g.sort_vals[1], sizeof(uint32_t) * (size_t)P, cudaMemcpyDeviceToDevice, s);
-        }
-    }
-    { StageTimer t(ST_OFFSETS, s); launch_offsets_scan(g.tiles, g.sort_vals[0], g.offsets, g.block_sums, P, s); }
+    depth_sort_and_offsets(P, g, s);   // low 32 key bits (depth) sorted over Gaussians, before duplication
 
     e = cudaEventSynchronize(ev);
     cudaEventDestroy(ev);
@@ -165,9 +228,7 @@ int gsr_forward_render(int P, int W, int H, int64_t num_rendered, const float* b
     if (W <= 0 || H <= 0) return fail(GSR_ERR_INVALID, "bad image size");
     if (!out_color || !out_depth || !out_alpha) return fail(GSR_ERR_INVALID, "outputs are required");
     if (P == 0) {  // reference returns zero images without launching (rasterize_points.cu:68-71,83)
-        cudaMemsetAsync(out_color, 0, sizeof(float) * 3 * (size_t)W * H, s);
-        cudaMemsetAsync(out_depth, 0, sizeof(float) * (size_t)W * H, s);
-        cudaMemsetAsync(out_alpha, 0, sizeof(float) * (size_t)W * H, s);
+        zero_images(W, H, out_color, out_depth, out_alpha, s);
         return GSR_OK;
     }
     if (!geometry || !binning || !image || !background)
@@ -175,35 +236,48 @@ int gsr_forward_render(int P, int W, int H, int64_t num_rendered, const float* b
     if (gsr_binning_bytes(num_rendered, W, H) > binning_bytes)
         return fail(GSR_ERR_WORKSPACE, "binning workspace too small: %zu < %zu", binning_bytes,
                     gsr_binning_bytes(num_rendered, W, H));
+    return bin_and_render(P, W, H, num_rendered, nullptr, background, geometry, binning, image, out_color, out_depth,
+                          out_alpha, s, debug);
+}
+
+int gsr_forward_fused(int P, int sh_degree, int M, const float* means3D, const float* scales, float scale_modifier,
+                      const float* rotations, const float* opacities, const float* shs, const float* cov3D_precomp,
+                      const float* colors_precomp, const float* viewmatrix, const float* projmatrix,
+                      const float* campos, int W, int H, float tanfovx, float tanfovy, const float* background,
+                      int* radii, void* geometry, size_t geometry_bytes, void* binning, size_t binning_bytes,
+                      int64_t capacity, void* image, float* out_color, float* out_depth, float* out_alpha,
+                      int64_t* status, void* stream, int debug)
+{
+    cudaStream_t s = (cudaStream_t)stream;
+    if (!out_color || !out_depth || !out_alpha || !status) return fail(GSR_ERR_INVALID, "outputs and status are required");
+    if (capacity < 1 || capacity > 0x7fffffffll) return fail(GSR_ERR_INVALID, "capacity out of range");
+    const int rc = check_forward_args(P, sh_degree, M, means3D, scales, rotations, opacities, shs, cov3D_precomp,
+                                      colors_precomp, viewmatrix, projmatrix, campos, W, H, radii, geometry, geometry_bytes);
+    if (rc != GSR_OK) return rc;
+    if (P == 0) {
+        zero_images(W, H, out_color, out_depth, out_alpha, s);
+        cudaMemsetAsync(status, 0, 2 * sizeof(int64_t), s);
+        return GSR_OK;
+    }
+    if (!binning || !image || !background) return fail(GSR_ERR_INVALID, "workspaces and background are required");
+    if (gsr_binning_bytes(capacity, W, H) > binning_bytes)
+        return fail(GSR_ERR_WORKSPACE, "binning workspace too small for capacity %lld: %zu < %zu", (long long)capacity,
+                    binning_bytes, gsr_binning_bytes(capacity, W, H));
     GeomView g;
     geom_layout((char*)geometry, P, g);
-    ImageView iv;
-    image_layout((char*)image, W, H, iv);
-    BinView b;
-    bin_layout((char*)binning, num_rendered, b);
-    const int gx = div_up(W, TILE), gy = div_up(H, TILE), tiles = gx * gy;
-
-    if (num_rendered > 0) {
-        { StageTimer t(ST_EMIT, s); launch_emit(g, g.sort_vals[0], P, gx, b.keys[0], b.vals[0], s); }
-        GSR_STAGE("emit");
-        {
-            StageTimer t(ST_TILE_SORT, s);
-            const int cur = radix_sort_pairs(b.keys, b.vals, num_rendered, 0, tile_bits(tiles), b.hist, b.digit_total, s);
-            if (cur != 0) {  // invariant: keys[0]/vals[0] hold the sorted list
-                cudaMemcpyAsync(b.keys[0], b.keys[1], sizeof(uint32_t) * (size_t)num_rendered, cudaMemcpyDeviceToDevice, s);
-                cudaMemcpyAsync(b.vals[0], b.vals[1], sizeof(uint32_t) * (size_t)num_rendered, cudaMemcpyDeviceToDevice, s);
-            }
-        }
-        GSR_STAGE("tile sort");
-    }
-    { StageTimer t(ST_RANGES, s); launch_tile_ranges(b.keys[0], num_rendered, iv.ranges, tiles, s); }
-    GSR_STAGE("tile ranges");
-    {
-        StageTimer t(ST_RENDER_FWD, s);
-        launch_render_forward(W, H, iv.ranges, b.vals[0], g, background, out_color, out_depth, out_alpha, iv.n_contrib, s);
-    }
-    GSR_STAGE("render");
-    return GSR_OK;
+    PreprocessArgs a;
+    a.P = P; a.D = sh_degree; a.M = M;
+    a.means3D = means3D; a.scales = scales; a.scale_modifier = scale_modifier; a.rotations = rotations;
+    a.opacities = opacities; a.shs = shs; a.cov3D_precomp = cov3D_precomp; a.colors_precomp = colors_precomp;
+    a.viewmatrix = viewmatrix; a.projmatrix = projmatrix; a.campos = campos ? campos : viewmatrix;
+    a.W = W; a.H = H; a.tanfovx = tanfovx; a.tanfovy = tanfovy; a.prefiltered = 0; a.radii = radii;
+    { StageTimer t(ST_PREPROCESS, s); launch_preprocess(a, g, s); }
+    GSR_STAGE("preprocess");
+    launch_publish_status(g.counters, capacity, (long long*)status, s);
+    depth_sort_and_offsets(P, g, s);
+    GSR_STAGE("depth sort + offsets");
+    return bin_and_render(P, W, H, capacity, g.counters, background, geometry, binning, image, out_color, out_depth,
+                          out_alpha, s, debug);
 }
 
 int gsr_backward(int P, int sh_degree, int M, int W, int H, int64_t num_rendered, const float* background,

@@ -30,15 +30,18 @@ void launch_mark_visible(int P, const float* means3D, const float* view, uint8_t
 // RADIX_BITS per pass, ping-ponging between buffers 0 and 1.  Returns the index (0/1) of the buffer that
 // holds the result.
 int radix_sort_pairs(uint32_t* keys[2], uint32_t* vals[2], int64_t n, int begin_bit, int end_bit,
-                     uint32_t* hist, uint32_t* digit_total, cudaStream_t s);
+                     uint32_t* hist, uint32_t* digit_total, cudaStream_t s,
+                     const unsigned long long* n_dev = nullptr);
 
 // offsets[i] = exclusive prefix sum of tiles[order[i]]
 void launch_offsets_scan(const uint32_t* tiles, const uint32_t* order, uint32_t* offsets, uint32_t* block_sums,
                          int P, cudaStream_t s);
 void launch_init_sort_input(const GeomView& g, int P, cudaStream_t s);
 void launch_emit(const GeomView& g, const uint32_t* order, int P, int grid_x, uint32_t* tile_keys,
-                 uint32_t* tile_vals, cudaStream_t s);
-void launch_tile_ranges(const uint32_t* sorted_tiles, int64_t R, uint2* ranges, int tiles, cudaStream_t s);
+                 uint32_t* tile_vals, int64_t cap, cudaStream_t s);
+void launch_tile_ranges(const uint32_t* sorted_tiles, int64_t R, uint2* ranges, int tiles, cudaStream_t s,
+                        const unsigned long long* n_dev = nullptr);
+void launch_publish_status(const unsigned long long* counters, int64_t cap, long long* status, cudaStream_t s);
 void launch_build_keys(const uint32_t* sorted_tiles, const uint32_t* point_list, const uint32_t* depth_key,
                        int64_t R, uint64_t* keys_out, cudaStream_t s);
 

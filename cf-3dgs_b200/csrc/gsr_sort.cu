@@ -26,13 +26,23 @@
 
 namespace gsr {
 
+// In the sync-free forward the instance count lives only on the device: kernels launched for `cap` items read the
+// real count (bit 62 of the counter is the prefilter flag) and clamp it to the capacity of the workspace.
+__device__ __forceinline__ int64_t device_count(const unsigned long long* n_dev, int64_t cap)
+{
+    if (!n_dev) return cap;
+    const unsigned long long v = *n_dev & ((1ull << 62) - 1ull);
+    return v < (unsigned long long)cap ? (int64_t)v : cap;
+}
+
 // ---------------------------------------------------------------------------------------------
 // pass kernel 1: per-block digit histogram, written digit-major: hist[d * nblk + block]
 __global__ void __launch_bounds__(SORT_THREADS)
-radix_hist_kernel(const uint32_t* __restrict__ keys, int64_t n, int shift, uint32_t mask,
-                  uint32_t* __restrict__ hist, int nblk)
+radix_hist_kernel(const uint32_t* __restrict__ keys, int64_t n_cap, const unsigned long long* __restrict__ n_dev,
+                  int shift, uint32_t mask, uint32_t* __restrict__ hist, int nblk)
 {
     __shared__ uint32_t sh[RADIX];
+    const int64_t n = device_count(n_dev, n_cap);
     sh[threadIdx.x] = 0;
     __syncthreads();
     const int64_t base = (int64_t)blockIdx.x * SORT_CHUNK;
@@ -80,12 +90,14 @@ radix_rowscan_kernel(uint32_t* __restrict__ hist, int nblk, uint32_t* __restrict
 // written out in that order, so a warp's stores fall into a few contiguous runs (one per digit) instead of 32 sectors.
 __global__ void __launch_bounds__(SORT_THREADS)
 radix_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
-                     uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int64_t n, int shift,
+                     uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int64_t n_cap,
+                     const unsigned long long* __restrict__ n_dev, int shift,
                      uint32_t mask, const uint32_t* __restrict__ hist, int nblk,
                      const uint32_t* __restrict__ digit_total)
 {
     __shared__ uint32_t wcount[SORT_THREADS / 32][RADIX + 1];
     __shared__ uint32_t goff[RADIX];   // global base of digit d for this block minus its block-local start
+    const int64_t n = device_count(n_dev, n_cap);
     __shared__ uint32_t warp_sums[8];
     __shared__ uint32_t skey[SORT_CHUNK], sval[SORT_CHUNK];
     const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -149,7 +161,7 @@ radix_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __res
         }
     }
     __syncthreads();
-    const int count = (int)min((int64_t)SORT_CHUNK, n - block_base);
+    const int count = (int)max((int64_t)0, min((int64_t)SORT_CHUNK, n - block_base));
 #pragma unroll
     for (int i = 0; i < SORT_ITEMS; i++) {
         const int t = i * SORT_THREADS + threadIdx.x;
@@ -315,20 +327,20 @@ static bool use_classic_sort()
 }
 
 int radix_sort_pairs(uint32_t* keys[2], uint32_t* vals[2], int64_t n, int begin_bit, int end_bit,
-                     uint32_t* hist, uint32_t* digit_total, cudaStream_t s)
+                     uint32_t* hist, uint32_t* digit_total, cudaStream_t s, const unsigned long long* n_dev)
 {
     int cur = 0;
     if (n <= 0) return cur;
     const int nblk = div_up(n, SORT_CHUNK);
     const int npass = (end_bit - begin_bit + RADIX_BITS - 1) / RADIX_BITS;
-    if (use_classic_sort() || n >= ((int64_t)1 << 30) || npass > SORT_MAX_PASSES) {
+    if (n_dev || use_classic_sort() || n >= ((int64_t)1 << 30) || npass > SORT_MAX_PASSES) {
         for (int shift = begin_bit; shift < end_bit; shift += RADIX_BITS) {
             const int bits = min(RADIX_BITS, end_bit - shift);
             const uint32_t mask = (1u << bits) - 1u;
-            radix_hist_kernel<<<nblk, SORT_THREADS, 0, s>>>(keys[cur], n, shift, mask, hist, nblk);
+            radix_hist_kernel<<<nblk, SORT_THREADS, 0, s>>>(keys[cur], n, n_dev, shift, mask, hist, nblk);
             radix_rowscan_kernel<<<RADIX, SORT_THREADS, 0, s>>>(hist, nblk, digit_total);
             radix_scatter_kernel<<<nblk, SORT_THREADS, 0, s>>>(keys[cur], vals[cur], keys[cur ^ 1], vals[cur ^ 1], n,
-                                                               shift, mask, hist, nblk, digit_total);
+                                                               n_dev, shift, mask, hist, nblk, digit_total);
             cur ^= 1;
         }
         return cur;
@@ -433,7 +445,7 @@ void launch_offsets_scan(const uint32_t* tiles, const uint32_t* order, uint32_t*
 // Gaussian order).  key = tile id only; the depth half of the reference key is implied by the order.
 __global__ void emit_kernel(const uint32_t* __restrict__ order, const uint32_t* __restrict__ tiles,
                             const uint32_t* __restrict__ offsets, const uint2* __restrict__ rect, int P, int grid_x,
-                            uint32_t* __restrict__ tile_keys, uint32_t* __restrict__ tile_vals)
+                            uint32_t* __restrict__ tile_keys, uint32_t* __restrict__ tile_vals, uint32_t cap)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= P) return;
@@ -444,22 +456,27 @@ __global__ void emit_kernel(const uint32_t* __restrict__ order, const uint32_t* 
     const uint32_t x0 = r.x & 0xffffu, x1 = r.x >> 16, y0 = r.y & 0xffffu, y1 = r.y >> 16;
     for (uint32_t y = y0; y < y1; y++)
         for (uint32_t x = x0; x < x1; x++) {
-            tile_keys[off] = y * (uint32_t)grid_x + x;
-            tile_vals[off] = gid;
+            if (off < cap) {   // only the sync-free path can run out of room; it raises the overflow flag elsewhere
+                tile_keys[off] = y * (uint32_t)grid_x + x;
+                tile_vals[off] = gid;
+            }
             off++;
         }
 }
 
 void launch_emit(const GeomView& g, const uint32_t* order, int P, int grid_x, uint32_t* tile_keys,
-                 uint32_t* tile_vals, cudaStream_t s)
+                 uint32_t* tile_vals, int64_t cap, cudaStream_t s)
 {
-    emit_kernel<<<div_up(P, 256), 256, 0, s>>>(order, g.tiles, g.offsets, g.rect, P, grid_x, tile_keys, tile_vals);
+    emit_kernel<<<div_up(P, 256), 256, 0, s>>>(order, g.tiles, g.offsets, g.rect, P, grid_x, tile_keys, tile_vals,
+                                               (uint32_t)cap);
 }
 
 // ---------------------------------------------------------------------------------------------
 // reference identifyTileRanges (rasterizer_impl.cu:116-138) on the sorted tile ids
-__global__ void tile_ranges_kernel(const uint32_t* __restrict__ sorted_tiles, int64_t R, uint2* __restrict__ ranges)
+__global__ void tile_ranges_kernel(const uint32_t* __restrict__ sorted_tiles, int64_t R_cap,
+                                   const unsigned long long* __restrict__ n_dev, uint2* __restrict__ ranges)
 {
+    const int64_t R = device_count(n_dev, R_cap);
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= R) return;
     const uint32_t cur = sorted_tiles[i];
@@ -474,10 +491,25 @@ __global__ void tile_ranges_kernel(const uint32_t* __restrict__ sorted_tiles, in
     if (i == R - 1) ranges[cur].y = (uint32_t)R;
 }
 
-void launch_tile_ranges(const uint32_t* sorted_tiles, int64_t R, uint2* ranges, int tiles, cudaStream_t s)
+void launch_tile_ranges(const uint32_t* sorted_tiles, int64_t R, uint2* ranges, int tiles, cudaStream_t s,
+                        const unsigned long long* n_dev)
 {
     cudaMemsetAsync(ranges, 0, sizeof(uint2) * (size_t)tiles, s);
-    if (R > 0) tile_ranges_kernel<<<div_up(R, 256), 256, 0, s>>>(sorted_tiles, R, ranges);
+    if (R > 0) tile_ranges_kernel<<<div_up(R, 256), 256, 0, s>>>(sorted_tiles, R, n_dev, ranges);
+}
+
+// sync-free forward: publish (count, overflow) for the host to look at whenever it likes
+__global__ void publish_status_kernel(const unsigned long long* __restrict__ counters, long long cap, long long* __restrict__ status)
+{
+    const unsigned long long raw = counters[0];
+    const unsigned long long n = raw & ((1ull << 62) - 1ull);
+    status[0] = (long long)n;
+    status[1] = (n > (unsigned long long)cap ? 1 : 0) | ((raw >> 62) ? 2 : 0);
+}
+
+void launch_publish_status(const unsigned long long* counters, int64_t cap, long long* status, cudaStream_t s)
+{
+    publish_status_kernel<<<1, 1, 0, s>>>(counters, (long long)cap, status);
 }
 
 __global__ void build_keys_kernel(const uint32_t* __restrict__ sorted_tiles, const uint32_t* __restrict__ point_list,

@@ -20,7 +20,7 @@ from . import _cabi
 from ._cabi import check, lib
 
 __all__ = ["GaussianRasterizationSettings", "GaussianRasterizer", "rasterize_gaussians",
-           "cpu_deep_copy_tuple", "rasterizer_state"]
+           "cpu_deep_copy_tuple", "rasterizer_state", "set_sync_free", "sync_free_status"]
 
 
 def cpu_deep_copy_tuple(input_tuple):
@@ -43,6 +43,54 @@ class GaussianRasterizationSettings(NamedTuple):
 
 
 # ---------------------------------------------------------------------------------------------------
+# Sync-free mode (not in the reference API).  The reference -- and the default path here -- reads num_rendered back to
+# the host in every forward to size the binning workspace.  With set_sync_free(True) the forward goes through
+# gsr_forward_fused: the binning workspace is sized from a running estimate (last count x slack), the count stays on
+# the device, nothing synchronises, and the whole training step can be captured in a CUDA graph.  If a call ever needs
+# more room than it was given, its images are incomplete; that is detected from the status word the next time the
+# wrapper gets a chance to look (never inside a graph capture), the estimate is raised and a warning is issued.
+class _SyncFree:
+    enabled = False
+    slack = 1.5
+    capacity = {}      # device index -> instances the binning workspace is sized for
+    pending = {}       # device index -> (event, pinned status, device status)
+    last_status = {}   # device index -> (num_rendered, flags) of the most recent checked call
+
+
+def set_sync_free(enabled: bool, slack: float = 1.5, capacity: Optional[int] = None, device: Optional[int] = None) -> None:
+    """Switch the host-synchronisation-free forward on or off.  `capacity` pins the binning capacity (instances)
+    for `device` (default: current); otherwise the first call on a device runs the synchronising path once to learn
+    the instance count."""
+    _SyncFree.enabled = bool(enabled)
+    _SyncFree.slack = float(slack)
+    if capacity is not None:
+        dev = torch.cuda.current_device() if device is None else device
+        _SyncFree.capacity[dev] = int(capacity)
+
+
+def sync_free_status(device: Optional[int] = None):
+    """(num_rendered, overflowed) of the latest sync-free forward on `device`; synchronises."""
+    dev = torch.cuda.current_device() if device is None else device
+    p = _SyncFree.pending.get(dev)
+    if p is not None:
+        p[0].synchronize()
+        _absorb_status(dev)
+    return _SyncFree.last_status.get(dev)
+
+
+def _absorb_status(dev: int) -> None:
+    ev, pinned, _ = _SyncFree.pending.pop(dev)
+    R, flags = int(pinned[0]), int(pinned[1])
+    _SyncFree.last_status[dev] = (R, bool(flags & 1))
+    want = int(R * _SyncFree.slack) + 1024
+    if flags & 1:
+        import warnings
+        warnings.warn(f"sync-free rasterizer: {R} tile instances exceeded the binning capacity "
+                      f"{_SyncFree.capacity.get(dev)}; that render was incomplete, capacity raised to {want}")
+    if want > _SyncFree.capacity.get(dev, 0):
+        _SyncFree.capacity[dev] = want
+
+
 _pinned_counts = {}
 
 
@@ -100,6 +148,28 @@ def _forward_impl(bg, means3D, colors_precomp, opacities, scales, rotations, sca
         stream = torch.cuda.current_stream().cuda_stream
         geom = torch.empty(lib.gsr_geometry_bytes(P), **u8)
         img = torch.empty(lib.gsr_image_bytes(W, H), **u8)
+        di = dev.index if dev.index is not None else torch.cuda.current_device()
+        if _SyncFree.enabled and not prefiltered and di in _SyncFree.capacity:
+            capturing = torch.cuda.is_current_stream_capturing()
+            if not capturing and di in _SyncFree.pending and _SyncFree.pending[di][0].query():
+                _absorb_status(di)
+            cap = _SyncFree.capacity[di]
+            binning = torch.empty(lib.gsr_binning_bytes(cap, W, H), **u8)
+            status = torch.empty(2, dtype=torch.int64, device=dev)
+            check(lib.gsr_forward_fused(
+                P, int(degree), int(M), _ptr(means3D), _ptr(scales), float(scale_modifier), _ptr(rotations),
+                _ptr(opacities), _ptr(sh), _ptr(cov3Ds_precomp), _ptr(colors_precomp), _ptr(viewmatrix),
+                _ptr(projmatrix), _ptr(campos), int(W), int(H), float(tanfovx), float(tanfovy), _ptr(bg),
+                radii.data_ptr(), geom.data_ptr(), geom.numel(), binning.data_ptr(), binning.numel(), cap,
+                img.data_ptr(), color.data_ptr(), depth.data_ptr(), alpha.data_ptr(), status.data_ptr(), stream,
+                int(bool(debug))))
+            if not capturing and di not in _SyncFree.pending:
+                pinned = torch.empty(2, dtype=torch.int64).pin_memory()
+                pinned.copy_(status, non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record()
+                _SyncFree.pending[di] = (ev, pinned, status)
+            return cap, color, depth, alpha, radii, geom, binning, img
         word = _count_word(dev)
         check(lib.gsr_forward_prepare(
             P, int(degree), int(M), _ptr(means3D), _ptr(scales), float(scale_modifier), _ptr(rotations),
@@ -107,6 +177,8 @@ def _forward_impl(bg, means3D, colors_precomp, opacities, scales, rotations, sca
             _ptr(projmatrix), _ptr(campos), int(W), int(H), float(tanfovx), float(tanfovy), int(bool(prefiltered)),
             radii.data_ptr(), geom.data_ptr(), geom.numel(), word.data_ptr(), stream, int(bool(debug))))
         R = int(word[0])
+        if _SyncFree.enabled:
+            _SyncFree.capacity[di] = max(_SyncFree.capacity.get(di, 0), int(R * _SyncFree.slack) + 1024)
         binning = torch.empty(lib.gsr_binning_bytes(R, W, H), **u8)
         check(lib.gsr_forward_render(
             P, int(W), int(H), R, _ptr(bg), _ptr(colors_precomp), geom.data_ptr(), binning.data_ptr(),
@@ -251,9 +323,10 @@ class GaussianRasterizer(nn.Module):
                                    cov3D_precomp, rs)
 
 
-def rasterizer_state(P, W, H, num_rendered, geom, binning, img):
+def rasterizer_state(P, W, H, num_rendered, geom, binning, img, actual=None):
     """Parity accessor (not in the reference API): the reference-visible contents of the three workspaces --
-    sorted 64-bit keys, point list, tile ranges, n_contrib and the per-Gaussian intermediates -- as tensors."""
+    sorted 64-bit keys, point list, tile ranges, n_contrib and the per-Gaussian intermediates -- as tensors.
+    After a sync-free forward pass the capacity as num_rendered and the real count as `actual`."""
     dev = geom.device
     R = int(num_rendered)
     tiles = ((W + 15) // 16) * ((H + 15) // 16)
@@ -277,4 +350,7 @@ def rasterizer_state(P, W, H, num_rendered, geom, binning, img):
                                      out["conic_opacity"].data_ptr(), out["rgb"].data_ptr(),
                                      out["tiles_touched"].data_ptr(), out["clamped"].data_ptr(),
                                      torch.cuda.current_stream().cuda_stream))
+    if actual is not None:
+        out["keys_sorted"] = out["keys_sorted"][:int(actual)]
+        out["point_list"] = out["point_list"][:int(actual)]
     return out

@@ -30,6 +30,27 @@ def se3_exp(xi: torch.Tensor) -> torch.Tensor:
     return torch.linalg.matrix_exp(A)
 
 
+def se3_exp_closed(xi: torch.Tensor) -> torch.Tensor:
+    """Closed-form SE(3) exponential (Rodrigues) made of element-wise tensor ops only, so it can sit inside a
+    captured CUDA graph (no matrix_exp, no host branch).  Series coefficients take over below 1e-4 rad."""
+    v, w = xi[:3], xi[3:]
+    th2 = (w * w).sum()
+    th = torch.sqrt(th2 + 1e-30)
+    small = th2 < 1e-8
+    A = torch.where(small, 1.0 - th2 / 6.0, torch.sin(th) / th)
+    B = torch.where(small, 0.5 - th2 / 24.0, (1.0 - torch.cos(th)) / (th2 + 1e-30))
+    C = torch.where(small, 1.0 / 6.0 - th2 / 120.0, (th - torch.sin(th)) / (th2 * th + 1e-30))
+    K = hat(w)
+    K2 = K @ K
+    eye = torch.eye(3, dtype=xi.dtype, device=xi.device)
+    R = eye + A * K + B * K2
+    V = eye + B * K + C * K2
+    top = torch.cat([R, (V @ v).unsqueeze(1)], 1)
+    bottom = torch.cat([torch.zeros(1, 3, dtype=xi.dtype, device=xi.device),
+                        torch.ones(1, 1, dtype=xi.dtype, device=xi.device)], 1)   # device fills only: graph-capturable
+    return torch.cat([top, bottom], 0)
+
+
 class _PoseRasterize(torch.autograd.Function):
     """means3D = T[:3,:3] @ xyz + T[:3,3]; gradient w.r.t. the twist `xi` (evaluated at xi = 0) is the fused
     dL_dpose; gradients w.r.t. the Gaussian parameters flow as in the plain rasterizer."""

@@ -124,19 +124,57 @@ def run_pair(p, args, dev, backend):
     T = torch.eye(4, device=dev)
     m = torch.zeros(6, device=dev); v = torch.zeros(6, device=dev)
     lr, b1, b2 = args.pose_lr, 0.9, 0.999
-    torch.cuda.synchronize(dev)
-    t0 = time.time()
-    for it in range(args.pose_iters):
+    if args.graph:
+        # whole pose iteration (render, loss, backward, Adam on the twist, pose retraction) as ONE CUDA graph:
+        # needs the sync-free forward (no host read of num_rendered inside the loop)
         xi = torch.zeros(6, device=dev, requires_grad=True)
-        img = backend["render"](rs, xi, xyz_f, T, opa, **fr)[0]
-        loss = loss_fn(img, frame1, window)
-        loss.backward()
-        g = xi.grad
-        m = b1 * m + (1 - b1) * g; v = b2 * v + (1 - b2) * g * g
-        step = -lr * (m / (1 - b1 ** (it + 1))) / ((v / (1 - b2 ** (it + 1))).sqrt() + 1e-8)
-        T = (GP.se3_exp(step) @ T)
-    torch.cuda.synchronize(dev)
-    pose_s = time.time() - t0
+        t_dev = torch.zeros((), device=dev)
+        b1_dev, b2_dev = torch.full((), b1, device=dev), torch.full((), b2, device=dev)
+
+        def iteration():
+            img = backend["render"](rs, xi, xyz_f, T, opa, **fr)[0]
+            loss = loss_fn(img, frame1, window)
+            loss.backward()
+            g = xi.grad
+            t_dev.add_(1.0)
+            m.mul_(b1).add_(g, alpha=1 - b1)
+            v.mul_(b2).addcmul_(g, g, value=1 - b2)
+            step = -lr * (m / (1 - torch.pow(b1_dev, t_dev))) / ((v / (1 - torch.pow(b2_dev, t_dev))).sqrt() + 1e-8)
+            T.copy_(GP.se3_exp_closed(step) @ T)
+            g.zero_()
+            return loss
+
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(3):
+                iteration()
+        torch.cuda.current_stream().wait_stream(side)
+        T.copy_(torch.eye(4, device=dev)); m.zero_(); v.zero_(); t_dev.zero_(); xi.grad = None
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            loss = iteration()
+        T.copy_(torch.eye(4, device=dev)); m.zero_(); v.zero_(); t_dev.zero_()
+        torch.cuda.synchronize(dev)
+        t0 = time.time()
+        for it in range(args.pose_iters):
+            graph.replay()
+        torch.cuda.synchronize(dev)
+        pose_s = time.time() - t0
+    else:
+        torch.cuda.synchronize(dev)
+        t0 = time.time()
+        for it in range(args.pose_iters):
+            xi = torch.zeros(6, device=dev, requires_grad=True)
+            img = backend["render"](rs, xi, xyz_f, T, opa, **fr)[0]
+            loss = loss_fn(img, frame1, window)
+            loss.backward()
+            g = xi.grad
+            m = b1 * m + (1 - b1) * g; v = b2 * v + (1 - b2) * g * g
+            step = -lr * (m / (1 - b1 ** (it + 1))) / ((v / (1 - b2 ** (it + 1))).sqrt() + 1e-8)
+            T = (GP.se3_exp(step) @ T)
+        torch.cuda.synchronize(dev)
+        pose_s = time.time() - t0
     err_t = float((T[:3, 3] - T_true[:3, 3]).norm())
     err_r = float(torch.acos(((T[:3, :3].t() @ T_true[:3, :3]).trace().clamp(-1, 3) - 1) / 2).abs()) * 180 / math.pi
     return dict(pair=p, P=P, fit_s=fit_s, pose_s=pose_s, fit_loss=fit_loss, pose_loss=float(loss.detach()),
@@ -195,6 +233,9 @@ def main():
     ap.add_argument("--height", type=int, default=540)
     ap.add_argument("--pose-lr", type=float, default=1e-3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--graph", action="store_true",
+                    help="sync-free forward + the pose iteration captured as one CUDA graph (ours only)")
+    ap.add_argument("--sync-free", action="store_true", help="sync-free forward without graph capture (ours only)")
     ap.add_argument("--loss", default=None, choices=["fused", "torch"],
                     help="fused CUDA L1+SSIM (default for --impl ours) or the PyTorch formulation (default for reference)")
     args = ap.parse_args()
@@ -211,6 +252,9 @@ def main():
     torch.cuda.set_device(dev)
     import gsr_parallel as GPar
     backend = make_backend(args.impl, dev)
+    if args.impl == "ours" and (args.graph or args.sync_free):
+        import diff_gaussian_rasterization as D
+        D.set_sync_free(True, slack=1.5)
     run_pair(0, argparse.Namespace(**{**vars(args), "fit_iters": 5, "pose_iters": 5}), dev, backend)   # warm-up
     mine = GPar.shard_pairs(args.pairs, rank, world)
     if world > 1:
@@ -234,7 +278,8 @@ def main():
         err_t, err_r = max(r["err_t"] for r in res), max(r["err_r_deg"] for r in res)
     if rank == 0:
         n_local = len(GPar.shard_pairs(args.pairs, 0, world))
-        line = {"workload": "cf3dgs_local_pair", "impl": args.impl, "loss": args.loss, "n_gpus": world, "pairs": args.pairs, "P": res[0]["P"] if res else 0,
+        line = {"workload": "cf3dgs_local_pair", "impl": args.impl, "loss": args.loss, "graph": bool(args.graph), "sync_free": bool(args.graph or args.sync_free),
+                "n_gpus": world, "pairs": args.pairs, "P": res[0]["P"] if res else 0,
                 "W": args.width, "H": args.height, "fit_iters": args.fit_iters, "pose_iters": args.pose_iters,
                 "wall_s": wall, "pairs_per_s": args.pairs / wall,
                 "pose_opt_iters_per_s": args.pairs * args.pose_iters / (pose_s * world) * world if pose_s > 0 else None,
