@@ -191,6 +191,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="run the end-to-end step eagerly instead of replaying a CUDA graph")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     world, rank, local = dist_setup(args.gpus, init=(args.impl == "ours"))
@@ -304,6 +305,46 @@ def main():
             cam_d[slot].copy_(cam_h, non_blocking=True)
             ready[slot].record(copy_stream)
 
+    # On one GPU the compute of a step (render, L1 loss, backward) is captured once as a CUDA graph per input slot --
+    # the sync-free forward makes that possible -- and replayed; uploads, the loss read-back and the per-step
+    # synchronisation stay outside the graph.  With several ranks (NCCL in the step) and for the reference arm the
+    # step runs eagerly.
+    use_graph = (args.impl == "ours" and world == 1 and not args.no_graph)
+    graphs = [None, None]
+    loss_dev = [torch.zeros((), device=dev) for _ in range(2)]
+    static_leaves = None
+
+    def compute(slot):
+        leaves = static_leaves if static_leaves is not None else {k: v.detach().requires_grad_(True) for k, v in params.items()}
+        if args.impl == "ours":
+            st2 = rs._replace(viewmatrix=view_d[slot], projmatrix=proj_d[slot], campos=cam_d[slot])
+            m2d = torch.zeros_like(leaves["means3D"], requires_grad=True)
+        else:
+            st2, m2d = (view_d[slot], proj_d[slot], cam_d[slot]), None
+        color = render(leaves, m2d, st2)[0]
+        loss = (color - tgt_dev[slot]).abs().mean()
+        loss.backward()
+        loss_dev[slot].copy_(loss.detach())
+        return leaves
+
+    if use_graph:
+        D.set_sync_free(True, slack=1.5)
+        static_leaves = {k: v.detach().clone().requires_grad_(True) for k, v in params.items()}
+        for slot in range(2):                        # real cameras / targets in both slots before anything is rendered
+            tgt_dev[slot].copy_(tgt_host); view_d[slot].copy_(view_h); proj_d[slot].copy_(proj_h); cam_d[slot].copy_(cam_h)
+        compute(0)                                   # learns the binning capacity through the synchronising path
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            compute(0); compute(1)
+        torch.cuda.current_stream().wait_stream(side)
+        for slot in range(2):
+            for v in static_leaves.values():
+                v.grad = None
+            graphs[slot] = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graphs[slot]):
+                compute(slot)
+
     def e2e_step():
         cur = torch.cuda.current_stream()
         slot = counter["i"] & 1
@@ -313,15 +354,10 @@ def main():
             counter["primed"] = True
         upload(slot ^ 1)                      # next step's inputs, overlapped with this step's kernels
         cur.wait_event(ready[slot])
-        leaves = {k: v.detach().requires_grad_(True) for k, v in params.items()}
-        if args.impl == "ours":
-            st2 = rs._replace(viewmatrix=view_d[slot], projmatrix=proj_d[slot], campos=cam_d[slot])
-            m2d = torch.zeros_like(leaves["means3D"], requires_grad=True)
+        if use_graph:
+            graphs[slot].replay()
         else:
-            st2, m2d = (view_d[slot], proj_d[slot], cam_d[slot]), None
-        color = render(leaves, m2d, st2)[0]
-        loss = (color - tgt_dev[slot]).abs().mean()
-        loss.backward()
+            leaves = compute(slot)
         consumed[slot].record(cur)
         if world > 1:
             import torch.distributed as dist
@@ -331,12 +367,19 @@ def main():
                 flat_grad[off:off + g.numel()].copy_(g.reshape(-1))
                 off += g.numel()
             dist.all_reduce(flat_grad)
-        loss_host.copy_(loss.detach().reshape(1), non_blocking=True)
+        loss_host.copy_(loss_dev[slot].reshape(1), non_blocking=True)
         cur.synchronize()   # the caller reads the loss every step
+        if os.environ.get("GSR_BENCH_DEBUG"):
+            print("e2e step", counter["i"], "slot", slot, "loss", float(loss_host[0]), file=sys.stderr)
         counter["i"] += 1
 
     e2e_ms, _ = timed(e2e_step, args.steps, 3, world, dev)
     e2e_value = world * args.steps / (e2e_ms / 1000.0)
+    if use_graph:
+        ovf = D.sync_free_status()
+        D.set_sync_free(False)
+        if ovf is not None and ovf[1]:
+            raise SystemExit("bench: sync-free binning capacity overflowed; the e2e number would be invalid")
 
     if rank != 0:
         return 0
@@ -349,7 +392,8 @@ def main():
             "gaussians_per_s": value * P, "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "what": "per step: camera + target image H2D from pinned memory (double-buffered on a copy stream), "
-                            "L1 loss, backward, loss D2H + sync"}}
+                            "render + L1 loss + backward (" + ("one CUDA graph replay, sync-free forward" if use_graph else "eager") +
+                            "), loss D2H + sync"}}
     if args.impl == "reference":
         line["impl"] = "reference"
         line["gpu_launches"] = 0

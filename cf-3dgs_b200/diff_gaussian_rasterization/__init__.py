@@ -55,6 +55,7 @@ class _SyncFree:
     capacity = {}      # device index -> instances the binning workspace is sized for
     pending = {}       # device index -> (event, pinned status, device status)
     last_status = {}   # device index -> (num_rendered, flags) of the most recent checked call
+    device_status = {}  # device index -> status tensor written by the most recent sync-free forward (also under capture)
 
 
 def set_sync_free(enabled: bool, slack: float = 1.5, capacity: Optional[int] = None, device: Optional[int] = None) -> None:
@@ -69,18 +70,26 @@ def set_sync_free(enabled: bool, slack: float = 1.5, capacity: Optional[int] = N
 
 
 def sync_free_status(device: Optional[int] = None):
-    """(num_rendered, overflowed) of the latest sync-free forward on `device`; synchronises."""
+    """(num_rendered, overflowed) of the latest sync-free forward on `device` -- including one that ran inside a
+    replayed CUDA graph; synchronises.  Call it after graph replays to make sure the capacity was never exceeded."""
     dev = torch.cuda.current_device() if device is None else device
-    p = _SyncFree.pending.get(dev)
-    if p is not None:
+    p = _SyncFree.pending.pop(dev, None)
+    st = _SyncFree.device_status.get(dev)
+    if st is not None:
+        vals = st.cpu()
+        _absorb_values(dev, int(vals[0]), int(vals[1]))
+    elif p is not None:
         p[0].synchronize()
-        _absorb_status(dev)
+        _absorb_values(dev, int(p[1][0]), int(p[1][1]))
     return _SyncFree.last_status.get(dev)
 
 
 def _absorb_status(dev: int) -> None:
     ev, pinned, _ = _SyncFree.pending.pop(dev)
-    R, flags = int(pinned[0]), int(pinned[1])
+    _absorb_values(dev, int(pinned[0]), int(pinned[1]))
+
+
+def _absorb_values(dev: int, R: int, flags: int) -> None:
     _SyncFree.last_status[dev] = (R, bool(flags & 1))
     want = int(R * _SyncFree.slack) + 1024
     if flags & 1:
@@ -163,6 +172,7 @@ def _forward_impl(bg, means3D, colors_precomp, opacities, scales, rotations, sca
                 radii.data_ptr(), geom.data_ptr(), geom.numel(), binning.data_ptr(), binning.numel(), cap,
                 img.data_ptr(), color.data_ptr(), depth.data_ptr(), alpha.data_ptr(), status.data_ptr(), stream,
                 int(bool(debug))))
+            _SyncFree.device_status[di] = status
             if not capturing and di not in _SyncFree.pending:
                 pinned = torch.empty(2, dtype=torch.int64).pin_memory()
                 pinned.copy_(status, non_blocking=True)
