@@ -35,6 +35,9 @@ import torch
 
 WORKLOAD = dict(name="gvol_1M_1080p_sh3", P=1_000_000, W=1920, H=1080, seed=5, sh_degree=3)
 PARAM_KEYS = ["means3D", "opacities", "shs", "scales", "rotations"]
+# DRAM bytes per launch of the kernels that can dominate, from the committed ncu capture of this workload
+NCU_TRAFFIC_BYTES = {"render_backward": 150.8e6 + 18.1e6, "render_forward": 69.3e6 + 31.5e6,
+                     "preprocess": 253.4e6 + 40.2e6, "preprocess_backward": 284.3e6 + 198.6e6}
 
 
 def load_peaks():
@@ -458,7 +461,9 @@ def main():
     d = stages[dom]
     line["roofline"] = {"kernel": dom, "bound": d["bound"], "achieved": d["achieved"],
                         "peak": hbm_peak if d["bound"] == "hbm" else fp32_peak, "unit": d["unit"], "frac": d["frac"],
-                        "traffic": None, "ms": d["ms"],
+                        "traffic": NCU_TRAFFIC_BYTES.get(dom), "ms": d["ms"],
+                        "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full, "
+                                          "profiles/r01_ncu_full_summary.txt (same workload)",
                         "peak_source": (f"{peak_kind} HBM copy" if d["bound"] == "hbm" else
                                         f"derived FP32 FMA peak {n_sm} SMs x 128 lanes x 2 x {sm_mhz:.0f} MHz (median SM clock "
                                         "under load); MEASURED_PEAKS.json holds no FP32 figure")}
