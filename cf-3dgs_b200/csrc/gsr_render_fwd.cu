@@ -37,19 +37,22 @@ render_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges
 
     const uint2 range = ranges[tile];
     const int total = (int)(range.y - range.x);
-    bool done = !inside;
-    float T = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f, weight = 0.f, Dacc = 0.f;
+    // A finished pixel (outside the image, or T*(1-alpha) < 1e-4 reached) is encoded as T = 0: every later entry then
+    // fails the same T test on its own, so the hot loop needs no separate "done" flag or branch.  The transmittance
+    // the pixel ended with is kept in T_out for the background term.
+    float T = inside ? 1.0f : 0.0f, T_out = 1.0f;
+    float C0 = 0.f, C1 = 0.f, C2 = 0.f, weight = 0.f, Dacc = 0.f;
     uint32_t last_contributor = 0;
 
     for (int base = 0; base < total; base += BATCH) {
         // whole tile finished? (also protects the staging buffers of the previous round)
-        if (__syncthreads_count(done) == BLEND_THREADS) break;
+        if (__syncthreads_count(T == 0.f) == BLEND_THREADS) break;
         const int n = min(BATCH, total - base);
         if ((int)threadIdx.x < n) stage_entry(sm, threadIdx.x, point_list[range.x + base + threadIdx.x], g, tile_x0, tile_y0);
         __syncthreads();
 
         for (int c0 = 0; c0 < n; c0 += 32) {
-            if (__all_sync(0xffffffffu, done)) break;
+            if (__all_sync(0xffffffffu, T == 0.f)) break;
             // one lane per entry: can this entry matter anywhere in the warp's footprint?
             const int e = c0 + lane;
             bool keep = false;
@@ -63,10 +66,11 @@ render_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges
                 }
             }
             unsigned live = __ballot_sync(0xffffffffu, keep);
+            const uint32_t pos0 = (uint32_t)(base + c0 + 1);
             while (live) {
-                const int j = c0 + __ffs(live) - 1;
+                const int b = __ffs(live) - 1;
                 live &= live - 1;
-                if (done) continue;
+                const int j = c0 + b;
                 const float4 r0 = sm.rec0[j];
                 const float4 r1 = sm.rec1[j];
                 const float dx = __fadd_rn(r0.x, -pxf), dy = __fadd_rn(r0.y, -pyf);
@@ -76,7 +80,7 @@ render_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges
                 if (alpha < 1.0f / 255.0f) continue;
                 const float test_T = __fmul_rn(T, __fadd_rn(1.f, -alpha));
                 if (test_T < 0.0001f) {
-                    done = true;
+                    if (T != 0.f) { T_out = T; T = 0.f; }   // this pixel is done (forward.cu:352-356)
                     continue;
                 }
                 const float4 r2 = sm.rec2[j];
@@ -86,18 +90,19 @@ render_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges
                 weight = __fmaf_rn(T, alpha, weight);
                 Dacc = __fmaf_rn(T, __fmul_rn(alpha, r2.w), Dacc);
                 T = test_T;
-                last_contributor = (uint32_t)(base + j + 1);
+                last_contributor = pos0 + (uint32_t)b;
             }
         }
     }
 
     if (inside) {
+        const float Tf = (T == 0.f) ? T_out : T;
         const size_t pid = (size_t)W * pix_y + pix_x;
         const size_t plane = (size_t)W * H;
         n_contrib[pid] = last_contributor;
-        out_color[pid] = __fmaf_rn(bg[0], T, C0);
-        out_color[plane + pid] = __fmaf_rn(bg[1], T, C1);
-        out_color[2 * plane + pid] = __fmaf_rn(bg[2], T, C2);
+        out_color[pid] = __fmaf_rn(bg[0], Tf, C0);
+        out_color[plane + pid] = __fmaf_rn(bg[1], Tf, C1);
+        out_color[2 * plane + pid] = __fmaf_rn(bg[2], Tf, C2);
         out_alpha[pid] = weight;
         out_depth[pid] = Dacc;
     }
