@@ -100,17 +100,41 @@ def run_pair(p, args, dev, backend):
     log_s = sc["scales"].to(dev).log().requires_grad_(True)
     rot = sc["rotations"].to(dev).clone().requires_grad_(True)
     opa_raw = torch.full((P, 1), math.log(0.1 / 0.9), device=dev).requires_grad_(True)   # inverse_sigmoid(0.1)
-    opt = torch.optim.Adam([{"params": [xyz], "lr": 0.0}, {"params": [f_dc], "lr": 0.0025}, {"params": [f_rest], "lr": 0.000125},
-                            {"params": [opa_raw], "lr": 0.05}, {"params": [log_s], "lr": 0.005}, {"params": [rot], "lr": 0.001}],
-                           eps=1e-15)
-    torch.cuda.synchronize(dev)
-    t0 = time.time()
-    for it in range(args.fit_iters):
+    groups = [{"params": [xyz], "lr": 0.0}, {"params": [f_dc], "lr": 0.0025}, {"params": [f_rest], "lr": 0.000125},
+              {"params": [opa_raw], "lr": 0.05}, {"params": [log_s], "lr": 0.005}, {"params": [rot], "lr": 0.001}]
+
+    def fit_iteration():
         img = backend["render"](rs, zero6, xyz, eye, torch.sigmoid(opa_raw), shs=torch.cat([f_dc, f_rest], 1),
                                 scales=torch.exp(log_s), rotations=F.normalize(rot))[0]
         loss = loss_fn(img, frame0, window)
         loss.backward()
-        opt.step(); opt.zero_grad(set_to_none=True)
+        return loss
+
+    if args.graph:
+        # one CUDA graph per fit iteration: render, loss, backward, fused multi-tensor Adam
+        opt = torch.optim.Adam(groups, eps=1e-15, capturable=True, fused=True)
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(3):
+                fit_iteration(); opt.step(); opt.zero_grad(set_to_none=True)
+        torch.cuda.current_stream().wait_stream(side)
+        fit_graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(fit_graph):
+            loss = fit_iteration()
+            opt.step()
+            opt.zero_grad(set_to_none=False)
+        torch.cuda.synchronize(dev)
+        t0 = time.time()
+        for it in range(args.fit_iters):
+            fit_graph.replay()
+    else:
+        opt = torch.optim.Adam(groups, eps=1e-15)
+        torch.cuda.synchronize(dev)
+        t0 = time.time()
+        for it in range(args.fit_iters):
+            loss = fit_iteration()
+            opt.step(); opt.zero_grad(set_to_none=True)
     torch.cuda.synchronize(dev)
     fit_s = time.time() - t0
     fit_loss = float(loss.detach())
