@@ -393,7 +393,7 @@ int gsr_debug_dump(int P, int W, int H, int64_t num_rendered, const void* geomet
     BinView b;
     bin_layout((char*)binning, num_rendered, b);
     const int tiles = div_up(W, TILE) * div_up(H, TILE);
-    if (keys_sorted && num_rendered > 0) launch_build_keys(b.keys[0], b.vals[0], g.depth_key, num_rendered, keys_sorted, s);
+    if (keys_sorted && num_rendered > 0) launch_build_keys(b.keys[0], b.vals[0], g.depth_key, num_rendered, g.counters, keys_sorted, s);
     if (point_list && num_rendered > 0)
         cudaMemcpyAsync(point_list, b.vals[0], sizeof(uint32_t) * (size_t)num_rendered, cudaMemcpyDeviceToDevice, s);
     if (ranges) cudaMemcpyAsync(ranges, iv.ranges, sizeof(uint2) * (size_t)tiles, cudaMemcpyDeviceToDevice, s);

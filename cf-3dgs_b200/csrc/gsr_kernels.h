@@ -43,7 +43,7 @@ void launch_tile_ranges(const uint32_t* sorted_tiles, int64_t R, uint2* ranges, 
                         const unsigned long long* n_dev = nullptr);
 void launch_publish_status(const unsigned long long* counters, int64_t cap, long long* status, cudaStream_t s);
 void launch_build_keys(const uint32_t* sorted_tiles, const uint32_t* point_list, const uint32_t* depth_key,
-                       int64_t R, uint64_t* keys_out, cudaStream_t s);
+                       int64_t R, const unsigned long long* n_dev, uint64_t* keys_out, cudaStream_t s);
 
 void launch_render_forward(int W, int H, const uint2* ranges, const uint32_t* point_list, const GeomView& g,
                            const float* bg, float* out_color, float* out_depth, float* out_alpha,

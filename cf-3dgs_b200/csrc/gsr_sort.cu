@@ -513,16 +513,20 @@ void launch_publish_status(const unsigned long long* counters, int64_t cap, long
 }
 
 __global__ void build_keys_kernel(const uint32_t* __restrict__ sorted_tiles, const uint32_t* __restrict__ point_list,
-                                  const uint32_t* __restrict__ depth_key, int64_t R, uint64_t* __restrict__ keys_out)
+                                  const uint32_t* __restrict__ depth_key, int64_t R_cap,
+                                  const unsigned long long* __restrict__ n_dev, uint64_t* __restrict__ keys_out)
 {
+    // after a sync-free forward only the first (device-side) count entries of the lists are defined
+    const int64_t R = device_count(n_dev, R_cap);
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < R) keys_out[i] = ((uint64_t)sorted_tiles[i] << 32) | depth_key[point_list[i]];
+    else if (i < R_cap) keys_out[i] = 0;
 }
 
 void launch_build_keys(const uint32_t* sorted_tiles, const uint32_t* point_list, const uint32_t* depth_key,
-                       int64_t R, uint64_t* keys_out, cudaStream_t s)
+                       int64_t R, const unsigned long long* n_dev, uint64_t* keys_out, cudaStream_t s)
 {
-    if (R > 0) build_keys_kernel<<<div_up(R, 256), 256, 0, s>>>(sorted_tiles, point_list, depth_key, R, keys_out);
+    if (R > 0) build_keys_kernel<<<div_up(R, 256), 256, 0, s>>>(sorted_tiles, point_list, depth_key, R, n_dev, keys_out);
 }
 
 }  // namespace gsr

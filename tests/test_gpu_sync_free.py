@@ -111,3 +111,28 @@ def test_whole_step_can_be_captured_in_a_cuda_graph():
     g.replay()
     torch.cuda.synchronize()
     assert not torch.equal(color.detach(), ref[0])
+
+
+def test_state_dump_after_sync_free_forward_matches_the_synchronising_path():
+    """The binning workspace is sized for the capacity; only the first num_rendered entries are defined."""
+    import diff_gaussian_rasterization as D
+    from helpers import cuda_forward
+    cam = S.second_view(200, 120)
+    sc = S.make_gvol(6000, 200, 120, seed=85, s0=0.02)
+    ref, _, _ = cuda_forward(sc, cam, (0, 0, 0))
+    D.set_sync_free(True, slack=2.0)
+    cuda_forward(sc, cam, (0, 0, 0))                     # learns the capacity
+    import torch as _t
+    leaves = {k: sc[k].to(DEV) for k in ["means3D", "opacities", "shs", "scales", "rotations"]}
+    rs = cuda_settings(D, cam, (0, 0, 0), 3, DEV)
+    e = _t.Tensor([])
+    cap, color, depth, alpha, radii, geom, binning, img = D._forward_impl(
+        rs.bg, leaves["means3D"], e, leaves["opacities"], leaves["scales"], leaves["rotations"], 1.0, e, rs.viewmatrix,
+        rs.projmatrix, rs.tanfovx, rs.tanfovy, 120, 200, leaves["shs"], 3, rs.campos, False, False)
+    R, overflow = D.sync_free_status()
+    assert not overflow and R == ref["num_rendered"] and cap > R
+    st = D.rasterizer_state(6000, 200, 120, cap, geom, binning, img, actual=R)
+    assert _t.equal(st["keys_sorted"], ref["state"]["keys_sorted"])
+    assert _t.equal(st["point_list"], ref["state"]["point_list"])
+    assert _t.equal(st["ranges"], ref["state"]["ranges"])
+    assert _t.equal(color, ref["color"].detach())
