@@ -441,34 +441,61 @@ void launch_offsets_scan(const uint32_t* tiles, const uint32_t* order, uint32_t*
 }
 
 // ---------------------------------------------------------------------------------------------
-// Instance emit in depth order (reference duplicateWithKeys, rasterizer_impl.cu:70-111, which emits in
-// Gaussian order).  key = tile id only; the depth half of the reference key is implied by the order.
-__global__ void emit_kernel(const uint32_t* __restrict__ order, const uint32_t* __restrict__ tiles,
-                            const uint32_t* __restrict__ offsets, const uint2* __restrict__ rect, int P, int grid_x,
-                            uint32_t* __restrict__ tile_keys, uint32_t* __restrict__ tile_vals, uint32_t cap)
+// Instance emit in depth order (reference duplicateWithKeys, rasterizer_impl.cu:70-111, which emits in Gaussian
+// order with one thread looping over each Gaussian's tiles).  key = tile id only; the depth half of the reference key
+// is implied by the order.  Load-balanced: a block owns 256 consecutive depth ranks, whose instances form ONE
+// contiguous output range; its threads walk that range with stride 256 and find the owning Gaussian of each slot by
+// binary search over the block's 257 offsets in shared memory, so every store is coalesced and a splat covering
+// hundreds of tiles costs no more per instance than one covering four.
+constexpr int EMIT_THREADS = 256;
+
+__global__ void __launch_bounds__(EMIT_THREADS)
+emit_kernel(const uint32_t* __restrict__ order, const uint32_t* __restrict__ tiles,
+            const uint32_t* __restrict__ offsets, const uint2* __restrict__ rect, int P, int grid_x,
+            uint32_t* __restrict__ tile_keys, uint32_t* __restrict__ tile_vals, uint32_t cap)
 {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= P) return;
-    const uint32_t gid = order[i];
-    if (tiles[gid] == 0) return;
-    uint32_t off = offsets[i];
-    const uint2 r = rect[gid];
-    const uint32_t x0 = r.x & 0xffffu, x1 = r.x >> 16, y0 = r.y & 0xffffu, y1 = r.y >> 16;
-    for (uint32_t y = y0; y < y1; y++)
-        for (uint32_t x = x0; x < x1; x++) {
-            if (off < cap) {   // only the sync-free path can run out of room; it raises the overflow flag elsewhere
-                tile_keys[off] = y * (uint32_t)grid_x + x;
-                tile_vals[off] = gid;
-            }
-            off++;
+    __shared__ uint32_t s_off[EMIT_THREADS + 1];
+    __shared__ uint32_t s_gid[EMIT_THREADS];
+    __shared__ uint2 s_rect[EMIT_THREADS];
+    const int r = blockIdx.x * EMIT_THREADS + threadIdx.x;
+    uint32_t off = 0xffffffffu, gid = 0, n = 0;
+    uint2 rc = make_uint2(0u, 0u);
+    if (r < P) {
+        gid = order[r];
+        off = offsets[r];
+        n = tiles[gid];
+        rc = rect[gid];
+    }
+    s_off[threadIdx.x] = off;
+    s_gid[threadIdx.x] = gid;
+    s_rect[threadIdx.x] = rc;
+    // end of the block's range = offset + count of its last valid rank
+    const int last = min(EMIT_THREADS, P - blockIdx.x * EMIT_THREADS) - 1;
+    if ((int)threadIdx.x == last) s_off[EMIT_THREADS] = off + n;
+    __syncthreads();
+    const uint32_t begin = s_off[0];
+    const uint32_t end = min(s_off[EMIT_THREADS], cap);   // cap: only the sync-free path can run out of room
+    for (uint32_t p = begin + threadIdx.x; p < end; p += EMIT_THREADS) {
+        // last k in [0, last] with s_off[k] <= p
+        int lo = 0, hi = last;
+        while (lo < hi) {
+            const int mid = (lo + hi + 1) >> 1;
+            if (s_off[mid] <= p) lo = mid; else hi = mid - 1;
         }
+        const uint2 q = s_rect[lo];
+        const uint32_t x0 = q.x & 0xffffu, x1 = q.x >> 16, y0 = q.y & 0xffffu;
+        const uint32_t local = p - s_off[lo], w = x1 - x0;
+        const uint32_t row = local / w, col = local - row * w;
+        tile_keys[p] = (y0 + row) * (uint32_t)grid_x + x0 + col;
+        tile_vals[p] = s_gid[lo];
+    }
 }
 
 void launch_emit(const GeomView& g, const uint32_t* order, int P, int grid_x, uint32_t* tile_keys,
                  uint32_t* tile_vals, int64_t cap, cudaStream_t s)
 {
-    emit_kernel<<<div_up(P, 256), 256, 0, s>>>(order, g.tiles, g.offsets, g.rect, P, grid_x, tile_keys, tile_vals,
-                                               (uint32_t)cap);
+    emit_kernel<<<div_up(P, EMIT_THREADS), EMIT_THREADS, 0, s>>>(order, g.tiles, g.offsets, g.rect, P, grid_x, tile_keys,
+                                                                 tile_vals, (uint32_t)cap);
 }
 
 // ---------------------------------------------------------------------------------------------
