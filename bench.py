@@ -5,8 +5,10 @@ Metric (BASELINE.json): forward+backward rendered frames/s at 1920x1080.
 Workload at N=1: `gvol_1M_1080p_sh3` -- synthetic G-vol scene, 1,000,000 Gaussians, SH degree 3,
 one fwd+bwd rasterization per step through the reference-shaped API (GaussianRasterizer autograd Function ->
 C ABI -> sm_100a kernels), colour cotangent only (CF-3DGS default: depth/alpha losses off).
-N>1: every rank holds a replica of the scene, renders its own view, then the flat 59-float/Gaussian gradient is
-summed with one NCCL all-reduce; weak scaling, value = N * frames / max-over-ranks time.
+N>1 (one process per GPU, weak scaling): `value` is the sharded form north_star asks near-linear scaling of -- independent
+frame pairs, every rank renders its own view of its own model replica with NO data-path collective (SURVEY.md 8e (i));
+value = N * frames / max-over-ranks time.  The same run also times the batched-views form (8e (ii)): the same step
+followed by one NCCL all-reduce of the flat 59-float/Gaussian gradient, reported as `allreduce_variant`.
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
 
@@ -281,8 +283,12 @@ def main():
         state["leaves"] = leaves
 
     # ---- device-resident throughput ----
-    ms, clocks = timed(step, args.steps, args.warmup, world, dev, clock_index=local if rank == 0 else None)
+    ms, clocks = timed(lambda: step(comm=False), args.steps, args.warmup, world, dev,
+                       clock_index=local if rank == 0 else None)
     value = world * args.steps / (ms / 1000.0)
+    ar_ms = None
+    if world > 1:   # batched views + gradient all-reduce, same step plus the collective
+        ar_ms, _ = timed(lambda: step(comm=True), args.steps, 3, world, dev)
 
     # ---- end to end: per step the camera + target image come from pinned host memory, the loss goes back ----
     tgt_host = torch.rand(3, H, W).pin_memory()
@@ -308,11 +314,10 @@ def main():
             cam_d[slot].copy_(cam_h, non_blocking=True)
             ready[slot].record(copy_stream)
 
-    # On one GPU the compute of a step (render, L1 loss, backward) is captured once as a CUDA graph per input slot --
-    # the sync-free forward makes that possible -- and replayed; uploads, the loss read-back and the per-step
-    # synchronisation stay outside the graph.  With several ranks (NCCL in the step) and for the reference arm the
-    # step runs eagerly.
-    use_graph = (args.impl == "ours" and world == 1 and not args.no_graph)
+    # The compute of a step (render, L1 loss, backward) is captured once as a CUDA graph per input slot -- the sync-free
+    # forward makes that possible -- and replayed; uploads, the loss read-back and the per-step synchronisation stay
+    # outside the graph.  The reference arm runs eagerly (it synchronises inside its forward).
+    use_graph = (args.impl == "ours" and not args.no_graph)
     graphs = [None, None]
     loss_dev = [torch.zeros((), device=dev) for _ in range(2)]
     static_leaves = None
@@ -362,14 +367,6 @@ def main():
         else:
             leaves = compute(slot)
         consumed[slot].record(cur)
-        if world > 1:
-            import torch.distributed as dist
-            off = 0
-            for k in PARAM_KEYS:
-                g = leaves[k].grad
-                flat_grad[off:off + g.numel()].copy_(g.reshape(-1))
-                off += g.numel()
-            dist.all_reduce(flat_grad)
         loss_host.copy_(loss_dev[slot].reshape(1), non_blocking=True)
         cur.synchronize()   # the caller reads the loss every step
         if os.environ.get("GSR_BENCH_DEBUG"):
@@ -390,13 +387,18 @@ def main():
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": wl["name"], "P": P, "W": W, "H": H, "sh_degree": wl["sh_degree"],
-                       "cotangents": "colour only (CF-3DGS default)", "parallelism": f"dp{world}",
+                       "cotangents": "colour only (CF-3DGS default)", "parallelism": f"dp{world}: independent frame pairs per rank, no data-path collective" if world > 1 else "dp1",
                        "l2": "per-step working set ~0.9 GB > 126 MB L2, no explicit flush"},
             "gaussians_per_s": value * P, "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "what": "per step: camera + target image H2D from pinned memory (double-buffered on a copy stream), "
                             "render + L1 loss + backward (" + ("one CUDA graph replay, sync-free forward" if use_graph else "eager") +
                             "), loss D2H + sync"}}
+    if ar_ms is not None:
+        line["allreduce_variant"] = {"what": "same step + one NCCL all-reduce(sum) of the flat 59-float/Gaussian gradient "
+                                             "(batched global views, SURVEY 8e (ii))",
+                                     "value": world * args.steps / (ar_ms / 1000.0), "unit": "frames/s",
+                                     "ms_per_step": ar_ms / args.steps, "allreduce_bytes": P * 59 * 4}
     if args.impl == "reference":
         line["impl"] = "reference"
         line["gpu_launches"] = 0

@@ -6,7 +6,10 @@
 namespace gsr {
 
 constexpr int BLEND_THREADS = 256;  // one 16x16 tile per CTA, 8 warps
-constexpr int BATCH = 256;          // tile-list entries staged per round
+#ifndef GSR_FWD_BATCH
+#define GSR_FWD_BATCH 256
+#endif
+constexpr int BATCH = GSR_FWD_BATCH;  // tile-list entries staged per round (forward)
 // each warp owns an 8x4 pixel footprint of the tile (tighter than the reference's 16x2 strip, which makes
 // the per-warp rejection test below bite more often)
 constexpr int FOOT_W = 8, FOOT_H = 4;
