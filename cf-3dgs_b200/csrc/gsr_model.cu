@@ -1,0 +1,206 @@
+// Fused Gaussian-model step: the per-iteration PyTorch work around the rasterizer in a
+// CF-3DGS training step, as three kernels.
+//   gaussian_activate : opacity = sigmoid(raw), scale = exp(raw), rotation = raw / max(|raw|, 1e-12)
+//                       (scene/gaussian_model_cf.py:41-56,115-172: the activations behind get_opacity / get_scaling /
+//                       get_rotation)
+//   adam_features     : Adam on the (P, M, 3) SH tensor, one thread per float (perfectly coalesced); coefficient 0 uses
+//                       the f_dc learning rate, the rest the f_rest rate (gaussian_model_cf.py:254-266)
+//   adam_gaussians    : per Gaussian: chain rule through the three activations (the gradients arriving from the
+//                       rasterizer are w.r.t. the ACTIVATED values), Adam on xyz / opacity / scaling / rotation, and
+//                       the densification statistics of add_densification_stats + max_radii2D
+//                       (gaussian_model_cf.py:716-719, trainer/cf3dgs_trainer.py:147-152)
+// Adam follows torch.optim.Adam (no amsgrad, no weight decay): m = b1 m + (1-b1) g;  v = b2 v + (1-b2) g^2;
+//   p -= (lr / (1 - b1^t)) * m / (sqrt(v) / sqrt(1 - b2^t) + eps).
+#include <cmath>
+
+#include "../../include/gsr.h"
+#include "gsr_kernels.h"
+
+namespace gsr {
+void set_last_error(const char* msg);
+
+namespace {
+
+struct AdamCfg {
+    float b1, b2, eps;
+    float inv_bias1;       // 1 / (1 - b1^t)
+    float inv_sqrt_bias2;  // 1 / sqrt(1 - b2^t)
+};
+
+__device__ __forceinline__ float adam_update(float p, float g, float& m, float& v, float lr, const AdamCfg& c)
+{
+    m = c.b1 * m + (1.f - c.b1) * g;
+    v = c.b2 * v + (1.f - c.b2) * g * g;
+    const float denom = sqrtf(v) * c.inv_sqrt_bias2 + c.eps;
+    return p - (lr * c.inv_bias1) * (m / denom);
+}
+
+__global__ void gaussian_activate_kernel(int P, const float* __restrict__ opacity_raw, const float* __restrict__ log_scale,
+                                         const float* __restrict__ rot_raw, float* __restrict__ opacity,
+                                         float* __restrict__ scale, float* __restrict__ rot)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    opacity[i] = 1.f / (1.f + expf(-opacity_raw[i]));
+    scale[3 * i] = expf(log_scale[3 * i]);
+    scale[3 * i + 1] = expf(log_scale[3 * i + 1]);
+    scale[3 * i + 2] = expf(log_scale[3 * i + 2]);
+    const float4 q = reinterpret_cast<const float4*>(rot_raw)[i];
+    const float n = fmaxf(sqrtf(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w), 1e-12f);
+    reinterpret_cast<float4*>(rot)[i] = make_float4(q.x / n, q.y / n, q.z / n, q.w / n);
+}
+
+__global__ void adam_features_kernel(size_t n, int floats_per_gaussian, float* __restrict__ p, const float* __restrict__ g,
+                                     float* __restrict__ m, float* __restrict__ v, float lr_dc, float lr_rest, AdamCfg c)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int k = (int)(i % (size_t)floats_per_gaussian);
+    float mm = m[i], vv = v[i];
+    p[i] = adam_update(p[i], g[i], mm, vv, k < 3 ? lr_dc : lr_rest, c);
+    m[i] = mm; v[i] = vv;
+}
+
+struct GaussianStepArgs {
+    int P;
+    float *xyz, *opacity_raw, *log_scale, *rot_raw;                 // parameters (updated in place)
+    const float *d_xyz, *d_opacity, *d_scale, *d_rot;               // gradients w.r.t. xyz and the ACTIVATED values
+    float *m_xyz, *v_xyz, *m_op, *v_op, *m_sc, *v_sc, *m_rot, *v_rot;
+    float lr_xyz, lr_op, lr_sc, lr_rot;
+    const float* d_means2D;   // optional (P,3)
+    const int* radii;         // optional
+    float *grad_accum, *denom, *max_radii2D;   // optional (P)
+};
+
+__global__ void adam_gaussians_kernel(GaussianStepArgs a, AdamCfg c)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= a.P) return;
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        const int j = 3 * i + k;
+        float mm = a.m_xyz[j], vv = a.v_xyz[j];
+        a.xyz[j] = adam_update(a.xyz[j], a.d_xyz[j], mm, vv, a.lr_xyz, c);
+        a.m_xyz[j] = mm; a.v_xyz[j] = vv;
+    }
+    {   // opacity = sigmoid(raw): d raw = d o * o (1 - o)
+        const float raw = a.opacity_raw[i];
+        const float o = 1.f / (1.f + expf(-raw));
+        const float g = a.d_opacity[i] * o * (1.f - o);
+        float mm = a.m_op[i], vv = a.v_op[i];
+        a.opacity_raw[i] = adam_update(raw, g, mm, vv, a.lr_op, c);
+        a.m_op[i] = mm; a.v_op[i] = vv;
+    }
+#pragma unroll
+    for (int k = 0; k < 3; k++) {   // scale = exp(raw): d raw = d s * s
+        const int j = 3 * i + k;
+        const float raw = a.log_scale[j];
+        const float g = a.d_scale[j] * expf(raw);
+        float mm = a.m_sc[j], vv = a.v_sc[j];
+        a.log_scale[j] = adam_update(raw, g, mm, vv, a.lr_sc, c);
+        a.m_sc[j] = mm; a.v_sc[j] = vv;
+    }
+    {   // rotation = q / max(|q|, eps): d q = (g - y (y . g)) / n
+        const float4 q = reinterpret_cast<const float4*>(a.rot_raw)[i];
+        const float4 gy = reinterpret_cast<const float4*>(a.d_rot)[i];
+        const float n2 = q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w;
+        const float n = sqrtf(n2);
+        float4 g;
+        if (n > 1e-12f) {
+            const float inv = 1.f / n;
+            const float4 y = make_float4(q.x * inv, q.y * inv, q.z * inv, q.w * inv);
+            const float d = y.x * gy.x + y.y * gy.y + y.z * gy.z + y.w * gy.w;
+            g = make_float4((gy.x - y.x * d) * inv, (gy.y - y.y * d) * inv, (gy.z - y.z * d) * inv, (gy.w - y.w * d) * inv);
+        } else {
+            g = make_float4(gy.x * 1e12f, gy.y * 1e12f, gy.z * 1e12f, gy.w * 1e12f);
+        }
+        float4 mm = reinterpret_cast<float4*>(a.m_rot)[i], vv = reinterpret_cast<float4*>(a.v_rot)[i];
+        float4 o;
+        o.x = adam_update(q.x, g.x, mm.x, vv.x, a.lr_rot, c);
+        o.y = adam_update(q.y, g.y, mm.y, vv.y, a.lr_rot, c);
+        o.z = adam_update(q.z, g.z, mm.z, vv.z, a.lr_rot, c);
+        o.w = adam_update(q.w, g.w, mm.w, vv.w, a.lr_rot, c);
+        reinterpret_cast<float4*>(a.rot_raw)[i] = o;
+        reinterpret_cast<float4*>(a.m_rot)[i] = mm;
+        reinterpret_cast<float4*>(a.v_rot)[i] = vv;
+    }
+    if (a.radii && a.grad_accum) {   // densification statistics for Gaussians visible in this view
+        const int r = a.radii[i];
+        if (r > 0) {
+            const float gx = a.d_means2D[3 * i], gy2 = a.d_means2D[3 * i + 1];
+            a.grad_accum[i] += sqrtf(gx * gx + gy2 * gy2);
+            a.denom[i] += 1.f;
+            if (a.max_radii2D) a.max_radii2D[i] = fmaxf(a.max_radii2D[i], (float)r);
+        }
+    }
+}
+
+}  // namespace
+}  // namespace gsr
+
+using namespace gsr;
+
+extern "C" int gsr_gaussian_activate(int P, const float* opacity_raw, const float* log_scale, const float* rot_raw,
+                                     float* opacity, float* scale, float* rot, void* stream)
+{
+    if (P < 0 || (P > 0 && (!opacity_raw || !log_scale || !rot_raw || !opacity || !scale || !rot))) {
+        set_last_error("gsr_gaussian_activate: bad argument");
+        return GSR_ERR_INVALID;
+    }
+    if (P == 0) return GSR_OK;
+    gaussian_activate_kernel<<<div_up(P, 256), 256, 0, (cudaStream_t)stream>>>(P, opacity_raw, log_scale, rot_raw, opacity,
+                                                                             scale, rot);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { set_last_error(cudaGetErrorString(e)); return GSR_ERR_CUDA; }
+    return GSR_OK;
+}
+
+extern "C" int gsr_gaussian_adam_step(int P, int M, int step, float beta1, float beta2, float eps, const float* lrs_host,
+                                      float* xyz, float* features, float* opacity_raw, float* log_scale, float* rot_raw,
+                                      const float* d_xyz, const float* d_features, const float* d_opacity,
+                                      const float* d_scale, const float* d_rot, float* state, const float* d_means2D,
+                                      const int* radii, float* grad_accum, float* denom, float* max_radii2D, void* stream)
+{
+    cudaStream_t s = (cudaStream_t)stream;
+    if (P < 0 || M < 0 || step < 1 || !lrs_host) { set_last_error("gsr_gaussian_adam_step: bad argument"); return GSR_ERR_INVALID; }
+    if (P == 0) return GSR_OK;
+    if (!xyz || !opacity_raw || !log_scale || !rot_raw || !d_xyz || !d_opacity || !d_scale || !d_rot || !state ||
+        (M > 0 && (!features || !d_features))) {
+        set_last_error("gsr_gaussian_adam_step: required pointer is NULL");
+        return GSR_ERR_INVALID;
+    }
+    AdamCfg c;
+    c.b1 = beta1; c.b2 = beta2; c.eps = eps;
+    c.inv_bias1 = (float)(1.0 / (1.0 - std::pow((double)beta1, (double)step)));
+    c.inv_sqrt_bias2 = (float)(1.0 / std::sqrt(1.0 - std::pow((double)beta2, (double)step)));
+    // state layout: [m | v] for xyz(3P) opacity(P) scale(3P) rot(4P) features(3MP), in that order
+    const size_t n = (size_t)P;
+    float* st = state;
+    GaussianStepArgs a;
+    a.P = P;
+    a.xyz = xyz; a.opacity_raw = opacity_raw; a.log_scale = log_scale; a.rot_raw = rot_raw;
+    a.d_xyz = d_xyz; a.d_opacity = d_opacity; a.d_scale = d_scale; a.d_rot = d_rot;
+    a.m_xyz = st; st += 3 * n; a.v_xyz = st; st += 3 * n;
+    a.m_op = st; st += n; a.v_op = st; st += n;
+    a.m_sc = st; st += 3 * n; a.v_sc = st; st += 3 * n;
+    a.m_rot = st; st += 4 * n; a.v_rot = st; st += 4 * n;
+    float* m_f = st; st += 3 * (size_t)M * n;
+    float* v_f = st;
+    a.lr_xyz = lrs_host[0]; a.lr_op = lrs_host[3]; a.lr_sc = lrs_host[4]; a.lr_rot = lrs_host[5];
+    a.d_means2D = d_means2D; a.radii = radii; a.grad_accum = (d_means2D && radii && denom) ? grad_accum : nullptr;
+    a.denom = denom; a.max_radii2D = max_radii2D;
+    adam_gaussians_kernel<<<div_up(P, 256), 256, 0, s>>>(a, c);
+    if (M > 0) {
+        const size_t nf = (size_t)3 * M * n;
+        adam_features_kernel<<<(unsigned)((nf + 255) / 256), 256, 0, s>>>(nf, 3 * M, features, d_features, m_f, v_f, lrs_host[1],
+                                                                      lrs_host[2], c);
+    }
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { set_last_error(cudaGetErrorString(e)); return GSR_ERR_CUDA; }
+    return GSR_OK;
+}
+
+extern "C" size_t gsr_gaussian_adam_state_floats(int P, int M)
+{
+    return (size_t)2 * ((size_t)3 + 1 + 3 + 4 + (size_t)3 * M) * (size_t)(P > 0 ? P : 0);
+}

@@ -34,6 +34,10 @@ SIGNATURES = {
     "gsr_photo_loss_scratch_bytes": (c_size_t, [c_int, c_int, c_int]),
     "gsr_photo_loss_forward": (c_int, [c_int, c_int, c_int, _P, _P, c_float, c_int, _P, _P, _P]),
     "gsr_photo_loss_backward": (c_int, [c_int, c_int, c_int, _P, _P, c_float, c_int, _P, _P, _P, _P]),
+    "gsr_gaussian_activate": (c_int, [c_int, _P, _P, _P, _P, _P, _P, _P]),
+    "gsr_gaussian_adam_state_floats": (c_size_t, [c_int, c_int]),
+    "gsr_gaussian_adam_step": (c_int, [c_int, c_int, c_int, c_float, c_float, c_float, _P, _P, _P, _P, _P, _P, _P, _P, _P,
+                                       _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "gsr_mark_visible": (c_int, [c_int, _P, _P, _P, _P, _P]),
     "gsr_debug_dump": (c_int, [c_int, c_int, c_int, c_int64, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "gsr_profile_enable": (c_int, [c_int]),

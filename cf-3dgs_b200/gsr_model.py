@@ -1,0 +1,65 @@
+"""Fused Gaussian-model step: activations, their backward, Adam and densification statistics as CUDA kernels
+(reference: scene/gaussian_model_cf.py:41-56,115-172,242-268,716-719).
+
+The reference keeps six parameter tensors in a torch.optim.Adam with per-group learning rates and lets autograd run
+sigmoid / exp / normalize / cat forward and backward around every rasterizer call.  FusedGaussianModel keeps the same
+raw parameters (features as ONE (P,M,3) tensor, so no cat), produces the activated tensors the rasterizer wants with one
+kernel, and applies the whole update -- chain rule through the activations + Adam + statistics -- with two more.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Dict, Optional
+
+import torch
+
+from diff_gaussian_rasterization._cabi import check, lib
+
+LR_ORDER = ("xyz", "f_dc", "f_rest", "opacity", "scaling", "rotation")
+
+
+class FusedGaussianModel:
+    def __init__(self, xyz, features, opacity_raw, log_scales, rot_raw, lrs: Dict[str, float], betas=(0.9, 0.999),
+                 eps: float = 1e-15):
+        self.xyz = xyz.detach().contiguous().float().clone()
+        self.features = features.detach().contiguous().float().clone()        # (P, M, 3), coefficient 0 = f_dc
+        self.opacity_raw = opacity_raw.detach().contiguous().float().clone()  # (P, 1)
+        self.log_scales = log_scales.detach().contiguous().float().clone()    # (P, 3)
+        self.rot_raw = rot_raw.detach().contiguous().float().clone()          # (P, 4)
+        dev = self.xyz.device
+        self.P, self.M = self.xyz.shape[0], self.features.shape[1]
+        self.lrs = dict(lrs)
+        self.betas, self.eps, self.step_count = betas, eps, 0
+        self.state = torch.zeros(lib.gsr_gaussian_adam_state_floats(self.P, self.M), dtype=torch.float32, device=dev)
+        self.xyz_gradient_accum = torch.zeros(self.P, device=dev)
+        self.denom = torch.zeros(self.P, device=dev)
+        self.max_radii2D = torch.zeros(self.P, device=dev)
+        self._act = None
+
+    def activated(self) -> Dict[str, torch.Tensor]:
+        """opacities (P,1), scales (P,3), rotations (P,4) for the rasterizer (fresh tensors, no autograd history)."""
+        dev = self.xyz.device
+        opa = torch.empty((self.P, 1), device=dev)
+        sc = torch.empty((self.P, 3), device=dev)
+        rot = torch.empty((self.P, 4), device=dev)
+        with torch.cuda.device(dev):
+            check(lib.gsr_gaussian_activate(self.P, self.opacity_raw.data_ptr(), self.log_scales.data_ptr(),
+                                            self.rot_raw.data_ptr(), opa.data_ptr(), sc.data_ptr(), rot.data_ptr(),
+                                            torch.cuda.current_stream().cuda_stream))
+        return dict(opacities=opa, scales=sc, rotations=rot)
+
+    def step(self, d_xyz, d_features, d_opacities, d_scales, d_rotations, d_means2D: Optional[torch.Tensor] = None,
+             radii: Optional[torch.Tensor] = None) -> None:
+        """One optimiser step from the gradients the rasterizer backward produced (w.r.t. the activated tensors)."""
+        self.step_count += 1
+        lr = (ctypes.c_float * 6)(*[float(self.lrs[k]) for k in LR_ORDER])
+        stats = d_means2D is not None and radii is not None
+        p = lambda t: None if t is None else t.contiguous().data_ptr()
+        with torch.cuda.device(self.xyz.device):
+            check(lib.gsr_gaussian_adam_step(
+                self.P, self.M, self.step_count, float(self.betas[0]), float(self.betas[1]), float(self.eps), lr,
+                self.xyz.data_ptr(), self.features.data_ptr(), self.opacity_raw.data_ptr(), self.log_scales.data_ptr(),
+                self.rot_raw.data_ptr(), p(d_xyz), p(d_features), p(d_opacities), p(d_scales), p(d_rotations),
+                self.state.data_ptr(), p(d_means2D) if stats else None, p(radii) if stats else None,
+                self.xyz_gradient_accum.data_ptr() if stats else None, self.denom.data_ptr() if stats else None,
+                self.max_radii2D.data_ptr() if stats else None, torch.cuda.current_stream().cuda_stream))

@@ -48,7 +48,11 @@ def main():
     ap.add_argument("--sh-degree", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--loss", default=None, choices=["fused", "torch"])
+    ap.add_argument("--model", default=None, choices=["fused", "torch"],
+                    help="fused activation/Adam/statistics kernels (default for ours) or torch.optim.Adam + autograd")
     args = ap.parse_args()
+    if args.model is None:
+        args.model = "fused" if args.impl == "ours" else "torch"
     if args.loss is None:
         args.loss = "fused" if args.impl == "ours" else "torch"
     real_stdout = os.dup(1); os.dup2(2, 1)
@@ -93,7 +97,31 @@ def main():
     settings = [backend["settings"](c, args.sh_degree) for c in cams]
     order = np.random.RandomState(0).randint(0, args.frames, size=args.iters + 10)
 
+    fused_model = None
+    if args.model == "fused":
+        import gsr_model
+        fused_model = gsr_model.FusedGaussianModel(
+            xyz, torch.cat([f_dc, f_rest], 1), opa_raw, log_s, rot,
+            dict(xyz=0.00016, f_dc=0.0025, f_rest=0.000125, opacity=0.05, scaling=0.005, rotation=0.001))
+
+    def fused_iteration(k):
+        f = int(order[k])
+        m = fused_model
+        act = m.activated()
+        x = m.xyz.detach().requires_grad_(True)
+        sh = m.features.detach().requires_grad_(True)
+        o, sc, r = act["opacities"].requires_grad_(True), act["scales"].requires_grad_(True), act["rotations"].requires_grad_(True)
+        m2d = torch.zeros_like(x, requires_grad=True)
+        import diff_gaussian_rasterization as D
+        img, radii, _, _ = D.GaussianRasterizer(settings[f])(x, m2d, o, shs=sh, scales=sc, rotations=r)
+        loss = loss_fn(img, targets[f], window)
+        loss.backward()
+        m.step(x.grad, sh.grad, o.grad, sc.grad, r.grad, d_means2D=m2d.grad, radii=radii)
+        return loss
+
     def iteration(k):
+        if fused_model is not None:
+            return fused_iteration(k)
         f = int(order[k])
         img = backend["render"](settings[f], zero6, xyz, eye, torch.sigmoid(opa_raw), shs=torch.cat([f_dc, f_rest], 1),
                                 scales=torch.exp(log_s), rotations=F.normalize(rot))[0]
@@ -110,7 +138,7 @@ def main():
         loss = iteration(k)
     torch.cuda.synchronize(dev)
     dt = time.time() - t0
-    line = {"workload": "cf3dgs_global_steps", "impl": args.impl, "loss": args.loss, "P": P, "frames": args.frames, "W": W, "H": H,
+    line = {"workload": "cf3dgs_global_steps", "impl": args.impl, "loss": args.loss, "model": args.model, "P": P, "frames": args.frames, "W": W, "H": H,
             "sh_degree": args.sh_degree, "iters": args.iters, "iters_per_s": args.iters / dt, "ms_per_iter": dt / args.iters * 1e3,
             "first_loss": float(first.detach()), "last_loss": float(loss.detach())}
     os.write(real_stdout, (json.dumps(line) + "\n").encode())

@@ -1,0 +1,56 @@
+"""GPU: fused activation / Adam / densification-statistics kernels against torch.optim.Adam + autograd through the
+reference's activations (scene/gaussian_model_cf.py:41-56,242-268,716-719)."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+LRS = dict(xyz=1.6e-4, f_dc=2.5e-3, f_rest=1.25e-4, opacity=0.05, scaling=5e-3, rotation=1e-3)
+
+
+def test_fused_model_step_matches_torch_adam_through_the_activations():
+    import gsr_model
+    g = torch.Generator().manual_seed(9)
+    P, M = 5000, 16
+    xyz = torch.randn(P, 3, generator=g).to(DEV)
+    feat = (0.3 * torch.randn(P, M, 3, generator=g)).to(DEV)
+    opa = torch.randn(P, 1, generator=g).to(DEV)
+    ls = (torch.randn(P, 3, generator=g) * 0.3 - 3).to(DEV)
+    rot = torch.randn(P, 4, generator=g).to(DEV)
+    model = gsr_model.FusedGaussianModel(xyz, feat, opa, ls, rot, LRS)
+    # torch reference: six parameter groups, Adam eps 1e-15, autograd through sigmoid / exp / normalize / cat
+    t = dict(xyz=xyz.clone().requires_grad_(True), f_dc=feat[:, :1].clone().requires_grad_(True),
+             f_rest=feat[:, 1:].clone().requires_grad_(True), opa=opa.clone().requires_grad_(True),
+             ls=ls.clone().requires_grad_(True), rot=rot.clone().requires_grad_(True))
+    opt = torch.optim.Adam([{"params": [t["xyz"]], "lr": LRS["xyz"]}, {"params": [t["f_dc"]], "lr": LRS["f_dc"]},
+                            {"params": [t["f_rest"]], "lr": LRS["f_rest"]}, {"params": [t["opa"]], "lr": LRS["opacity"]},
+                            {"params": [t["ls"]], "lr": LRS["scaling"]}, {"params": [t["rot"]], "lr": LRS["rotation"]}], eps=1e-15)
+    accum = torch.zeros(P, 1, device=DEV); denom = torch.zeros(P, 1, device=DEV); maxr = torch.zeros(P, device=DEV)
+    for it in range(5):
+        gg = torch.Generator().manual_seed(100 + it)
+        # "rasterizer" gradients w.r.t. the activated tensors
+        d_xyz = torch.randn(P, 3, generator=gg).to(DEV); d_f = torch.randn(P, M, 3, generator=gg).to(DEV)
+        d_o = torch.randn(P, 1, generator=gg).to(DEV); d_s = torch.randn(P, 3, generator=gg).to(DEV)
+        d_r = torch.randn(P, 4, generator=gg).to(DEV)
+        d_m2 = torch.randn(P, 3, generator=gg).to(DEV)
+        radii = (torch.rand(P, generator=gg) * 20 - 5).clamp(min=0).int().to(DEV)
+        act = model.activated()
+        o_ref, s_ref, r_ref = torch.sigmoid(t["opa"]), torch.exp(t["ls"]), F.normalize(t["rot"])
+        for a, b in [(act["opacities"], o_ref), (act["scales"], s_ref), (act["rotations"], r_ref)]:
+            assert float((a - b).abs().max()) <= 2e-6 * max(1.0, float(b.abs().max()))
+        feats = torch.cat([t["f_dc"], t["f_rest"]], 1)
+        loss = (t["xyz"] * d_xyz).sum() + (feats * d_f).sum() + (o_ref * d_o).sum() + (s_ref * d_s).sum() + (r_ref * d_r).sum()
+        loss.backward()
+        opt.step(); opt.zero_grad(set_to_none=True)
+        vis = radii > 0
+        accum[vis] += torch.norm(d_m2[vis, :2], dim=-1, keepdim=True); denom[vis] += 1
+        maxr[vis] = torch.max(maxr[vis], radii[vis].float())
+        model.step(d_xyz, d_f, d_o, d_s, d_r, d_means2D=d_m2, radii=radii)
+    pairs = [(model.xyz, t["xyz"]), (model.features, torch.cat([t["f_dc"], t["f_rest"]], 1)), (model.opacity_raw, t["opa"]),
+             (model.log_scales, t["ls"]), (model.rot_raw, t["rot"])]
+    for a, b in pairs:
+        # five Adam steps of size ~lr each: agreement far below one step
+        assert float((a - b.detach()).abs().max()) <= 2e-5 * max(1e-2, float((b.detach() - 0).abs().max())) + 1e-6
+    assert float((model.xyz_gradient_accum - accum[:, 0]).abs().max()) <= 1e-4
+    assert torch.equal(model.denom, denom[:, 0]) and torch.equal(model.max_radii2D, maxr)
