@@ -453,4 +453,14 @@ int gsr_debug_pair_counts(int P, int W, int H, int64_t num_rendered, const void*
     return GSR_OK;
 }
 
+int gsr_debug_expf_check(uint32_t first_bits, uint32_t count, uint64_t* mismatches, void* stream)
+{
+    cudaStream_t s = (cudaStream_t)stream;
+    const int debug = 1;
+    if (!mismatches) return fail(GSR_ERR_INVALID, "mismatches is NULL");
+    launch_expf_check(first_bits, count, (unsigned long long*)mismatches, s);
+    GSR_STAGE("expf check");
+    return GSR_OK;
+}
+
 }  // extern "C"

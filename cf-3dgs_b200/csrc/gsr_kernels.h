@@ -49,6 +49,9 @@ void launch_render_forward(int W, int H, const uint2* ranges, const uint32_t* po
                            const float* bg, float* out_color, float* out_depth, float* out_alpha,
                            uint32_t* n_contrib, cudaStream_t s);
 
+bool blend_packed();   // false when GSR_BLEND=scalar (one pixel per lane kernels, kept for A/B runs)
+void launch_expf_check(uint32_t first_bits, uint32_t count, unsigned long long* mismatches, cudaStream_t s);
+
 void launch_pair_counts(int W, int H, const uint2* ranges, const uint32_t* point_list, const GeomView& g,
                         const uint32_t* n_contrib, unsigned long long* counts, cudaStream_t s);
 

@@ -11,9 +11,23 @@
 // with one lane per entry + a ballot, then walks only the surviving bits.  Rejected pairs are exactly
 // pairs the reference would have skipped at its alpha test.
 #include "gsr_blend.cuh"
+#include "gsr_f32x2.cuh"
 #include "gsr_kernels.h"
 
+#include <cstdlib>
+#include <cstring>
+
 namespace gsr {
+
+// GSR_BLEND=scalar selects the one-pixel-per-lane kernels (kept for A/B measurements); default: packed pairs.
+bool blend_packed()
+{
+    static const bool packed = [] {
+        const char* e = getenv("GSR_BLEND");
+        return !(e && strcmp(e, "scalar") == 0);
+    }();
+    return packed;
+}
 
 #ifndef GSR_FWD_MIN_BLOCKS
 #define GSR_FWD_MIN_BLOCKS 6
@@ -108,6 +122,158 @@ render_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// Packed variant: two pixels per lane, FP32 pairs (gsr_f32x2.cuh).  128 threads per tile; each warp owns an 8x8
+// footprint and lane (lx, ly) blends pixels (lx, ly) and (lx, ly + 4) of it.  The entry walk, the record loads, dx and
+// the scalar factors dx*A, dx*B are shared by the two pixels; dy, the exponent, alpha, the transmittance and the five
+// accumulators are FFMA2 / FMUL2 / FADD2 pairs.  Per-pixel control flow becomes selects: a pixel that skips an entry
+// (power > 0, alpha < 1/255, or already finished) blends it with alpha = 0, which leaves T and every accumulator
+// bit-unchanged (T*1, C + 0), and the entry that would drop T below 1e-4 is blended with alpha = 0 too and latches the
+// pixel's `done` predicate -- so each pixel sees exactly the reference's sequence of rounded operations.
+#ifndef GSR_FWDP_MIN_BLOCKS
+#define GSR_FWDP_MIN_BLOCKS 8
+#endif
+constexpr int PK_THREADS = 128;
+constexpr int PK_FOOT = 8;
+
+__global__ void __launch_bounds__(PK_THREADS, GSR_FWDP_MIN_BLOCKS)
+render_forward_packed_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges,
+                             const uint32_t* __restrict__ point_list, GeomView g, const float* __restrict__ bg,
+                             float* __restrict__ out_color, float* __restrict__ out_depth,
+                             float* __restrict__ out_alpha, uint32_t* __restrict__ n_contrib)
+{
+    __shared__ Staged sm;
+    const int tile = blockIdx.x;
+    const int tile_x = tile % grid_x, tile_y = tile / grid_x;
+    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int fx0 = tile_x * TILE + (warp & 1) * PK_FOOT, fy0 = tile_y * TILE + (warp >> 1) * PK_FOOT;
+    const int pix_x = fx0 + (lane & 7), pix_ya = fy0 + (lane >> 3), pix_yb = pix_ya + 4;
+    const float pxf = (float)pix_x;
+    const f32x2 py2 = pk((float)pix_ya, (float)pix_yb);
+    const float foot_x0 = (float)fx0, foot_y0 = (float)fy0;
+    const float tile_x0 = (float)(tile_x * TILE), tile_y0 = (float)(tile_y * TILE);
+
+    const uint2 range = ranges[tile];
+    const int total = (int)(range.y - range.x);
+    const bool inside_a = pix_x < W && pix_ya < H, inside_b = pix_x < W && pix_yb < H;
+    // A finished pixel (outside the image, or T*(1-alpha) < 1e-4 reached) carries its transmittance with the sign
+    // flipped: T < 0 <=> done, |T| is the value the background term needs.  No separate flag to keep in a register.
+    // (kept as two floats and packed at its uses: ptxas then updates the pair in place)
+    float2 T = {inside_a ? 1.0f : -1.0f, inside_b ? 1.0f : -1.0f};
+    f32x2 C0 = bc(0.f), C1 = bc(0.f), C2 = bc(0.f), Wt = bc(0.f), Dacc = bc(0.f);
+    uint32_t last_a = 0, last_b = 0;
+    const auto all_done = [&]() { return (T.x < 0.f) && (T.y < 0.f); };
+
+    for (int base = 0; base < total; base += BATCH) {
+        if (__syncthreads_count(all_done()) == PK_THREADS) break;
+        const int n = min(BATCH, total - base);
+        for (int k = threadIdx.x; k < n; k += PK_THREADS)
+            stage_entry(sm, k, point_list[range.x + base + k], g, tile_x0, tile_y0);
+        __syncthreads();
+
+        for (int c0 = 0; c0 < n; c0 += 32) {
+            if (__all_sync(0xffffffffu, all_done())) break;
+            const int e = c0 + lane;
+            bool keep = false;
+            if (e < n) {
+                const float thr = sm.thr[e];
+                if (!(thr < 0.f)) {
+                    const float4 r0 = sm.rec0[e];
+                    const float4 r1 = sm.rec1[e];
+                    keep = !reject_rect(r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, thr, foot_x0,
+                                        foot_x0 + (PK_FOOT - 1), foot_y0, foot_y0 + (PK_FOOT - 1));
+                }
+            }
+            unsigned live = __ballot_sync(0xffffffffu, keep);
+            const uint32_t pos0 = (uint32_t)(base + c0 + 1);
+            while (live) {
+                const int b = __ffs(live) - 1;
+                live &= live - 1;
+                const int j = c0 + b;
+                const float4 r0 = sm.rec0[j];
+                const float4 r1 = sm.rec1[j];
+                // blend_power() for both pixels: t = fma(dx, dx*A, dy*(dy*C)); power = fma(t, -0.5, -(dy*(dx*B)))
+                const float dx = __fadd_rn(r0.x, -pxf);
+                const f32x2 dy = sub2(bc(r0.y), py2);
+                const float dxA = __fmul_rn(dx, r1.x), ndxB = __fmul_rn(dx, -r1.y);
+                const f32x2 t = fma2(bc(dx), bc(dxA), mul2(dy, mul2(dy, bc(r1.z))));
+                const f32x2 power = fma2(t, bc(-0.5f), mul2(dy, bc(ndxB)));
+                float pa, pb, ala, alb, tta, ttb;
+                const float Ta = T.x, Tb = T.y;
+                const f32x2 Tp = pk(Ta, Tb);
+                unpk(power, pa, pb);
+                unpk(mul2(bc(r1.w), exp2x(pa, pb)), ala, alb);
+                ala = fminf(0.99f, ala);
+                alb = fminf(0.99f, alb);
+                const bool skip_a = (Ta < 0.f) || (pa > 0.0f) || (ala < 1.0f / 255.0f);
+                const bool skip_b = (Tb < 0.f) || (pb > 0.0f) || (alb < 1.0f / 255.0f);
+                ala = skip_a ? 0.f : ala;
+                alb = skip_b ? 0.f : alb;
+                unpk(mul2(Tp, sub2(bc(1.f), pk(ala, alb))), tta, ttb);
+                // forward.cu:352-356: the entry that would take T below 1e-4 ends the pixel and is not blended.
+                // (a finished pixel has T < 0 and alpha = 0 here, so it lands in the same branch and keeps -|T|)
+                const bool fin_a = tta < 0.0001f, fin_b = ttb < 0.0001f;
+                ala = fin_a ? 0.f : ala;
+                alb = fin_b ? 0.f : alb;
+                const f32x2 al = pk(ala, alb);
+                const float4 r2 = sm.rec2[j];
+                C0 = fma2(Tp, mul2(al, bc(r2.x)), C0);
+                C1 = fma2(Tp, mul2(al, bc(r2.y)), C1);
+                C2 = fma2(Tp, mul2(al, bc(r2.z)), C2);
+                Wt = fma2(Tp, al, Wt);
+                Dacc = fma2(Tp, mul2(al, bc(r2.w)), Dacc);
+                T.x = fin_a ? -fabsf(Ta) : tta;
+                T.y = fin_b ? -fabsf(Tb) : ttb;
+                const uint32_t pos = pos0 + (uint32_t)b;
+                last_a = (skip_a || fin_a) ? last_a : pos;
+                last_b = (skip_b || fin_b) ? last_b : pos;
+            }
+        }
+    }
+
+    const size_t plane = (size_t)W * H;
+    float Ta, Tb, c0a, c0b, c1a, c1b, c2a, c2b, wa, wb, da, db;
+    Ta = fabsf(T.x); Tb = fabsf(T.y); unpk(C0, c0a, c0b); unpk(C1, c1a, c1b); unpk(C2, c2a, c2b); unpk(Wt, wa, wb); unpk(Dacc, da, db);
+    if (inside_a) {
+        const size_t pid = (size_t)W * pix_ya + pix_x;
+        n_contrib[pid] = last_a;
+        out_color[pid] = __fmaf_rn(bg[0], Ta, c0a);
+        out_color[plane + pid] = __fmaf_rn(bg[1], Ta, c1a);
+        out_color[2 * plane + pid] = __fmaf_rn(bg[2], Ta, c2a);
+        out_alpha[pid] = wa;
+        out_depth[pid] = da;
+    }
+    if (inside_b) {
+        const size_t pid = (size_t)W * pix_yb + pix_x;
+        n_contrib[pid] = last_b;
+        out_color[pid] = __fmaf_rn(bg[0], Tb, c0b);
+        out_color[plane + pid] = __fmaf_rn(bg[1], Tb, c1b);
+        out_color[2 * plane + pid] = __fmaf_rn(bg[2], Tb, c2b);
+        out_alpha[pid] = wb;
+        out_depth[pid] = db;
+    }
+}
+
+// Exhaustive check of exp2x() against expf() over a range of float bit patterns (test hook).
+__global__ void expf_check_kernel(uint32_t first_bits, uint32_t count, unsigned long long* mismatches)
+{
+    unsigned long long bad = 0;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += (uint64_t)gridDim.x * blockDim.x) {
+        const float x = __uint_as_float(first_bits + (uint32_t)i);
+        float a, b;
+        unpk(exp2x(x, x * 0.5f), a, b);
+        const float ra = expf(x), rb = expf(x * 0.5f);
+        bad += (__float_as_uint(a) != __float_as_uint(ra)) + (__float_as_uint(b) != __float_as_uint(rb));
+    }
+    if (bad) atomicAdd(mismatches, bad);
+}
+
+void launch_expf_check(uint32_t first_bits, uint32_t count, unsigned long long* mismatches, cudaStream_t s)
+{
+    cudaMemsetAsync(mismatches, 0, sizeof(unsigned long long), s);
+    expf_check_kernel<<<148 * 8, 256, 0, s>>>(first_bits, count, mismatches);
+}
+
 // Work counters for roofline accounting (see gsr_debug_pair_counts in include/gsr.h).
 __global__ void __launch_bounds__(BLEND_THREADS)
 pair_counts_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
@@ -200,8 +366,12 @@ void launch_render_forward(int W, int H, const uint2* ranges, const uint32_t* po
                            uint32_t* n_contrib, cudaStream_t s)
 {
     const int gx = div_up(W, TILE), gy = div_up(H, TILE);
-    render_forward_kernel<<<gx * gy, BLEND_THREADS, 0, s>>>(W, H, gx, ranges, point_list, g, bg, out_color,
-                                                            out_depth, out_alpha, n_contrib);
+    if (blend_packed())
+        render_forward_packed_kernel<<<gx * gy, PK_THREADS, 0, s>>>(W, H, gx, ranges, point_list, g, bg, out_color,
+                                                                    out_depth, out_alpha, n_contrib);
+    else
+        render_forward_kernel<<<gx * gy, BLEND_THREADS, 0, s>>>(W, H, gx, ranges, point_list, g, bg, out_color,
+                                                                out_depth, out_alpha, n_contrib);
 }
 
 }  // namespace gsr

@@ -7,7 +7,7 @@ from __future__ import annotations
 
 import ctypes
 import os
-from ctypes import c_char_p, c_float, c_int, c_int64, c_size_t, c_void_p
+from ctypes import c_char_p, c_float, c_int, c_int64, c_size_t, c_uint32, c_void_p
 
 _PKG_ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB_PATH = os.environ.get("GSR_B200_LIB", os.path.join(_PKG_ROOT, "libgsr_b200.so"))
@@ -45,6 +45,7 @@ SIGNATURES = {
     "gsr_profile_name": (c_char_p, [c_int]),
     "gsr_profile_read": (c_int, [_P, c_int]),
     "gsr_debug_pair_counts": (c_int, [c_int, c_int, c_int, c_int64, _P, _P, _P, _P, _P]),
+    "gsr_debug_expf_check": (c_int, [c_uint32, c_uint32, _P, _P]),
 }
 
 

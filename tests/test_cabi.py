@@ -36,7 +36,8 @@ def test_ctypes_signatures_match_header():
         if "*" in a:
             return ctypes.c_void_p
         t = " ".join(a.split()[:-1])
-        return {"int": ctypes.c_int, "float": ctypes.c_float, "int64_t": ctypes.c_int64, "size_t": ctypes.c_size_t}[t]
+        return {"int": ctypes.c_int, "float": ctypes.c_float, "int64_t": ctypes.c_int64, "size_t": ctypes.c_size_t,
+                "uint32_t": ctypes.c_uint32}[t]
 
     decls = _header_decls()
     assert {n for _, n, _ in decls} == set(_cabi.SIGNATURES), "binding and header list different entry points"
