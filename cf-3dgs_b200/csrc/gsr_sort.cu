@@ -88,7 +88,15 @@ radix_rowscan_kernel(uint32_t* __restrict__ hist, int nblk, uint32_t* __restrict
 
 // pass kernel 3: stable scatter.  Items are first placed at their block-local sorted position in shared memory, then
 // written out in that order, so a warp's stores fall into a few contiguous runs (one per digit) instead of 32 sectors.
-__global__ void __launch_bounds__(SORT_THREADS)
+#ifndef GSR_SCATTER_MIN_BLOCKS
+#define GSR_SCATTER_MIN_BLOCKS 4
+#endif
+// BALLOT_BITS > 0: the lanes holding the same digit are found with one ballot per digit bit instead of MATCH.ANY.
+// Measured on B200 (tools/micro/match_bench.cu): MATCH.ANY costs ~7 cycles per DISTINCT value in the warp (226 cycles
+// for 32 distinct values), eight ballots a flat ~109 -- and the digits a warp sees here are mostly distinct (low tile
+// bits of consecutive instances, low mantissa bits of depths).
+template <int BALLOT_BITS>
+__global__ void __launch_bounds__(SORT_THREADS, GSR_SCATTER_MIN_BLOCKS)
 radix_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                      uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int64_t n_cap,
                      const unsigned long long* __restrict__ n_dev, int shift,
@@ -112,29 +120,46 @@ radix_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __res
     // each warp owns a contiguous run of SORT_ITEMS*32 items; order inside it is (step, lane)
     const int64_t block_base = (int64_t)blockIdx.x * SORT_CHUNK;
     const int64_t wbase = block_base + (int64_t)warp * (SORT_ITEMS * 32);
-    uint32_t key[SORT_ITEMS], val[SORT_ITEMS], rank[SORT_ITEMS];
+    uint32_t key[SORT_ITEMS], rank[SORT_ITEMS];
 #pragma unroll
     for (int i = 0; i < SORT_ITEMS; i++) {
         const int64_t idx = wbase + i * 32 + lane;
-        const bool act = idx < n;
-        key[i] = act ? keys_in[idx] : 0u;
-        val[i] = act ? vals_in[idx] : 0u;
+        key[i] = idx < n ? keys_in[idx] : 0u;
+    }
+    // Ranking, written so that the eight items' latencies overlap instead of adding up: all MATCHes first, then one
+    // shared-memory atomic per digit group (the group leader fetches-and-adds the warp-private counter; a warp's
+    // shared-memory instructions execute in order, so item i's groups are counted before item i+1's), then the
+    // broadcasts.  Nothing in one item's chain waits for another item's result.
+    unsigned grp[SORT_ITEMS];
+#pragma unroll
+    for (int i = 0; i < SORT_ITEMS; i++) {
+        const bool act = (wbase + i * 32 + lane) < n;
+        const uint32_t d = act ? ((key[i] >> shift) & mask) : (uint32_t)RADIX;
+        if (BALLOT_BITS > 0) {
+            unsigned same = __ballot_sync(0xffffffffu, act);
+            if (!act) same = ~same;
+#pragma unroll
+            for (int b = 0; b < BALLOT_BITS; b++) {
+                const bool bit = (d >> b) & 1u;
+                const unsigned bal = __ballot_sync(0xffffffffu, bit);
+                same &= bit ? bal : ~bal;
+            }
+            grp[i] = same;
+        } else {
+            grp[i] = __match_any_sync(0xffffffffu, d);
+        }
     }
 #pragma unroll
     for (int i = 0; i < SORT_ITEMS; i++) {
         const bool act = (wbase + i * 32 + lane) < n;
         const uint32_t d = act ? ((key[i] >> shift) & mask) : (uint32_t)RADIX;
-        const unsigned m = __match_any_sync(0xffffffffu, d);
-        const int leader = __ffs(m) - 1;
-        uint32_t prev = 0;
-        if (lane == (unsigned)leader) {
-            prev = wcount[warp][d];
-            wcount[warp][d] = prev + (uint32_t)__popc(m);
-        }
-        prev = __shfl_sync(0xffffffffu, prev, leader);
-        rank[i] = prev + (uint32_t)__popc(m & ((1u << lane) - 1u));
+        rank[i] = 0;
+        if (lane == (unsigned)(__ffs(grp[i]) - 1)) rank[i] = atomicAdd(&wcount[warp][d], (uint32_t)__popc(grp[i]));
         __syncwarp();
     }
+#pragma unroll
+    for (int i = 0; i < SORT_ITEMS; i++)
+        rank[i] = __shfl_sync(0xffffffffu, rank[i], __ffs(grp[i]) - 1) + (uint32_t)__popc(grp[i] & ((1u << lane) - 1u));
     __syncthreads();
     // per digit: total over the block, its block-local start (scan over digits), then warp bases
     {
@@ -151,6 +176,14 @@ radix_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __res
         }
     }
     __syncthreads();
+    // the values are only needed now: loading them here instead of next to the keys keeps 8 registers free during the
+    // ranking loop (occupancy is what hides its shared-memory / MATCH latency)
+    uint32_t val[SORT_ITEMS];
+#pragma unroll
+    for (int i = 0; i < SORT_ITEMS; i++) {
+        const int64_t idx = wbase + i * 32 + lane;
+        val[i] = idx < n ? vals_in[idx] : 0u;
+    }
 #pragma unroll
     for (int i = 0; i < SORT_ITEMS; i++) {
         if ((wbase + i * 32 + lane) < n) {
@@ -316,6 +349,17 @@ radix_onesweep_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __re
     }
 }
 
+// GSR_RANK=match|ballot forces one grouping method for every pass (default: chosen per digit)
+static int rank_mode()
+{
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("GSR_RANK");
+        v = !e ? 0 : (strcmp(e, "match") == 0 ? 1 : (strcmp(e, "ballot") == 0 ? 2 : 0));
+    }
+    return v;
+}
+
 static bool use_classic_sort()
 {
     static int v = -1;
@@ -339,8 +383,17 @@ int radix_sort_pairs(uint32_t* keys[2], uint32_t* vals[2], int64_t n, int begin_
             const uint32_t mask = (1u << bits) - 1u;
             radix_hist_kernel<<<nblk, SORT_THREADS, 0, s>>>(keys[cur], n, n_dev, shift, mask, hist, nblk);
             radix_rowscan_kernel<<<RADIX, SORT_THREADS, 0, s>>>(hist, nblk, digit_total);
-            radix_scatter_kernel<<<nblk, SORT_THREADS, 0, s>>>(keys[cur], vals[cur], keys[cur ^ 1], vals[cur ^ 1], n,
-                                                               n_dev, shift, mask, hist, nblk, digit_total);
+            // the sign/exponent byte of a depth takes few distinct values (MATCH is cheap there); every other digit is
+            // close to all-distinct within a warp
+            const int mode = rank_mode();
+            const bool ballots = mode == 2 || (mode == 0 && !(shift == 24 && end_bit == 32));
+#define GSR_SCATTER(B)                                                                                                \
+    radix_scatter_kernel<B><<<nblk, SORT_THREADS, 0, s>>>(keys[cur], vals[cur], keys[cur ^ 1], vals[cur ^ 1], n, n_dev,  \
+                                                          shift, mask, hist, nblk, digit_total)
+            if (!ballots) GSR_SCATTER(0);
+            else if (bits <= 5) GSR_SCATTER(5);
+            else GSR_SCATTER(8);
+#undef GSR_SCATTER
             cur ^= 1;
         }
         return cur;
