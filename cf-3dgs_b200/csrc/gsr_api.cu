@@ -118,10 +118,10 @@ static int depth_sort_and_offsets(int P, const GeomView& g, cudaStream_t s)
 {
     {
         StageTimer t(ST_DEPTH_SORT, s);
-        launch_init_sort_input(g, P, s);
         uint32_t* keys[2] = {g.sort_keys[0], g.sort_keys[1]};
         uint32_t* vals[2] = {g.sort_vals[0], g.sort_vals[1]};
-        const int cur = radix_sort_pairs(keys, vals, P, 0, 32, g.hist, g.digit_total, s);
+        // first pass straight from the depth keys preprocess wrote, values = Gaussian index
+        const int cur = radix_sort_pairs(keys, vals, P, 0, 32, g.hist, g.digit_total, s, nullptr, g.depth_key);
         if (cur != 0)  // keep the invariant "sort_vals[0] holds the depth order"
             cudaMemcpyAsync(g.sort_vals[0], g.sort_vals[1], sizeof(uint32_t) * (size_t)P, cudaMemcpyDeviceToDevice, s);
     }

@@ -31,7 +31,7 @@ void launch_mark_visible(int P, const float* means3D, const float* view, uint8_t
 // holds the result.
 int radix_sort_pairs(uint32_t* keys[2], uint32_t* vals[2], int64_t n, int begin_bit, int end_bit,
                      uint32_t* hist, uint32_t* digit_total, cudaStream_t s,
-                     const unsigned long long* n_dev = nullptr);
+                     const unsigned long long* n_dev = nullptr, const uint32_t* first_keys = nullptr);
 
 // offsets[i] = exclusive prefix sum of tiles[order[i]]
 void launch_offsets_scan(const uint32_t* tiles, const uint32_t* order, uint32_t* offsets, uint32_t* block_sums,

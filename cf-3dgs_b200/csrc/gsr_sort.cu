@@ -207,7 +207,7 @@ radix_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __res
 #pragma unroll
     for (int i = 0; i < SORT_ITEMS; i++) {
         const int64_t idx = wbase + i * 32 + lane;
-        val[i] = idx < n ? vals_in[idx] : 0u;
+        val[i] = vals_in ? (idx < n ? vals_in[idx] : 0u) : (uint32_t)idx;   // no value array: the item index
     }
 #pragma unroll
     for (int i = 0; i < SORT_ITEMS; i++) {
@@ -396,25 +396,31 @@ static bool use_classic_sort()
 }
 
 int radix_sort_pairs(uint32_t* keys[2], uint32_t* vals[2], int64_t n, int begin_bit, int end_bit,
-                     uint32_t* hist, uint32_t* digit_total, cudaStream_t s, const unsigned long long* n_dev)
+                     uint32_t* hist, uint32_t* digit_total, cudaStream_t s, const unsigned long long* n_dev,
+                     const uint32_t* first_keys)
 {
     int cur = 0;
     if (n <= 0) return cur;
     const int nblk = div_up(n, SORT_CHUNK);
     const int npass = (end_bit - begin_bit + RADIX_BITS - 1) / RADIX_BITS;
-    if (n_dev || use_classic_sort() || n >= ((int64_t)1 << 30) || npass > SORT_MAX_PASSES) {
+    if (first_keys || n_dev || use_classic_sort() || n >= ((int64_t)1 << 30) || npass > SORT_MAX_PASSES) {
         for (int shift = begin_bit; shift < end_bit; shift += RADIX_BITS) {
             const int bits = min(RADIX_BITS, end_bit - shift);
             const uint32_t mask = (1u << bits) - 1u;
-            radix_hist_kernel<<<nblk, SORT_THREADS, 0, s>>>(keys[cur], n, n_dev, shift, mask, hist, nblk);
+            // first_keys: the first pass reads its keys there and takes the item index as the value, so the caller
+            // does not have to materialise (key, iota) pairs first
+            const bool first = first_keys && shift == begin_bit;
+            const uint32_t* kin = first ? first_keys : keys[cur];
+            const uint32_t* vin = first ? nullptr : vals[cur];
+            radix_hist_kernel<<<nblk, SORT_THREADS, 0, s>>>(kin, n, n_dev, shift, mask, hist, nblk);
             radix_rowscan_kernel<<<RADIX, SORT_THREADS, 0, s>>>(hist, nblk, digit_total);
             // the sign/exponent byte of a depth takes few distinct values (MATCH is cheap there); every other digit is
             // close to all-distinct within a warp
             const int mode = rank_mode();
             const bool ballots = mode == 2 || (mode == 0 && !(shift == 24 && end_bit == 32));
 #define GSR_SCATTER(B)                                                                                                \
-    radix_scatter_kernel<B><<<nblk, SORT_THREADS, 0, s>>>(keys[cur], vals[cur], keys[cur ^ 1], vals[cur ^ 1], n, n_dev,  \
-                                                          shift, mask, hist, nblk, digit_total)
+    radix_scatter_kernel<B><<<nblk, SORT_THREADS, 0, s>>>(kin, vin, keys[cur ^ 1], vals[cur ^ 1], n, n_dev, shift, mask, \
+                                                          hist, nblk, digit_total)
             if (!ballots) GSR_SCATTER(0);
             else if (bits <= 5) GSR_SCATTER(5);
             else GSR_SCATTER(8);
@@ -578,29 +584,42 @@ void launch_emit(const GeomView& g, const uint32_t* order, int P, int grid_x, ui
 
 // ---------------------------------------------------------------------------------------------
 // reference identifyTileRanges (rasterizer_impl.cu:116-138) on the sorted tile ids
-__global__ void tile_ranges_kernel(const uint32_t* __restrict__ sorted_tiles, int64_t R_cap,
-                                   const unsigned long long* __restrict__ n_dev, uint2* __restrict__ ranges)
+__global__ void __launch_bounds__(256)
+tile_ranges_kernel(const uint32_t* __restrict__ sorted_tiles, int64_t R_cap,
+                   const unsigned long long* __restrict__ n_dev, uint2* __restrict__ ranges)
 {
+    // four consecutive entries per thread (one 16-byte load) plus the entry before them
     const int64_t R = device_count(n_dev, R_cap);
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= R) return;
-    const uint32_t cur = sorted_tiles[i];
-    if (i == 0) ranges[cur].x = 0;
-    else {
-        const uint32_t prev = sorted_tiles[i - 1];
-        if (cur != prev) {
+    const int64_t i0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    if (i0 >= R) return;
+    uint32_t t[5];
+    t[0] = i0 > 0 ? __ldg(sorted_tiles + i0 - 1) : 0xffffffffu;
+    if (i0 + 3 < R) {
+        const uint4 q = __ldg(reinterpret_cast<const uint4*>(sorted_tiles + i0));
+        t[1] = q.x; t[2] = q.y; t[3] = q.z; t[4] = q.w;
+    } else {
+#pragma unroll
+        for (int c = 0; c < 4; c++) t[c + 1] = i0 + c < R ? __ldg(sorted_tiles + i0 + c) : 0xffffffffu;
+    }
+#pragma unroll
+    for (int c = 0; c < 4; c++) {
+        const int64_t i = i0 + c;
+        if (i >= R) break;
+        const uint32_t cur = t[c + 1], prev = t[c];
+        if (i == 0) ranges[cur].x = 0;
+        else if (cur != prev) {
             ranges[prev].y = (uint32_t)i;
             ranges[cur].x = (uint32_t)i;
         }
+        if (i == R - 1) ranges[cur].y = (uint32_t)R;
     }
-    if (i == R - 1) ranges[cur].y = (uint32_t)R;
 }
 
 void launch_tile_ranges(const uint32_t* sorted_tiles, int64_t R, uint2* ranges, int tiles, cudaStream_t s,
                         const unsigned long long* n_dev)
 {
     cudaMemsetAsync(ranges, 0, sizeof(uint2) * (size_t)tiles, s);
-    if (R > 0) tile_ranges_kernel<<<div_up(R, 256), 256, 0, s>>>(sorted_tiles, R, n_dev, ranges);
+    if (R > 0) tile_ranges_kernel<<<div_up(div_up(R, 4), 256), 256, 0, s>>>(sorted_tiles, R, n_dev, ranges);
 }
 
 // sync-free forward: publish (count, overflow) for the host to look at whenever it likes
