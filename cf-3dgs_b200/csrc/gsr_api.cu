@@ -453,6 +453,22 @@ int gsr_debug_pair_counts(int P, int W, int H, int64_t num_rendered, const void*
     return GSR_OK;
 }
 
+size_t gsr_knn_scratch_bytes(int P) { return knn_scratch_bytes(P); }
+
+int gsr_knn_mean_dist2(int P, const float* points, float* mean_dist2, void* scratch, size_t scratch_bytes, void* stream)
+{
+    cudaStream_t s = (cudaStream_t)stream;
+    const int debug = 0;
+    if (P < 0) return fail(GSR_ERR_INVALID, "P < 0");
+    if (P == 0) return GSR_OK;
+    if (!points || !mean_dist2 || !scratch) return fail(GSR_ERR_INVALID, "points, mean_dist2 and scratch are required");
+    if (scratch_bytes < knn_scratch_bytes(P))
+        return fail(GSR_ERR_WORKSPACE, "knn scratch too small: %zu < %zu", scratch_bytes, knn_scratch_bytes(P));
+    launch_knn_mean_dist2(P, points, mean_dist2, scratch, s);
+    GSR_STAGE("knn");
+    return GSR_OK;
+}
+
 int gsr_debug_expf_check(uint32_t first_bits, uint32_t count, uint64_t* mismatches, void* stream)
 {
     cudaStream_t s = (cudaStream_t)stream;

@@ -49,6 +49,9 @@ void launch_render_forward(int W, int H, const uint2* ranges, const uint32_t* po
                            const float* bg, float* out_color, float* out_depth, float* out_alpha,
                            uint32_t* n_contrib, cudaStream_t s);
 
+size_t knn_scratch_bytes(int P);
+int launch_knn_mean_dist2(int P, const float* points, float* mean_d2, void* scratch, cudaStream_t s);
+
 bool blend_packed();   // false when GSR_BLEND=scalar (one pixel per lane kernels, kept for A/B runs)
 void launch_expf_check(uint32_t first_bits, uint32_t count, unsigned long long* mismatches, cudaStream_t s);
 

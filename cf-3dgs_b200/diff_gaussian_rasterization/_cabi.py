@@ -45,6 +45,8 @@ SIGNATURES = {
     "gsr_profile_name": (c_char_p, [c_int]),
     "gsr_profile_read": (c_int, [_P, c_int]),
     "gsr_debug_pair_counts": (c_int, [c_int, c_int, c_int, c_int64, _P, _P, _P, _P, _P]),
+    "gsr_knn_scratch_bytes": (c_size_t, [c_int]),
+    "gsr_knn_mean_dist2": (c_int, [c_int, _P, _P, _P, c_size_t, _P]),
     "gsr_debug_expf_check": (c_int, [c_uint32, c_uint32, _P, _P]),
 }
 

@@ -8,6 +8,11 @@ reference's setup.py / CMake are not run) and writes ONE artefact:
     oracle/_ref/_dgr_ref.so      (python extension module, pybind names as in
                                   submodules/diff-gaussian-rasterization/ext.cpp:15-19)
 
+and, for the simple-knn row, a second one from the single source file
+submodules/simple-knn/simple_knn.cu (no torch needed; `SimpleKNN::knn` is called through its mangled name):
+
+    oracle/_ref/_sknn_ref.so
+
 oracle/_ref/ is git-ignored but travels to the GPU box with the snapshot.  It cannot
 execute in the build container (no GPU); on the GPU box it is
   * the parity pin for keys / sorted order / tile ranges / images / gradients, and
@@ -71,6 +76,30 @@ def build(force: bool = False, verbose: bool = False) -> str | None:
     return OUT
 
 
+SKNN_DIR = os.path.join(REF, "submodules", "simple-knn")
+SKNN_OUT = os.path.join(OUT_DIR, "_sknn_ref.so")
+SKNN_SYMBOL = "_ZN9SimpleKNN3knnEiP6float3Pf"   # SimpleKNN::knn(int, float3*, float*), simple_knn.h
+
+
+def build_sknn(force: bool = False, verbose: bool = False) -> str | None:
+    """oracle/_ref/_sknn_ref.so from simple_knn.cu alone.  Additions to the reference's flags: `-include cfloat`
+    (FLT_MAX is used without its header) and the sm_100a target."""
+    src = os.path.join(SKNN_DIR, "simple_knn.cu")
+    if not os.path.exists(src):
+        return SKNN_OUT if os.path.exists(SKNN_OUT) else None
+    if os.path.exists(SKNN_OUT) and not force and os.path.getmtime(SKNN_OUT) >= os.path.getmtime(src):
+        return SKNN_OUT
+    os.makedirs(OUT_DIR, exist_ok=True)
+    cmd = ["nvcc", "-shared", "-o", SKNN_OUT, src, "-std=c++17", "-O3", "-include", "cstdint", "-include", "cfloat",
+           "-I" + SKNN_DIR, "-Xcompiler", "-fPIC", "-gencode", "arch=compute_100a,code=sm_100a", "-w"]
+    if verbose:
+        print(" ".join(cmd))
+    subprocess.check_call(cmd)
+    return SKNN_OUT
+
+
 if __name__ == "__main__":
     p = build(force="--force" in sys.argv, verbose=True)
     print("built:" if p else "reference sources not found; nothing built", p or "")
+    p = build_sknn(force="--force" in sys.argv, verbose=True)
+    print("built:" if p else "simple-knn sources not found; nothing built", p or "")

@@ -697,3 +697,30 @@ int gsro_sort_bits(int W, int H)
     const int gx = (W + TILE - 1) / TILE, gy = (H + TILE - 1) / TILE;
     return 32 + (int)higher_msb((uint32_t)(gx * gy));
 }
+
+/* simple-knn distCUDA2 (submodules/simple-knn/simple_knn.cu:131-183, spatial.cu:15-26): mean of the three smallest
+ * squared distances from every point to the others.  The reference's Morton boxes only prune its search, so the
+ * restatement is the brute-force definition with the reference build's rounding sequence:
+ *   d = other - self;  d2 = fma(dz, dz, fma(dx, dx, rn(dy*dy)));  mean = rn(rn(rn(b0 + b1) + b2) / 3)
+ * (b0 <= b1 <= b2 start at FLT_MAX, simple_knn.cu:151; a point is excluded by index, so coincident points count). */
+void gsro_knn_mean_dist2(int P, const float* pts, float* out)
+{
+#pragma omp parallel for schedule(static)
+    for (int i = 0; i < P; i++) {
+        const float sx = pts[3 * i], sy = pts[3 * i + 1], sz = pts[3 * i + 2];
+        float best[3] = {3.402823466e+38f, 3.402823466e+38f, 3.402823466e+38f};
+        for (int j = 0; j < P; j++) {
+            if (j == i) continue;
+            const float dx = pts[3 * j] - sx, dy = pts[3 * j + 1] - sy, dz = pts[3 * j + 2] - sz;
+            float dist = fmaf(dz, dz, fmaf(dx, dx, dy * dy));
+            for (int k = 0; k < 3; k++) {   /* updateKBest<3>, simple_knn.cu:131-145 */
+                if (best[k] > dist) {
+                    const float t = best[k];
+                    best[k] = dist;
+                    dist = t;
+                }
+            }
+        }
+        out[i] = ((best[0] + best[1]) + best[2]) / 3.0f;
+    }
+}

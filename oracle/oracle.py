@@ -160,6 +160,15 @@ def backward(st, grad_color, grad_depth=None, grad_alpha=None):
     return g
 
 
+def knn_mean_dist2(points):
+    """distCUDA2 (simple-knn): mean squared distance to the three nearest other points, brute force O(P^2)."""
+    lib = _load()
+    points = _f32(points).reshape(-1, 3)
+    out = np.zeros(points.shape[0], np.float32)
+    lib.gsro_knn_mean_dist2(c_int(points.shape[0]), _p(points), _p(out))
+    return out
+
+
 def mark_visible(means3D, viewmatrix):
     lib = _load()
     means3D = _f32(means3D)

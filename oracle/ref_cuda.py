@@ -100,3 +100,28 @@ def parse_state(st, P, W, H):
     out["rgb"] = rgb.view(P, 3)
     out["tiles_touched"], off = _carve(g, off, 4 * P, torch.int32)
     return out
+
+
+# ---- simple-knn (oracle/_ref/_sknn_ref.so) -------------------------------------------------------
+_sknn = None
+
+
+def sknn_available() -> bool:
+    return os.path.exists(os.path.join(_REF_DIR, "_sknn_ref.so")) and torch.cuda.is_available()
+
+
+def dist_cuda2(points: torch.Tensor) -> torch.Tensor:
+    """The reference's distCUDA2 (spatial.cu:15-26): SimpleKNN::knn on a contiguous float32 CUDA tensor."""
+    global _sknn
+    import ctypes
+    if _sknn is None:
+        _sknn = ctypes.CDLL(os.path.join(_REF_DIR, "_sknn_ref.so"))
+    fn = getattr(_sknn, "_ZN9SimpleKNN3knnEiP6float3Pf")
+    fn.restype = None
+    fn.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p]
+    pts = points.contiguous().float()
+    out = torch.zeros(pts.shape[0], dtype=torch.float32, device=pts.device)
+    torch.cuda.synchronize()
+    fn(pts.shape[0], pts.data_ptr(), out.data_ptr())   # launches on the legacy default stream
+    torch.cuda.synchronize()
+    return out

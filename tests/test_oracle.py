@@ -93,3 +93,25 @@ def test_mark_visible_is_the_near_plane_test():
     vis = O.mark_visible(sc["means3D"].numpy(), cam["viewmatrix"].numpy())
     z = (torch.cat([sc["means3D"], torch.ones(1000, 1)], 1) @ cam["viewmatrix"])[:, 2].numpy()
     assert (vis == (z > 0.2)).mean() > 0.999
+
+
+def test_knn_oracle_is_the_three_nearest_neighbour_mean():
+    """gsro_knn_mean_dist2 (restating simple_knn.cu:131-183) against scipy's exact k-d tree in float64."""
+    from scipy.spatial import cKDTree
+    from oracle import oracle as O
+    rng = np.random.default_rng(5)
+    pts = (rng.standard_normal((3000, 3)) * 2 + 1).astype(np.float32)
+    got = O.knn_mean_dist2(pts)
+    d, _ = cKDTree(pts.astype(np.float64)).query(pts.astype(np.float64), k=4)
+    want = (d[:, 1:] ** 2).mean(1)
+    assert np.abs(got - want).max() <= 1e-6 * want.max()
+    # fewer than three neighbours: the missing ones stay at FLT_MAX (simple_knn.cu:151,182)
+    assert np.allclose(O.knn_mean_dist2(pts[:3]), np.float32(3.402823466e38) / 3, rtol=1e-6)
+    assert np.isinf(O.knn_mean_dist2(pts[:2])).all()
+
+
+def test_simple_knn_shim_has_no_cpu_path():
+    import torch
+    from simple_knn._C import distCUDA2
+    with pytest.raises(RuntimeError):
+        distCUDA2(torch.zeros(8, 3))
