@@ -38,7 +38,7 @@ import torch
 WORKLOAD = dict(name="gvol_1M_1080p_sh3", P=1_000_000, W=1920, H=1080, seed=5, sh_degree=3)
 PARAM_KEYS = ["means3D", "opacities", "shs", "scales", "rotations"]
 # DRAM bytes per launch of the kernels that can dominate, from the committed ncu capture of this workload
-NCU_TRAFFIC_BYTES = {"render_backward": 150.8e6 + 18.1e6, "render_forward": 69.3e6 + 31.5e6,
+NCU_TRAFFIC_BYTES = {"render_backward": 150.2e6 + 16.9e6, "render_forward": 66.7e6 + 29.1e6,
                      "preprocess": 253.4e6 + 40.2e6, "preprocess_backward": 284.3e6 + 198.6e6}
 
 
@@ -465,7 +465,7 @@ def main():
                         "peak": hbm_peak if d["bound"] == "hbm" else fp32_peak, "unit": d["unit"], "frac": d["frac"],
                         "traffic": NCU_TRAFFIC_BYTES.get(dom), "ms": d["ms"],
                         "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full, "
-                                          "profiles/r01_ncu_full_summary.txt (same workload)",
+                                          "profiles/r01_ncu_packed_summary.txt (same workload)",
                         "peak_source": (f"{peak_kind} HBM copy" if d["bound"] == "hbm" else
                                         f"derived FP32 FMA peak {n_sm} SMs x 128 lanes x 2 x {sm_mhz:.0f} MHz (median SM clock "
                                         "under load); MEASURED_PEAKS.json holds no FP32 figure")}
@@ -473,7 +473,7 @@ def main():
     line["work"] = {"num_rendered": R, "visible": P_vis, "pairs_in_range": in_range, "pairs_blended": blended,
                     "reference_pairs_no_early_exit": ref_pairs, "tile_rejected_entries": tile_rej}
     depth_passes, tile_passes = 4, (max(1, (tiles - 1).bit_length()) + 7) // 8
-    line["gpu_launches"] = args.steps * (1 + 1 + 3 * depth_passes + 3 + 1 + 3 * tile_passes + 1 + 1 + 1 + 1)
+    line["gpu_launches"] = args.steps * (1 + 3 * depth_passes + 3 + 1 + 3 * tile_passes + 1 + 1 + 1 + 1)
     if world == 1 and not args.no_cpu_baseline:
         try:
             line["cpu_baseline"] = cpu_oracle_baseline(S, wl, S.make_camera(W, H))
