@@ -320,6 +320,7 @@ render_backward_packed_kernel(int W, int H, int grid_x, const uint2* __restrict_
     const float4* const my_row = reinterpret_cast<const float4*>(slab + lane * RED_STRIDE);
     int pending = 0;
     uint32_t pj = 0;    // slots of the pending entries, 8 bits each, newest in the low byte
+    float* park = slab + lane;   // where this lane parks the partials of the next entry
 
     auto flush_slab = [&]() {
         __syncwarp();
@@ -335,6 +336,7 @@ render_backward_packed_kernel(int W, int H, int grid_x, const uint2* __restrict_
         }
         __syncwarp();
         pending = 0;
+        park = slab + lane;
     };
 
     for (int base = 0; base < start; base += BWD_BATCH) {
@@ -432,25 +434,24 @@ render_backward_packed_kernel(int W, int H, int grid_x, const uint2* __restrict_
                     unpk(d, da, db);
                     d = pk(ca ? da : 0.f, cb ? db : 0.f);
                 }
-                // partials without their per-entry factors (applied in the batch flush):
-                //   0,1: d*(gdx*A + gdy*B), d*(gdy*C + gdx*B)    2,3,4: d*gdx*dx, d*gdx*dy, d*gdy*dy    5: G*d
-                const f32x2 gdx = mul2(G, bc(dx)), gdy = mul2(G, dy);
-                const f32x2 hx = mul2(d, gdx), hy = mul2(d, gdy);
+                // The six geometric partials are the moments of m0 = G*d over the pixel offsets: the mean and conic
+                // gradients are per-entry linear combinations of them (applied in the batch flush):
+                //   0,1: sum m0*dx, m0*dy    2,3,4: sum m0*dx*dx, m0*dx*dy, m0*dy*dy    5: sum m0
                 f32x2 v[10];
-                v[0] = mul2(d, fma2(gdy, bc(r1.y), mul2(gdx, bc(r1.x))));
-                v[1] = mul2(d, fma2(gdx, bc(r1.y), mul2(gdy, bc(r1.z))));
-                v[2] = mul2(hx, bc(dx));
-                v[3] = mul2(hx, dy);
-                v[4] = mul2(hy, dy);
                 v[5] = mul2(G, d);
+                v[0] = mul2(v[5], bc(dx));
+                v[1] = mul2(v[5], dy);
+                v[2] = mul2(v[0], bc(dx));
+                v[3] = mul2(v[0], dy);
+                v[4] = mul2(v[1], dy);
                 v[6] = mul2(aT, dLp0);
                 v[7] = mul2(aT, dLp1);
                 v[8] = mul2(aT, dLp2);
                 v[9] = HAS_DEPTH ? mul2(aT, dLd) : bc(0.f);
                 {
-                    float* dst = slab + pending * (NV * RED_STRIDE) + lane;
 #pragma unroll
-                    for (int k = 0; k < NV; k++) dst[k * RED_STRIDE] = lo(v[k]) + hi(v[k]);
+                    for (int k = 0; k < NV; k++) park[k * RED_STRIDE] = lo(v[k]) + hi(v[k]);
+                    park += NV * RED_STRIDE;      // running pointer: next pending entry's rows
                     pj = (pj << 8) | (uint32_t)j;
                     pending++;
                     if (pending == GROUP) flush_slab();
@@ -467,10 +468,13 @@ render_backward_packed_kernel(int W, int H, int grid_x, const uint2* __restrict_
             const bool nz = (a0.x != 0.f) | (a0.y != 0.f) | (a0.z != 0.f) | (a0.w != 0.f) | (a1.x != 0.f) |
                             (a1.y != 0.f) | (a1.z != 0.f) | (a1.w != 0.f) | (a2.x != 0.f) | (a2.y != 0.f);
             if (nz) {
-                const float o = sm.rec1[threadIdx.x].w;
-                const float nh = -0.5f * o;
-                a0.x *= nh * W;     // dL_dG = o*d ; dG/ddelx = -(gdx*A + gdy*B) ; ddelx/dx = W/2
-                a0.y *= nh * H;
+                // dL_dG = o*d;  dG/ddelx = -G (A dx + B dy), dG/ddely = -G (C dy + B dx);  ddelx/dx = W/2, ddely/dy = H/2
+                // dL/dconic = -1/2 o (sum m0 dx^2, sum m0 dx dy, sum m0 dy^2)
+                const float4 co = sm.rec1[threadIdx.x];
+                const float nh = -0.5f * co.w;
+                const float s1x = a0.x, s1y = a0.y;
+                a0.x = nh * W * (co.x * s1x + co.y * s1y);
+                a0.y = nh * H * (co.z * s1y + co.y * s1x);
                 a0.z *= nh;
                 a0.w *= nh;
                 a1.x *= nh;

@@ -205,8 +205,10 @@ render_forward_packed_kernel(int W, int H, int grid_x, const uint2* __restrict__
                 unpk(mul2(bc(r1.w), exp2x(pa, pb)), ala, alb);
                 ala = fminf(0.99f, ala);
                 alb = fminf(0.99f, alb);
-                const bool skip_a = (Ta < 0.f) || (pa > 0.0f) || (ala < 1.0f / 255.0f);
-                const bool skip_b = (Tb < 0.f) || (pb > 0.0f) || (alb < 1.0f / 255.0f);
+                // (a finished pixel, T < 0, needs no test of its own: T*(1-alpha) < 0 sends it down the `fin` path below,
+                //  which zeroes its alpha and keeps -|T|)
+                const bool skip_a = (pa > 0.0f) || (ala < 1.0f / 255.0f);
+                const bool skip_b = (pb > 0.0f) || (alb < 1.0f / 255.0f);
                 ala = skip_a ? 0.f : ala;
                 alb = skip_b ? 0.f : alb;
                 unpk(mul2(Tp, sub2(bc(1.f), pk(ala, alb))), tta, ttb);
