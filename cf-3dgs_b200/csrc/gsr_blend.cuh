@@ -54,7 +54,7 @@ __device__ __forceinline__ bool reject_rect(float X, float Y, float nBoC, float 
 // Stage one tile-list entry.  Also applies the rejection test for the whole tile.
 template <int N>
 __device__ __forceinline__ void stage_entry(StagedT<N>& sm, int slot, uint32_t gid, const GeomView& g, float tile_x0,
-                                            float tile_y0)
+                                            float tile_y0, float rect_h = (float)(TILE - 1))
 {
     const float2 xy = g.xy[gid];
     const float4 co = g.conic_op[gid];
@@ -67,7 +67,7 @@ __device__ __forceinline__ void stage_entry(StagedT<N>& sm, int slot, uint32_t g
         nBoC = -co.y / co.z;
         nBoA = -co.y / co.x;
         if (reject_rect(xy.x, xy.y, nBoC, nBoA, co.x, co.y, co.z, thr, tile_x0, tile_x0 + (TILE - 1), tile_y0,
-                        tile_y0 + (TILE - 1)))
+                        tile_y0 + rect_h))
             thr = -1.f;
     }
     sm.rec0[slot] = make_float4(xy.x, xy.y, nBoC, nBoA);

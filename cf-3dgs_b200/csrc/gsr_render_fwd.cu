@@ -133,7 +133,11 @@ render_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges
 #ifndef GSR_FWDP_MIN_BLOCKS
 #define GSR_FWDP_MIN_BLOCKS 8
 #endif
-constexpr int PK_THREADS = 128;
+#ifndef GSR_FWDP_WARPS
+#define GSR_FWDP_WARPS 4      // 4: one CTA per tile; 2: one CTA per 16x8 half tile (experiment)
+#endif
+constexpr int PK_WARPS = GSR_FWDP_WARPS;
+constexpr int PK_THREADS = 32 * PK_WARPS;
 constexpr int PK_FOOT = 8;
 
 __global__ void __launch_bounds__(PK_THREADS, GSR_FWDP_MIN_BLOCKS)
@@ -143,15 +147,18 @@ render_forward_packed_kernel(int W, int H, int grid_x, const uint2* __restrict__
                              float* __restrict__ out_alpha, uint32_t* __restrict__ n_contrib)
 {
     __shared__ Staged sm;
-    const int tile = blockIdx.x;
+    constexpr int PARTS = 4 / PK_WARPS;                 // CTAs per tile
+    const int tile = blockIdx.x / PARTS, part = blockIdx.x % PARTS;
     const int tile_x = tile % grid_x, tile_y = tile / grid_x;
-    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const unsigned lane = threadIdx.x & 31, warp = (threadIdx.x >> 5) + part * PK_WARPS;   // footprint index 0..3
     const int fx0 = tile_x * TILE + (warp & 1) * PK_FOOT, fy0 = tile_y * TILE + (warp >> 1) * PK_FOOT;
     const int pix_x = fx0 + (lane & 7), pix_ya = fy0 + (lane >> 3), pix_yb = pix_ya + 4;
     const float pxf = (float)pix_x;
     const f32x2 py2 = pk((float)pix_ya, (float)pix_yb);
     const float foot_x0 = (float)fx0, foot_y0 = (float)fy0;
-    const float tile_x0 = (float)(tile_x * TILE), tile_y0 = (float)(tile_y * TILE);
+    // the rectangle this CTA covers: the whole tile, or its upper / lower half
+    const float tile_x0 = (float)(tile_x * TILE), tile_y0 = (float)(tile_y * TILE + part * (TILE / PARTS));
+    const float rect_h = (float)(TILE / PARTS - 1);
 
     const uint2 range = ranges[tile];
     const int total = (int)(range.y - range.x);
@@ -168,7 +175,7 @@ render_forward_packed_kernel(int W, int H, int grid_x, const uint2* __restrict__
         if (__syncthreads_count(all_done()) == PK_THREADS) break;
         const int n = min(BATCH, total - base);
         for (int k = threadIdx.x; k < n; k += PK_THREADS)
-            stage_entry(sm, k, point_list[range.x + base + k], g, tile_x0, tile_y0);
+            stage_entry(sm, k, point_list[range.x + base + k], g, tile_x0, tile_y0, rect_h);
         __syncthreads();
 
         for (int c0 = 0; c0 < n; c0 += 32) {
@@ -369,7 +376,7 @@ void launch_render_forward(int W, int H, const uint2* ranges, const uint32_t* po
 {
     const int gx = div_up(W, TILE), gy = div_up(H, TILE);
     if (blend_packed())
-        render_forward_packed_kernel<<<gx * gy, PK_THREADS, 0, s>>>(W, H, gx, ranges, point_list, g, bg, out_color,
+        render_forward_packed_kernel<<<gx * gy * (4 / PK_WARPS), PK_THREADS, 0, s>>>(W, H, gx, ranges, point_list, g, bg, out_color,
                                                                     out_depth, out_alpha, n_contrib);
     else
         render_forward_kernel<<<gx * gy, BLEND_THREADS, 0, s>>>(W, H, gx, ranges, point_list, g, bg, out_color,
