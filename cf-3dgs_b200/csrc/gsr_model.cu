@@ -51,10 +51,12 @@ __global__ void gaussian_activate_kernel(int P, const float* __restrict__ opacit
 }
 
 __global__ void adam_features_kernel(size_t n, int floats_per_gaussian, float* __restrict__ p, const float* __restrict__ g,
-                                     float* __restrict__ m, float* __restrict__ v, float lr_dc, float lr_rest, AdamCfg c)
+                                     float* __restrict__ m, float* __restrict__ v, float lr_dc, float lr_rest, AdamCfg c,
+                                     const float* __restrict__ bias_dev)
 {
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
+    if (bias_dev) { c.inv_bias1 = bias_dev[0]; c.inv_sqrt_bias2 = bias_dev[1]; }
     const int k = (int)(i % (size_t)floats_per_gaussian);
     float mm = m[i], vv = v[i];
     p[i] = adam_update(p[i], g[i], mm, vv, k < 3 ? lr_dc : lr_rest, c);
@@ -72,10 +74,11 @@ struct GaussianStepArgs {
     float *grad_accum, *denom, *max_radii2D;   // optional (P)
 };
 
-__global__ void adam_gaussians_kernel(GaussianStepArgs a, AdamCfg c)
+__global__ void adam_gaussians_kernel(GaussianStepArgs a, AdamCfg c, const float* __restrict__ bias_dev)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= a.P) return;
+    if (bias_dev) { c.inv_bias1 = bias_dev[0]; c.inv_sqrt_bias2 = bias_dev[1]; }
 #pragma unroll
     for (int k = 0; k < 3; k++) {
         const int j = 3 * i + k;
@@ -155,14 +158,24 @@ extern "C" int gsr_gaussian_activate(int P, const float* opacity_raw, const floa
     return GSR_OK;
 }
 
-extern "C" int gsr_gaussian_adam_step(int P, int M, int step, float beta1, float beta2, float eps, const float* lrs_host,
-                                      float* xyz, float* features, float* opacity_raw, float* log_scale, float* rot_raw,
-                                      const float* d_xyz, const float* d_features, const float* d_opacity,
-                                      const float* d_scale, const float* d_rot, float* state, const float* d_means2D,
-                                      const int* radii, float* grad_accum, float* denom, float* max_radii2D, void* stream)
+// step counter kept on the device: [0] int64 step count, then two floats 1/(1-b1^t), 1/sqrt(1-b2^t)
+__global__ void adam_tick_kernel(long long* step_state, float b1, float b2)
+{
+    const long long t = step_state[0] + 1;
+    step_state[0] = t;
+    float* f = reinterpret_cast<float*>(step_state + 1);
+    f[0] = (float)(1.0 / (1.0 - pow((double)b1, (double)t)));
+    f[1] = (float)(1.0 / sqrt(1.0 - pow((double)b2, (double)t)));
+}
+
+static int adam_step_impl(int P, int M, int step, long long* step_state, float beta1, float beta2, float eps,
+                          const float* lrs_host, float* xyz, float* features, float* opacity_raw, float* log_scale,
+                          float* rot_raw, const float* d_xyz, const float* d_features, const float* d_opacity,
+                          const float* d_scale, const float* d_rot, float* state, const float* d_means2D,
+                          const int* radii, float* grad_accum, float* denom, float* max_radii2D, void* stream)
 {
     cudaStream_t s = (cudaStream_t)stream;
-    if (P < 0 || M < 0 || step < 1 || !lrs_host) { set_last_error("gsr_gaussian_adam_step: bad argument"); return GSR_ERR_INVALID; }
+    if (P < 0 || M < 0 || (!step_state && step < 1) || !lrs_host) { set_last_error("gsr_gaussian_adam_step: bad argument"); return GSR_ERR_INVALID; }
     if (P == 0) return GSR_OK;
     if (!xyz || !opacity_raw || !log_scale || !rot_raw || !d_xyz || !d_opacity || !d_scale || !d_rot || !state ||
         (M > 0 && (!features || !d_features))) {
@@ -171,8 +184,15 @@ extern "C" int gsr_gaussian_adam_step(int P, int M, int step, float beta1, float
     }
     AdamCfg c;
     c.b1 = beta1; c.b2 = beta2; c.eps = eps;
-    c.inv_bias1 = (float)(1.0 / (1.0 - std::pow((double)beta1, (double)step)));
-    c.inv_sqrt_bias2 = (float)(1.0 / std::sqrt(1.0 - std::pow((double)beta2, (double)step)));
+    c.inv_bias1 = c.inv_sqrt_bias2 = 1.f;
+    const float* bias_dev = nullptr;
+    if (step_state) {   // the step number lives on the device (the call can be captured in a CUDA graph and replayed)
+        adam_tick_kernel<<<1, 1, 0, s>>>(step_state, beta1, beta2);
+        bias_dev = reinterpret_cast<const float*>(step_state + 1);
+    } else {
+        c.inv_bias1 = (float)(1.0 / (1.0 - std::pow((double)beta1, (double)step)));
+        c.inv_sqrt_bias2 = (float)(1.0 / std::sqrt(1.0 - std::pow((double)beta2, (double)step)));
+    }
     // state layout: [m | v] for xyz(3P) opacity(P) scale(3P) rot(4P) features(3MP), in that order
     const size_t n = (size_t)P;
     float* st = state;
@@ -189,15 +209,39 @@ extern "C" int gsr_gaussian_adam_step(int P, int M, int step, float beta1, float
     a.lr_xyz = lrs_host[0]; a.lr_op = lrs_host[3]; a.lr_sc = lrs_host[4]; a.lr_rot = lrs_host[5];
     a.d_means2D = d_means2D; a.radii = radii; a.grad_accum = (d_means2D && radii && denom) ? grad_accum : nullptr;
     a.denom = denom; a.max_radii2D = max_radii2D;
-    adam_gaussians_kernel<<<div_up(P, 256), 256, 0, s>>>(a, c);
+    adam_gaussians_kernel<<<div_up(P, 256), 256, 0, s>>>(a, c, bias_dev);
     if (M > 0) {
         const size_t nf = (size_t)3 * M * n;
         adam_features_kernel<<<(unsigned)((nf + 255) / 256), 256, 0, s>>>(nf, 3 * M, features, d_features, m_f, v_f, lrs_host[1],
-                                                                      lrs_host[2], c);
+                                                                      lrs_host[2], c, bias_dev);
     }
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) { set_last_error(cudaGetErrorString(e)); return GSR_ERR_CUDA; }
     return GSR_OK;
+}
+
+extern "C" int gsr_gaussian_adam_step(int P, int M, int step, float beta1, float beta2, float eps, const float* lrs_host,
+                                      float* xyz, float* features, float* opacity_raw, float* log_scale, float* rot_raw,
+                                      const float* d_xyz, const float* d_features, const float* d_opacity,
+                                      const float* d_scale, const float* d_rot, float* state, const float* d_means2D,
+                                      const int* radii, float* grad_accum, float* denom, float* max_radii2D, void* stream)
+{
+    return adam_step_impl(P, M, step, nullptr, beta1, beta2, eps, lrs_host, xyz, features, opacity_raw, log_scale, rot_raw,
+                          d_xyz, d_features, d_opacity, d_scale, d_rot, state, d_means2D, radii, grad_accum, denom,
+                          max_radii2D, stream);
+}
+
+extern "C" int gsr_gaussian_adam_step_dev(int P, int M, int64_t* step_state, float beta1, float beta2, float eps,
+                                          const float* lrs_host, float* xyz, float* features, float* opacity_raw,
+                                          float* log_scale, float* rot_raw, const float* d_xyz, const float* d_features,
+                                          const float* d_opacity, const float* d_scale, const float* d_rot, float* state,
+                                          const float* d_means2D, const int* radii, float* grad_accum, float* denom,
+                                          float* max_radii2D, void* stream)
+{
+    if (!step_state) { set_last_error("gsr_gaussian_adam_step_dev: step_state is NULL"); return GSR_ERR_INVALID; }
+    return adam_step_impl(P, M, 0, reinterpret_cast<long long*>(step_state), beta1, beta2, eps, lrs_host, xyz, features,
+                          opacity_raw, log_scale, rot_raw, d_xyz, d_features, d_opacity, d_scale, d_rot, state, d_means2D,
+                          radii, grad_accum, denom, max_radii2D, stream);
 }
 
 extern "C" size_t gsr_gaussian_adam_state_floats(int P, int M)

@@ -38,6 +38,8 @@ SIGNATURES = {
     "gsr_gaussian_adam_state_floats": (c_size_t, [c_int, c_int]),
     "gsr_gaussian_adam_step": (c_int, [c_int, c_int, c_int, c_float, c_float, c_float, _P, _P, _P, _P, _P, _P, _P, _P, _P,
                                        _P, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "gsr_gaussian_adam_step_dev": (c_int, [c_int, c_int, _P, c_float, c_float, c_float, _P, _P, _P, _P, _P, _P, _P, _P, _P,
+                                           _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "gsr_mark_visible": (c_int, [c_int, _P, _P, _P, _P, _P]),
     "gsr_debug_dump": (c_int, [c_int, c_int, c_int, c_int64, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "gsr_profile_enable": (c_int, [c_int]),

@@ -20,7 +20,7 @@ LR_ORDER = ("xyz", "f_dc", "f_rest", "opacity", "scaling", "rotation")
 
 class FusedGaussianModel:
     def __init__(self, xyz, features, opacity_raw, log_scales, rot_raw, lrs: Dict[str, float], betas=(0.9, 0.999),
-                 eps: float = 1e-15):
+                 eps: float = 1e-15, device_step: bool = False):
         self.xyz = xyz.detach().contiguous().float().clone()
         self.features = features.detach().contiguous().float().clone()        # (P, M, 3), coefficient 0 = f_dc
         self.opacity_raw = opacity_raw.detach().contiguous().float().clone()  # (P, 1)
@@ -35,6 +35,9 @@ class FusedGaussianModel:
         self.denom = torch.zeros(self.P, device=dev)
         self.max_radii2D = torch.zeros(self.P, device=dev)
         self._act = None
+        # device_step: the step number lives in device memory (gsr_gaussian_adam_step_dev), so step() can be captured in
+        # a CUDA graph and replayed; step_count on the host is then only a call counter
+        self.step_state = torch.zeros(2, dtype=torch.int64, device=dev) if device_step else None
 
     def activated(self) -> Dict[str, torch.Tensor]:
         """opacities (P,1), scales (P,3), rotations (P,4) for the rasterizer (fresh tensors, no autograd history)."""
@@ -55,11 +58,15 @@ class FusedGaussianModel:
         lr = (ctypes.c_float * 6)(*[float(self.lrs[k]) for k in LR_ORDER])
         stats = d_means2D is not None and radii is not None
         p = lambda t: None if t is None else t.contiguous().data_ptr()
-        with torch.cuda.device(self.xyz.device):
-            check(lib.gsr_gaussian_adam_step(
-                self.P, self.M, self.step_count, float(self.betas[0]), float(self.betas[1]), float(self.eps), lr,
-                self.xyz.data_ptr(), self.features.data_ptr(), self.opacity_raw.data_ptr(), self.log_scales.data_ptr(),
+        tail = (self.xyz.data_ptr(), self.features.data_ptr(), self.opacity_raw.data_ptr(), self.log_scales.data_ptr(),
                 self.rot_raw.data_ptr(), p(d_xyz), p(d_features), p(d_opacities), p(d_scales), p(d_rotations),
                 self.state.data_ptr(), p(d_means2D) if stats else None, p(radii) if stats else None,
                 self.xyz_gradient_accum.data_ptr() if stats else None, self.denom.data_ptr() if stats else None,
-                self.max_radii2D.data_ptr() if stats else None, torch.cuda.current_stream().cuda_stream))
+                self.max_radii2D.data_ptr() if stats else None, torch.cuda.current_stream().cuda_stream)
+        with torch.cuda.device(self.xyz.device):
+            if self.step_state is not None:
+                check(lib.gsr_gaussian_adam_step_dev(self.P, self.M, self.step_state.data_ptr(), float(self.betas[0]),
+                                                     float(self.betas[1]), float(self.eps), lr, *tail))
+            else:
+                check(lib.gsr_gaussian_adam_step(self.P, self.M, self.step_count, float(self.betas[0]),
+                                                 float(self.betas[1]), float(self.eps), lr, *tail))

@@ -48,6 +48,8 @@ def main():
     ap.add_argument("--sh-degree", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--loss", default=None, choices=["fused", "torch"])
+    ap.add_argument("--graph", action="store_true",
+                    help="sync-free forward + one CUDA graph per training view holding the whole iteration (ours, fused model)")
     ap.add_argument("--model", default=None, choices=["fused", "torch"],
                     help="fused activation/Adam/statistics kernels (default for ours) or torch.optim.Adam + autograd")
     args = ap.parse_args()
@@ -102,10 +104,13 @@ def main():
         import gsr_model
         fused_model = gsr_model.FusedGaussianModel(
             xyz, torch.cat([f_dc, f_rest], 1), opa_raw, log_s, rot,
-            dict(xyz=0.00016, f_dc=0.0025, f_rest=0.000125, opacity=0.05, scaling=0.005, rotation=0.001))
+            dict(xyz=0.00016, f_dc=0.0025, f_rest=0.000125, opacity=0.05, scaling=0.005, rotation=0.001),
+            device_step=bool(args.graph))
 
     def fused_iteration(k):
-        f = int(order[k])
+        return fused_iteration_frame(int(order[k]))
+
+    def fused_iteration_frame(f):
         m = fused_model
         act = m.activated()
         x = m.xyz.detach().requires_grad_(True)
@@ -130,17 +135,50 @@ def main():
         opt.step(); opt.zero_grad(set_to_none=True)
         return loss
 
-    for k in range(10):
-        first = iteration(k)
-    torch.cuda.synchronize(dev)
-    t0 = time.time()
-    for k in range(10, 10 + args.iters):
-        loss = iteration(k)
-    torch.cuda.synchronize(dev)
-    dt = time.time() - t0
+    overflow = None
+    if args.graph:
+        if fused_model is None:
+            raise SystemExit("--graph needs --impl ours --model fused")
+        import diff_gaussian_rasterization as D
+        D.set_sync_free(True, slack=2.0)
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for f in range(args.frames):     # learns the binning capacity over all views (raised if a view needs more)
+                first = fused_iteration_frame(f)
+            for k in range(10):
+                first = iteration(k)
+        torch.cuda.current_stream().wait_stream(side)
+        D.sync_free_status()
+        graphs = []
+        for f in range(args.frames):
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                lf = fused_iteration_frame(f)
+            graphs.append((g, lf))
+        torch.cuda.synchronize(dev)
+        t0 = time.time()
+        for k in range(10, 10 + args.iters):
+            g, loss = graphs[int(order[k])]
+            g.replay()
+        torch.cuda.synchronize(dev)
+        dt = time.time() - t0
+        st = D.sync_free_status()
+        overflow = bool(st[1]) if st else None
+    else:
+        for k in range(10):
+            first = iteration(k)
+        torch.cuda.synchronize(dev)
+        t0 = time.time()
+        for k in range(10, 10 + args.iters):
+            loss = iteration(k)
+        torch.cuda.synchronize(dev)
+        dt = time.time() - t0
     line = {"workload": "cf3dgs_global_steps", "impl": args.impl, "loss": args.loss, "model": args.model, "P": P, "frames": args.frames, "W": W, "H": H,
             "sh_degree": args.sh_degree, "iters": args.iters, "iters_per_s": args.iters / dt, "ms_per_iter": dt / args.iters * 1e3,
-            "first_loss": float(first.detach()), "last_loss": float(loss.detach())}
+            "first_loss": float(first.detach()), "last_loss": float(loss.detach()), "graph": bool(args.graph)}
+    if overflow is not None:
+        line["binning_overflow"] = overflow
     os.write(real_stdout, (json.dumps(line) + "\n").encode())
 
 

@@ -54,3 +54,37 @@ def test_fused_model_step_matches_torch_adam_through_the_activations():
         assert float((a - b.detach()).abs().max()) <= 2e-5 * max(1e-2, float((b.detach() - 0).abs().max())) + 1e-6
     assert float((model.xyz_gradient_accum - accum[:, 0]).abs().max()) <= 1e-4
     assert torch.equal(model.denom, denom[:, 0]) and torch.equal(model.max_radii2D, maxr)
+
+
+def test_device_side_step_counter_matches_the_host_one_and_replays_in_a_graph():
+    """gsr_gaussian_adam_step_dev keeps the step number on the device: same updates as the host-counted call, also
+    when the step is captured once in a CUDA graph and replayed."""
+    import gsr_model
+    P, M = 3000, 16
+    g = torch.Generator().manual_seed(4)
+    init = [torch.randn(P, 3, generator=g), torch.randn(P, M, 3, generator=g) * 0.2, torch.randn(P, 1, generator=g),
+            torch.randn(P, 3, generator=g) * 0.3 - 3, torch.randn(P, 4, generator=g)]
+    lrs = dict(xyz=1e-3, f_dc=2e-3, f_rest=1e-4, opacity=0.05, scaling=5e-3, rotation=1e-3)
+    host = gsr_model.FusedGaussianModel(*[t.to(DEV) for t in init], lrs)
+    dev_eager = gsr_model.FusedGaussianModel(*[t.to(DEV) for t in init], lrs, device_step=True)
+    dev_graph = gsr_model.FusedGaussianModel(*[t.to(DEV) for t in init], lrs, device_step=True)
+    grads = [torch.randn(P, 3, generator=g).to(DEV), (torch.randn(P, M, 3, generator=g) * 0.1).to(DEV),
+             torch.randn(P, 1, generator=g).to(DEV), torch.randn(P, 3, generator=g).to(DEV), torch.randn(P, 4, generator=g).to(DEV)]
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        dev_graph.step(*grads)                      # step 1 eagerly (warm-up outside the capture)
+    torch.cuda.current_stream().wait_stream(side)
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        dev_graph.step(*grads)                      # step 2 is captured and executed by the first replay
+    for _ in range(6):
+        host.step(*grads); dev_eager.step(*grads)
+    for _ in range(5):
+        graph.replay()                               # steps 2..6
+    torch.cuda.synchronize()
+    assert int(dev_eager.step_state[0]) == 6 and int(dev_graph.step_state[0]) == 6
+    for name in ["xyz", "features", "opacity_raw", "log_scales", "rot_raw", "state"]:
+        a, b, c = getattr(host, name), getattr(dev_eager, name), getattr(dev_graph, name)
+        assert torch.equal(a, b), name
+        assert torch.equal(a, c), name
