@@ -118,3 +118,15 @@ def test_runs_on_a_side_stream():
         out, _, _ = cuda_forward(sc, cam, (0, 0, 0))
     s.synchronize()
     assert torch.equal(out["color"], ref["color"])
+
+
+def test_graft_entry_smoke_runs():
+    """The driver's smoke entry point (one small fwd+bwd checked against the oracle) must stay runnable."""
+    import importlib
+    import os
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    if root not in sys.path:
+        sys.path.insert(0, root)
+    g = importlib.import_module("__graft_entry__")
+    g.smoke()
