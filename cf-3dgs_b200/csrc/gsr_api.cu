@@ -178,6 +178,19 @@ int gsr_forward_prepare(int P, int sh_degree, int M, const float* means3D, const
                         float tanfovx, float tanfovy, int prefiltered, int* radii, void* geometry,
                         size_t geometry_bytes, int64_t* num_rendered_host, void* stream, int debug)
 {
+    return gsr_forward_prepare_rigid(P, sh_degree, M, means3D, scales, scale_modifier, rotations, opacities, shs,
+                                     cov3D_precomp, colors_precomp, viewmatrix, projmatrix, campos, W, H, tanfovx, tanfovy,
+                                     prefiltered, radii, geometry, geometry_bytes, num_rendered_host, nullptr, stream, debug);
+}
+
+int gsr_forward_prepare_rigid(int P, int sh_degree, int M, const float* means3D, const float* scales,
+                              float scale_modifier, const float* rotations, const float* opacities,
+                              const float* shs, const float* cov3D_precomp, const float* colors_precomp,
+                              const float* viewmatrix, const float* projmatrix, const float* campos, int W, int H,
+                              float tanfovx, float tanfovy, int prefiltered, int* radii, void* geometry,
+                              size_t geometry_bytes, int64_t* num_rendered_host, const float* rigid, void* stream,
+                              int debug)
+{
     cudaStream_t s = (cudaStream_t)stream;
     if (!num_rendered_host) return fail(GSR_ERR_INVALID, "num_rendered_host is NULL");
     *num_rendered_host = 0;
@@ -194,6 +207,7 @@ int gsr_forward_prepare(int P, int sh_degree, int M, const float* means3D, const
     a.opacities = opacities; a.shs = shs; a.cov3D_precomp = cov3D_precomp; a.colors_precomp = colors_precomp;
     a.viewmatrix = viewmatrix; a.projmatrix = projmatrix; a.campos = campos ? campos : viewmatrix;
     a.W = W; a.H = H; a.tanfovx = tanfovx; a.tanfovy = tanfovy; a.prefiltered = prefiltered; a.radii = radii;
+    a.rigid = rigid;
     { StageTimer t(ST_PREPROCESS, s); launch_preprocess(a, g, s); }
     GSR_STAGE("preprocess");
 
@@ -248,6 +262,20 @@ int gsr_forward_fused(int P, int sh_degree, int M, const float* means3D, const f
                       int64_t capacity, void* image, float* out_color, float* out_depth, float* out_alpha,
                       int64_t* status, void* stream, int debug)
 {
+    return gsr_forward_fused_rigid(P, sh_degree, M, means3D, scales, scale_modifier, rotations, opacities, shs,
+                                   cov3D_precomp, colors_precomp, viewmatrix, projmatrix, campos, W, H, tanfovx, tanfovy,
+                                   background, radii, geometry, geometry_bytes, binning, binning_bytes, capacity, image,
+                                   out_color, out_depth, out_alpha, status, nullptr, stream, debug);
+}
+
+int gsr_forward_fused_rigid(int P, int sh_degree, int M, const float* means3D, const float* scales, float scale_modifier,
+                            const float* rotations, const float* opacities, const float* shs,
+                            const float* cov3D_precomp, const float* colors_precomp, const float* viewmatrix,
+                            const float* projmatrix, const float* campos, int W, int H, float tanfovx, float tanfovy,
+                            const float* background, int* radii, void* geometry, size_t geometry_bytes, void* binning,
+                            size_t binning_bytes, int64_t capacity, void* image, float* out_color, float* out_depth,
+                            float* out_alpha, int64_t* status, const float* rigid, void* stream, int debug)
+{
     cudaStream_t s = (cudaStream_t)stream;
     if (!out_color || !out_depth || !out_alpha || !status) return fail(GSR_ERR_INVALID, "outputs and status are required");
     if (capacity < 1 || capacity > 0x7fffffffll) return fail(GSR_ERR_INVALID, "capacity out of range");
@@ -271,6 +299,7 @@ int gsr_forward_fused(int P, int sh_degree, int M, const float* means3D, const f
     a.opacities = opacities; a.shs = shs; a.cov3D_precomp = cov3D_precomp; a.colors_precomp = colors_precomp;
     a.viewmatrix = viewmatrix; a.projmatrix = projmatrix; a.campos = campos ? campos : viewmatrix;
     a.W = W; a.H = H; a.tanfovx = tanfovx; a.tanfovy = tanfovy; a.prefiltered = 0; a.radii = radii;
+    a.rigid = rigid;
     { StageTimer t(ST_PREPROCESS, s); launch_preprocess(a, g, s); }
     GSR_STAGE("preprocess");
     launch_publish_status(g.counters, capacity, (long long*)status, s);
@@ -290,6 +319,24 @@ int gsr_backward(int P, int sh_degree, int M, int W, int H, int64_t num_rendered
                  float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh,
                  float* dL_dscales, float* dL_drotations, float* dL_dpose, void* pose_scratch, void* stream,
                  int debug)
+{
+    return gsr_backward_rigid(P, sh_degree, M, W, H, num_rendered, background, means3D, radii, colors_precomp, scales,
+                              rotations, scale_modifier, cov3D_precomp, viewmatrix, projmatrix, campos, tanfovx, tanfovy,
+                              shs, out_alpha, dL_dout_color, dL_dout_depth, dL_dout_alpha, geometry, binning, image,
+                              grad_scratch, dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh,
+                              dL_dscales, dL_drotations, dL_dpose, pose_scratch, nullptr, stream, debug);
+}
+
+int gsr_backward_rigid(int P, int sh_degree, int M, int W, int H, int64_t num_rendered, const float* background,
+                       const float* means3D, const int* radii, const float* colors_precomp, const float* scales,
+                       const float* rotations, float scale_modifier, const float* cov3D_precomp,
+                       const float* viewmatrix, const float* projmatrix, const float* campos, float tanfovx,
+                       float tanfovy, const float* shs, const float* out_alpha, const float* dL_dout_color,
+                       const float* dL_dout_depth, const float* dL_dout_alpha, const void* geometry,
+                       const void* binning, const void* image, void* grad_scratch, float* dL_dmeans2D,
+                       float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh,
+                       float* dL_dscales, float* dL_drotations, float* dL_dpose, void* pose_scratch,
+                       const float* rigid, void* stream, int debug)
 {
     cudaStream_t s = (cudaStream_t)stream;
     if (P == 0) {
@@ -331,6 +378,7 @@ int gsr_backward(int P, int sh_degree, int M, int W, int H, int64_t num_rendered
     a.dL_dmeans3D = dL_dmeans3D; a.dL_dcov3D = dL_dcov3D; a.dL_dsh = shs ? dL_dsh : nullptr;
     a.dL_dscales = scales ? dL_dscales : nullptr; a.dL_drotations = scales ? dL_drotations : nullptr;
     a.dL_dpose = dL_dpose; a.pose_scratch = (float*)pose_scratch;
+    a.rigid = rigid;
     { StageTimer t(ST_PREPROCESS_BWD, s); launch_preprocess_backward(a, g, s); }
     GSR_STAGE("preprocess backward");
     return GSR_OK;

@@ -5,6 +5,7 @@
 namespace gsr {
 
 struct PreprocessArgs {
+    const float* rigid = nullptr;   // optional 3x4 row-major [R | t]: means3D are moved by p' = R p + t first
     int P, D, M;
     const float* means3D;
     const float* scales;
@@ -64,6 +65,7 @@ void launch_render_backward(int W, int H, const uint2* ranges, const uint32_t* p
                             float* grad_scratch, cudaStream_t s);
 
 struct PreprocessBwdArgs {
+    const float* rigid = nullptr;   // same transform as the forward; dL_dmeans3D is then w.r.t. the raw points
     int P, D, M;
     const float* means3D;
     const int* radii;

@@ -21,6 +21,15 @@ __device__ __forceinline__ float xform_row(const float* __restrict__ m, int r, f
     return __fadd_rn(t, m[12 + r]);
 }
 
+// p' = R p + t for a 3x4 row-major [R | t]; one fixed rounding sequence shared by forward and backward
+__device__ __forceinline__ void rigid_apply(const float* __restrict__ T, float& x, float& y, float& z)
+{
+    const float nx = __fmaf_rn(T[2], z, __fmaf_rn(T[1], y, __fmaf_rn(T[0], x, T[3])));
+    const float ny = __fmaf_rn(T[6], z, __fmaf_rn(T[5], y, __fmaf_rn(T[4], x, T[7])));
+    const float nz = __fmaf_rn(T[10], z, __fmaf_rn(T[9], y, __fmaf_rn(T[8], x, T[11])));
+    x = nx; y = ny; z = nz;
+}
+
 // Sigma = (S R)^T (S R) from scale * modifier and the un-normalised quaternion (w,x,y,z).
 __device__ __forceinline__ void cov3d_from_scale_rot(float s0, float s1, float s2, float mod, float4 q, float* c3)
 {

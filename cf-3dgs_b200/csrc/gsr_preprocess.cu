@@ -41,7 +41,8 @@ preprocess_kernel(PreprocessArgs a, GeomView g)
     if (idx < a.P) {
         int radius = 0;
         uint32_t depth_key = CULLED_KEY;
-        const float px = a.means3D[3 * idx], py = a.means3D[3 * idx + 1], pz = a.means3D[3 * idx + 2];
+        float px = a.means3D[3 * idx], py = a.means3D[3 * idx + 1], pz = a.means3D[3 * idx + 2];
+        if (a.rigid) rigid_apply(a.rigid, px, py, pz);
         const float depth = xform_row(sV, 2, px, py, pz);
         if (!(depth <= 0.2f)) {  // auxiliary.h:154 (NaN depth is not culled there either)
             const float hw = xform_row(sP, 3, px, py, pz);

@@ -81,6 +81,7 @@ preprocess_backward_kernel(PreprocessBwdArgs a, GeomView g)
             dcol0 = q1.z; dcol1 = q1.w; dcol2 = q2.x;
             const float ddepth = q2.y;
             px = a.means3D[3 * idx]; py = a.means3D[3 * idx + 1]; pz = a.means3D[3 * idx + 2];
+            if (a.rigid) rigid_apply(a.rigid, px, py, pz);
             float c3[6];
             float4 rq = make_float4(0.f, 0.f, 0.f, 0.f);
             float sc0 = 0.f, sc1 = 0.f, sc2 = 0.f;
@@ -268,9 +269,16 @@ preprocess_backward_kernel(PreprocessBwdArgs a, GeomView g)
         a.dL_dmeans2D[3 * idx + 1] = dmean2y;
         a.dL_dmeans2D[3 * idx + 2] = 0.f;
         a.dL_dopacity[idx] = dopac;
-        a.dL_dmeans3D[3 * idx] = gmx;
-        a.dL_dmeans3D[3 * idx + 1] = gmy;
-        a.dL_dmeans3D[3 * idx + 2] = gmz;
+        if (a.rigid) {   // gradient w.r.t. the raw point: R^T g  (the pose partials below keep using p' and g)
+            const float* T = a.rigid;
+            a.dL_dmeans3D[3 * idx] = T[0] * gmx + T[4] * gmy + T[8] * gmz;
+            a.dL_dmeans3D[3 * idx + 1] = T[1] * gmx + T[5] * gmy + T[9] * gmz;
+            a.dL_dmeans3D[3 * idx + 2] = T[2] * gmx + T[6] * gmy + T[10] * gmz;
+        } else {
+            a.dL_dmeans3D[3 * idx] = gmx;
+            a.dL_dmeans3D[3 * idx + 1] = gmy;
+            a.dL_dmeans3D[3 * idx + 2] = gmz;
+        }
         if (a.dL_dcolors) {
             a.dL_dcolors[3 * idx] = dcol0;
             a.dL_dcolors[3 * idx + 1] = dcol1;

@@ -131,8 +131,9 @@ def _dense(t: torch.Tensor, name: str) -> torch.Tensor:
 
 
 def _forward_impl(bg, means3D, colors_precomp, opacities, scales, rotations, scale_modifier, cov3Ds_precomp,
-                  viewmatrix, projmatrix, tanfovx, tanfovy, H, W, sh, degree, campos, prefiltered, debug):
-    """Counterpart of _C.rasterize_gaussians (rasterize_points.cu:35-119); same return tuple."""
+                  viewmatrix, projmatrix, tanfovx, tanfovy, H, W, sh, degree, campos, prefiltered, debug, rigid=None):
+    """Counterpart of _C.rasterize_gaussians (rasterize_points.cu:35-119); same return tuple.
+    rigid (optional, 12 floats on the device, row-major 3x4 [R | t]): the kernels move means3D by it first."""
     if means3D.ndim != 2 or means3D.shape[1] != 3:
         raise RuntimeError("means3D must have dimensions (num_points, 3)")
     dev = means3D.device
@@ -165,13 +166,13 @@ def _forward_impl(bg, means3D, colors_precomp, opacities, scales, rotations, sca
             cap = _SyncFree.capacity[di]
             binning = torch.empty(lib.gsr_binning_bytes(cap, W, H), **u8)
             status = torch.empty(2, dtype=torch.int64, device=dev)
-            check(lib.gsr_forward_fused(
+            check(lib.gsr_forward_fused_rigid(
                 P, int(degree), int(M), _ptr(means3D), _ptr(scales), float(scale_modifier), _ptr(rotations),
                 _ptr(opacities), _ptr(sh), _ptr(cov3Ds_precomp), _ptr(colors_precomp), _ptr(viewmatrix),
                 _ptr(projmatrix), _ptr(campos), int(W), int(H), float(tanfovx), float(tanfovy), _ptr(bg),
                 radii.data_ptr(), geom.data_ptr(), geom.numel(), binning.data_ptr(), binning.numel(), cap,
-                img.data_ptr(), color.data_ptr(), depth.data_ptr(), alpha.data_ptr(), status.data_ptr(), stream,
-                int(bool(debug))))
+                img.data_ptr(), color.data_ptr(), depth.data_ptr(), alpha.data_ptr(), status.data_ptr(),
+                None if rigid is None else rigid.data_ptr(), stream, int(bool(debug))))
             _SyncFree.device_status[di] = status
             if not capturing and di not in _SyncFree.pending:
                 pinned = torch.empty(2, dtype=torch.int64).pin_memory()
@@ -181,11 +182,12 @@ def _forward_impl(bg, means3D, colors_precomp, opacities, scales, rotations, sca
                 _SyncFree.pending[di] = (ev, pinned, status)
             return cap, color, depth, alpha, radii, geom, binning, img
         word = _count_word(dev)
-        check(lib.gsr_forward_prepare(
+        check(lib.gsr_forward_prepare_rigid(
             P, int(degree), int(M), _ptr(means3D), _ptr(scales), float(scale_modifier), _ptr(rotations),
             _ptr(opacities), _ptr(sh), _ptr(cov3Ds_precomp), _ptr(colors_precomp), _ptr(viewmatrix),
             _ptr(projmatrix), _ptr(campos), int(W), int(H), float(tanfovx), float(tanfovy), int(bool(prefiltered)),
-            radii.data_ptr(), geom.data_ptr(), geom.numel(), word.data_ptr(), stream, int(bool(debug))))
+            radii.data_ptr(), geom.data_ptr(), geom.numel(), word.data_ptr(),
+            None if rigid is None else rigid.data_ptr(), stream, int(bool(debug))))
         R = int(word[0])
         if _SyncFree.enabled:
             _SyncFree.capacity[di] = max(_SyncFree.capacity.get(di, 0), int(R * _SyncFree.slack) + 1024)
@@ -199,7 +201,7 @@ def _forward_impl(bg, means3D, colors_precomp, opacities, scales, rotations, sca
 
 def _backward_impl(bg, means3D, radii, colors_precomp, scales, rotations, scale_modifier, cov3Ds_precomp,
                    viewmatrix, projmatrix, tanfovx, tanfovy, grad_color, grad_depth, grad_alpha, sh, degree,
-                   campos, geom, R, binning, img, alpha, debug, want_pose_grad=False):
+                   campos, geom, R, binning, img, alpha, debug, want_pose_grad=False, rigid=None):
     """Counterpart of _C.rasterize_gaussians_backward (rasterize_points.cu:121-208).  Returns the same eight
     gradients (None where the matching input was absent) plus the optional fused pose gradient."""
     dev = means3D.device
@@ -227,14 +229,14 @@ def _backward_impl(bg, means3D, radii, colors_precomp, scales, rotations, scale_
         stream = torch.cuda.current_stream().cuda_stream
         scratch = torch.empty(P * 12, **f32)
         pose_scratch = torch.empty(lib.gsr_pose_scratch_bytes(P) // 4, **f32) if want_pose_grad else None
-        check(lib.gsr_backward(
+        check(lib.gsr_backward_rigid(
             P, int(degree), int(M), int(W), int(H), int(R), _ptr(bg), _ptr(means3D), radii.data_ptr(),
             _ptr(colors_precomp), _ptr(scales), _ptr(rotations), float(scale_modifier), _ptr(cov3Ds_precomp),
             _ptr(viewmatrix), _ptr(projmatrix), _ptr(campos), float(tanfovx), float(tanfovy), _ptr(sh),
             alpha.data_ptr(), grad_color.data_ptr(), _ptr(grad_depth), _ptr(grad_alpha), geom.data_ptr(),
             binning.data_ptr(), img.data_ptr(), scratch.data_ptr(), dmeans2D.data_ptr(), _ptr(dcolors),
             dopacity.data_ptr(), dmeans3D.data_ptr(), _ptr(dcov3D), _ptr(dsh), _ptr(dscales), _ptr(drots),
-            _ptr(dpose), _ptr(pose_scratch), stream, int(bool(debug))))
+            _ptr(dpose), _ptr(pose_scratch), None if rigid is None else rigid.data_ptr(), stream, int(bool(debug))))
     return dmeans2D, dcolors, dopacity, dmeans3D, dcov3D, dsh, dscales, drots, dpose
 
 

@@ -26,6 +26,14 @@ SIGNATURES = {
     "gsr_forward_fused": (c_int, [c_int, c_int, c_int, _P, _P, c_float, _P, _P, _P, _P, _P, _P, _P, _P, c_int, c_int,
                                   c_float, c_float, _P, _P, _P, c_size_t, _P, c_size_t, c_int64, _P, _P, _P, _P, _P, _P,
                                   c_int]),
+    "gsr_forward_prepare_rigid": (c_int, [c_int, c_int, c_int, _P, _P, c_float, _P, _P, _P, _P, _P, _P, _P, _P,
+                                          c_int, c_int, c_float, c_float, c_int, _P, _P, c_size_t, _P, _P, _P, c_int]),
+    "gsr_forward_fused_rigid": (c_int, [c_int, c_int, c_int, _P, _P, c_float, _P, _P, _P, _P, _P, _P, _P, _P, c_int, c_int,
+                                        c_float, c_float, _P, _P, _P, c_size_t, _P, c_size_t, c_int64, _P, _P, _P, _P, _P,
+                                        _P, _P, c_int]),
+    "gsr_backward_rigid": (c_int, [c_int, c_int, c_int, c_int, c_int, c_int64, _P, _P, _P, _P, _P, _P, c_float, _P, _P,
+                                   _P, _P, c_float, c_float, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P,
+                                   _P, _P, _P, _P, _P, _P, c_int]),
     "gsr_pose_scratch_bytes": (c_size_t, [c_int]),
     "gsr_backward": (c_int, [c_int, c_int, c_int, c_int, c_int, c_int64, _P, _P, _P, _P, _P, _P, c_float, _P, _P,
                              _P, _P, c_float, c_float, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P,

@@ -52,35 +52,37 @@ def se3_exp_closed(xi: torch.Tensor) -> torch.Tensor:
 
 
 class _PoseRasterize(torch.autograd.Function):
-    """means3D = T[:3,:3] @ xyz + T[:3,3]; gradient w.r.t. the twist `xi` (evaluated at xi = 0) is the fused
-    dL_dpose; gradients w.r.t. the Gaussian parameters flow as in the plain rasterizer."""
+    """Renders xyz moved by T: the per-Gaussian kernels apply p' = T[:3,:3] p + T[:3,3] themselves (gsr_*_rigid, include/gsr.h),
+    so there is no transformed copy of the points and no PyTorch op on the P x 3 tensor in either direction.  The
+    gradient w.r.t. the twist `xi` (evaluated at xi = 0) is the fused dL_dpose; the gradient w.r.t. xyz comes back from
+    the kernel already rotated into the frame of the raw points."""
 
     @staticmethod
     def forward(ctx, xi, xyz, T, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, rs):
-        means3D = (xyz @ T[:3, :3].t() + T[:3, 3]).contiguous()
-        out = D._forward_impl(rs.bg, means3D, colors_precomp, opacities, scales, rotations, rs.scale_modifier,
+        rigid = T[:3, :4].to(torch.float32).contiguous()
+        out = D._forward_impl(rs.bg, xyz, colors_precomp, opacities, scales, rotations, rs.scale_modifier,
                               cov3Ds_precomp, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, rs.image_height,
-                              rs.image_width, sh, rs.sh_degree, rs.campos, rs.prefiltered, rs.debug)
+                              rs.image_width, sh, rs.sh_degree, rs.campos, rs.prefiltered, rs.debug, rigid=rigid)
         R, color, depth, alpha, radii, geom, binning, img = out
         ctx.rs, ctx.R = rs, R
         ctx.set_materialize_grads(False)
         ctx.mark_non_differentiable(radii)
-        ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, geom, binning, img,
-                              alpha, T)
+        ctx.save_for_backward(colors_precomp, xyz, scales, rotations, cov3Ds_precomp, radii, sh, geom, binning, img,
+                              alpha, rigid)
         return color, radii, depth, alpha
 
     @staticmethod
     def backward(ctx, grad_color, grad_radii, grad_depth, grad_alpha):
         rs = ctx.rs
-        colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, geom, binning, img, alpha, T = ctx.saved_tensors
+        colors_precomp, xyz, scales, rotations, cov3Ds_precomp, radii, sh, geom, binning, img, alpha, rigid = ctx.saved_tensors
         if grad_color is None:
-            grad_color = torch.zeros((3, rs.image_height, rs.image_width), dtype=torch.float32, device=means3D.device)
-        res = D._backward_impl(rs.bg, means3D, radii, colors_precomp, scales, rotations, rs.scale_modifier, cov3Ds_precomp,
+            grad_color = torch.zeros((3, rs.image_height, rs.image_width), dtype=torch.float32, device=xyz.device)
+        res = D._backward_impl(rs.bg, xyz, radii, colors_precomp, scales, rotations, rs.scale_modifier, cov3Ds_precomp,
                                rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, grad_color, grad_depth, grad_alpha,
-                               sh, rs.sh_degree, rs.campos, geom, ctx.R, binning, img, alpha, rs.debug, want_pose_grad=True)
-        dmeans2D, dcolors, dopacity, dmeans3D, dcov3D, dsh, dscales, drots, dpose = res
-        dxyz = dmeans3D @ T[:3, :3] if ctx.needs_input_grad[1] else None
-        return dpose, dxyz, None, dsh, dcolors, dopacity, dscales, drots, dcov3D, None
+                               sh, rs.sh_degree, rs.campos, geom, ctx.R, binning, img, alpha, rs.debug, want_pose_grad=True,
+                               rigid=rigid)
+        dmeans2D, dcolors, dopacity, dxyz, dcov3D, dsh, dscales, drots, dpose = res
+        return dpose, (dxyz if ctx.needs_input_grad[1] else None), None, dsh, dcolors, dopacity, dscales, drots, dcov3D, None
 
 
 def rasterize_with_pose(raster_settings, xi, xyz, T, opacities, shs=None, colors_precomp=None, scales=None,
