@@ -257,7 +257,7 @@ render_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ range
 //    batch flush instead of once per pixel pair.
 //  * The two pixels of a lane are added before the slab reduction, so that reduction runs once per 64 pixels.
 #ifndef GSR_BWDP_MIN_BLOCKS
-#define GSR_BWDP_MIN_BLOCKS 7
+#define GSR_BWDP_MIN_BLOCKS 6
 #endif
 
 template <bool HAS_DEPTH, bool HAS_ALPHA>
@@ -388,9 +388,7 @@ render_backward_packed_kernel(int W, int H, int grid_x, const uint2* __restrict_
                 alb = fminf(0.99f, alb);
                 const bool ca = (pos < last_a) && !(pa > 0.0f) && !(ala < 1.0f / 255.0f);
                 const bool cb = (pos < last_b) && !(pb > 0.0f) && !(alb < 1.0f / 255.0f);
-#ifndef GSR_BWDP_NO_ANY
                 if (!__any_sync(0xffffffffu, ca || cb)) continue;
-#endif
                 const f32x2 al = pk(ca ? ala : 0.f, cb ? alb : 0.f);
 
                 // T <- T / (1 - alpha): reciprocal seed + one residual correction
