@@ -110,7 +110,49 @@ def run_pair(p, args, dev, backend):
         loss.backward()
         return loss
 
-    if args.graph:
+    fused_model = None
+    if args.model == "fused":
+        # activations + their chain rule + Adam in the library's fused model step (gsr_model.py) instead of PyTorch ops
+        import gsr_model
+        import diff_gaussian_rasterization as D
+        fused_model = gsr_model.FusedGaussianModel(
+            xyz, torch.cat([f_dc, f_rest], 1), opa_raw, log_s, rot,
+            dict(xyz=0.0, f_dc=0.0025, f_rest=0.000125, opacity=0.05, scaling=0.005, rotation=0.001),
+            device_step=bool(args.graph))
+
+        def fit_iteration_fused():
+            mdl = fused_model
+            act = mdl.activated()
+            x = mdl.xyz.detach().requires_grad_(True)
+            sh = mdl.features.detach().requires_grad_(True)
+            o, sc_, r = act["opacities"].requires_grad_(True), act["scales"].requires_grad_(True), act["rotations"].requires_grad_(True)
+            m2d = torch.zeros_like(x, requires_grad=True)
+            img = D.GaussianRasterizer(rs)(x, m2d, o, shs=sh, scales=sc_, rotations=r)[0]
+            loss = loss_fn(img, frame0, window)
+            loss.backward()
+            mdl.step(x.grad, sh.grad, o.grad, sc_.grad, r.grad)
+            return loss
+
+    if fused_model is not None and args.graph:
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(3):
+                fit_iteration_fused()
+        torch.cuda.current_stream().wait_stream(side)
+        fit_graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(fit_graph):
+            loss = fit_iteration_fused()
+        torch.cuda.synchronize(dev)
+        t0 = time.time()
+        for it in range(args.fit_iters):
+            fit_graph.replay()
+    elif fused_model is not None:
+        torch.cuda.synchronize(dev)
+        t0 = time.time()
+        for it in range(args.fit_iters):
+            loss = fit_iteration_fused()
+    elif args.graph:
         # one CUDA graph per fit iteration: render, loss, backward, fused multi-tensor Adam
         opt = torch.optim.Adam(groups, eps=1e-15, capturable=True, fused=True)
         side = torch.cuda.Stream()
@@ -138,6 +180,10 @@ def run_pair(p, args, dev, backend):
     torch.cuda.synchronize(dev)
     fit_s = time.time() - t0
     fit_loss = float(loss.detach())
+
+    if fused_model is not None:   # hand the fitted raw parameters to the pose stage below
+        f_dc, f_rest = fused_model.features[:, :1], fused_model.features[:, 1:]
+        opa_raw, log_s, rot, xyz = fused_model.opacity_raw, fused_model.log_scales, fused_model.rot_raw, fused_model.xyz
 
     # ---- 2. local pose fit: Gaussians frozen, pose only ----
     with torch.no_grad():
@@ -260,11 +306,17 @@ def main():
     ap.add_argument("--graph", action="store_true",
                     help="sync-free forward + the pose iteration captured as one CUDA graph (ours only)")
     ap.add_argument("--sync-free", action="store_true", help="sync-free forward without graph capture (ours only)")
+    ap.add_argument("--model", default=None, choices=["fused", "torch"],
+                    help="Gaussian fit: the library's fused model step (default for ours) or PyTorch activations + Adam")
     ap.add_argument("--loss", default=None, choices=["fused", "torch"],
                     help="fused CUDA L1+SSIM (default for --impl ours) or the PyTorch formulation (default for reference)")
     args = ap.parse_args()
     if args.loss is None:
         args.loss = "fused" if args.impl == "ours" else "torch"
+    if args.model is None:
+        args.model = "fused" if args.impl == "ours" else "torch"
+    if args.model == "fused" and args.impl != "ours":
+        raise SystemExit("--model fused needs --impl ours")
     world = int(os.environ.get("WORLD_SIZE", "1")); rank = int(os.environ.get("RANK", "0")); local = int(os.environ.get("LOCAL_RANK", "0"))
     real_stdout = os.dup(1); os.dup2(2, 1)
     if world > 1:
@@ -302,7 +354,7 @@ def main():
         err_t, err_r = max(r["err_t"] for r in res), max(r["err_r_deg"] for r in res)
     if rank == 0:
         n_local = len(GPar.shard_pairs(args.pairs, 0, world))
-        line = {"workload": "cf3dgs_local_pair", "impl": args.impl, "loss": args.loss, "graph": bool(args.graph), "sync_free": bool(args.graph or args.sync_free),
+        line = {"workload": "cf3dgs_local_pair", "impl": args.impl, "loss": args.loss, "model": args.model, "graph": bool(args.graph), "sync_free": bool(args.graph or args.sync_free),
                 "n_gpus": world, "pairs": args.pairs, "P": res[0]["P"] if res else 0,
                 "W": args.width, "H": args.height, "fit_iters": args.fit_iters, "pose_iters": args.pose_iters,
                 "wall_s": wall, "pairs_per_s": args.pairs / wall,
