@@ -172,6 +172,25 @@ def cpu_oracle_baseline(S, wl, cam, sample_frac=1.0):
             "sample": f"1 full fwd+bwd frame of {wl['name']} (C oracle, OpenMP {cores} threads, {dt:.2f} s)"}
 
 
+def torch_cpu_baseline(S):
+    """north_star's "PyTorch-CPU evaluation of the same rasterization equations": oracle/torch_oracle.py (plain tensor ops,
+    autograd backward) on the box's host cores, on a bounded sample -- BASELINE.json configs[0], 100k Gaussians at 640x360."""
+    from oracle import torch_oracle as TO
+    P, W, H = 100_000, 640, 360
+    cam = S.make_camera(W, H)
+    sc = S.make_gvol(P, W, H, seed=1, sh_degree=3)
+    lv = {k: sc[k].clone().requires_grad_(True) for k in PARAM_KEYS}
+    t0 = time.time()
+    out = TO.forward(lv["means3D"], lv["opacities"], shs=lv["shs"], scales=lv["scales"], rotations=lv["rotations"],
+                     viewmatrix=cam["viewmatrix"], projmatrix=cam["projmatrix"], campos=cam["campos"], bg=torch.zeros(3),
+                     W=W, H=H, tanfovx=cam["tanfovx"], tanfovy=cam["tanfovy"], sh_degree=3)
+    out["color"].sum().backward()
+    dt = time.time() - t0
+    return {"value": 1.0 / dt, "unit": "frames/s", "cores": torch.get_num_threads(), "kind": "port",
+            "sample": f"1 fwd+bwd frame of 100k Gaussians at 640x360 (PyTorch CPU tensor ops + autograd, {dt:.1f} s); "
+                      "not the 1M/1080p workload"}
+
+
 _REAL_STDOUT = None
 
 
@@ -479,6 +498,10 @@ def main():
             line["cpu_baseline"] = cpu_oracle_baseline(S, wl, S.make_camera(W, H))
         except Exception as ex:  # the CPU checker must never take the GPU number down with it
             line["cpu_baseline"] = {"error": str(ex)}
+        try:
+            line["cpu_baseline"]["torch_cpu"] = torch_cpu_baseline(S)
+        except Exception as ex:
+            line["cpu_baseline"]["torch_cpu"] = {"error": str(ex)}
     emit(line)
     return 0
 
