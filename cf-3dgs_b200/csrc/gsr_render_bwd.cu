@@ -325,12 +325,14 @@ render_backward_packed_kernel(int W, int H, int grid_x, const uint2* __restrict_
     auto flush_slab = [&]() {
         __syncwarp();
         if ((int)lane < pending * NV) {
-            float sacc = 0.f;
+            // 32 floats -> 1: packed adds on the register pairs the 16-byte loads deliver
+            f32x2 s2 = bc(0.f);
 #pragma unroll
             for (int q = 0; q < 8; q += 2) {
                 const float4 a = my_row[q], b = my_row[q + 1];
-                sacc += ((a.x + a.y) + (a.z + a.w)) + ((b.x + b.y) + (b.z + b.w));
+                s2 = add2(s2, add2(add2(pk(a.x, a.y), pk(a.z, a.w)), add2(pk(b.x, b.y), pk(b.z, b.w))));
             }
+            const float sacc = lo(s2) + hi(s2);
             const int jj = (int)((pj >> (8 * (pending - 1 - my_grp))) & 0xffu);
             atomicAdd(&acc[jj][my_comp], sacc);
         }
