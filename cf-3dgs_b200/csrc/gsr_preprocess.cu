@@ -16,7 +16,10 @@ constexpr int PRE_THREADS = 128;
 constexpr int PRE_ROW4 = 13;
 
 template <bool SLAB>
-__global__ void __launch_bounds__(PRE_THREADS)
+#ifndef GSR_PRE_MIN_BLOCKS
+#define GSR_PRE_MIN_BLOCKS 8
+#endif
+__global__ void __launch_bounds__(PRE_THREADS, GSR_PRE_MIN_BLOCKS)
 preprocess_kernel(PreprocessArgs a, GeomView g)
 {
     __shared__ float sV[16], sP[16], sCam[3];

@@ -35,7 +35,10 @@ __device__ __forceinline__ float block_sum_256(float v, float* red)
 }
 
 template <bool SLAB>
-__global__ void __launch_bounds__(PB_THREADS)
+#ifndef GSR_PB_MIN_BLOCKS
+#define GSR_PB_MIN_BLOCKS 5
+#endif
+__global__ void __launch_bounds__(PB_THREADS, GSR_PB_MIN_BLOCKS)
 preprocess_backward_kernel(PreprocessBwdArgs a, GeomView g)
 {
     __shared__ float sV[16], sP[16], sCam[3];
