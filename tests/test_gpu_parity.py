@@ -175,3 +175,54 @@ def test_full_size_workloads_vs_reference_cuda(name, kind, P, W, H, seed, deg):
     floor = 1e-3 * float(np.abs(gr["scales"].cpu().numpy()).max())
     assert float(np.abs(a - b).max()) <= 1e-4 * max(float(np.abs(b).max()), floor), "rotations"
     assert rel_to_max(m2d.grad.cpu().numpy(), gr["means2D"].cpu().numpy()) <= 1e-4
+
+
+ALT_REF_CASES = [CASES[5], CASES[6], CASES[7], CASES[2], CASES[4]]
+
+
+@pytest.mark.parametrize("case", ALT_REF_CASES, ids=[f"P{c[0]}_{c[1]}x{c[2]}_d{c[6]}_{c[7]}_{c[8]}" for c in ALT_REF_CASES])
+def test_alternative_inputs_vs_reference_cuda(case):
+    """colors_precomp / cov3D_precomp inputs, SH degrees 0 and 2, a ragged image size: against the live reference build."""
+    from oracle import ref_cuda as RC
+    if not RC.available():
+        pytest.skip("oracle/_ref/_dgr_ref.so not present")
+    P, W, H, seed, view, bg, deg, mode, cov_mode, dense, s0 = case
+    cam, sc, ct = _build(case)
+    out, leaves, m2d = cuda_forward(sc, cam, bg, sh_degree=deg, mode=mode, cov_mode=cov_mode)
+    dev = out["color"].device
+    kw = {}
+    if mode == "sh":
+        kw["shs"] = sc["shs"].to(dev)
+    else:
+        kw["colors_precomp"] = sc["colors"].to(dev)
+    if cov_mode == "scale_rot":
+        kw["scales"] = sc["scales"].to(dev); kw["rotations"] = sc["rotations"].to(dev)
+    else:
+        kw["cov3D_precomp"] = sc["cov3D"].to(dev)
+    rst = RC.forward(sc["means3D"].to(dev), sc["opacities"].to(dev), viewmatrix=cam["viewmatrix"].to(dev),
+                     projmatrix=cam["projmatrix"].to(dev), campos=cam["campos"].to(dev),
+                     bg=torch.tensor(bg, dtype=torch.float32, device=dev), W=W, H=H, tanfovx=cam["tanfovx"],
+                     tanfovy=cam["tanfovy"], sh_degree=deg, **kw)
+    ref = RC.parse_state(rst, P, W, H)
+    mine = out["state"]
+    assert out["num_rendered"] == rst["num_rendered"]
+    assert torch.equal(out["radii"], rst["radii"])
+    assert torch.equal(mine["keys_sorted"], ref["keys_sorted"])
+    assert torch.equal(mine["point_list"], ref["point_list"])
+    assert torch.equal(mine["ranges"], ref["ranges"])
+    assert torch.equal(mine["n_contrib"], ref["n_contrib"])
+    for k in ["color", "depth", "alpha"]:
+        assert float((out[k].detach() - rst[k]).abs().max()) <= 1e-5, k
+    loss = (out["color"] * ct["grad_color"].to(dev)).sum()
+    if dense:
+        loss = loss + (out["depth"] * ct["grad_depth"].to(dev)).sum() + (out["alpha"] * ct["grad_alpha"].to(dev)).sum()
+    loss.backward()
+    zero = torch.zeros(1, H, W, device=dev)
+    gr = RC.backward(rst, ct["grad_color"].to(dev), ct["grad_depth"].to(dev) if dense else zero,
+                     ct["grad_alpha"].to(dev) if dense else zero)
+    names = [("means3D", "means3D"), ("opacities", "opacities")]
+    names += [("shs", "sh")] if mode == "sh" else [("colors", "colors_precomp")]
+    names += [("scales", "scales"), ("rotations", "rotations")] if cov_mode == "scale_rot" else [("cov3D", "cov3Ds_precomp")]
+    for nm, key in names:
+        assert rel_to_max(leaves[nm].grad.cpu().numpy(), gr[key].cpu().numpy()) <= 1e-4, nm
+    assert rel_to_max(m2d.grad.cpu().numpy(), gr["means2D"].cpu().numpy()) <= 1e-4
