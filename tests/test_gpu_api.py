@@ -130,3 +130,29 @@ def test_graft_entry_smoke_runs():
         sys.path.insert(0, root)
     g = importlib.import_module("__graft_entry__")
     g.smoke()
+
+
+def test_mark_visible_and_scale_modifier_match_the_reference_build():
+    """The two remaining pybind entry points / arguments, against the live reference build: mark_visible
+    (rasterize_points.cu:210-229) and a scale_modifier != 1 render."""
+    from oracle import ref_cuda as RC
+    if not RC.available():
+        pytest.skip("oracle/_ref/_dgr_ref.so not present")
+    import diff_gaussian_rasterization as D
+    W, H, P = 320, 180, 60000
+    cam = S.second_view(W, H)
+    sc = S.make_gvol(P, W, H, seed=37)
+    rs = cuda_settings(D, cam, (0.3, 0.2, 0.1), 3, DEV, scale_modifier=0.6)
+    means = sc["means3D"].to(DEV)
+    mine = D.GaussianRasterizer(rs).markVisible(means)
+    ref = RC.module().mark_visible(means, rs.viewmatrix, rs.projmatrix)
+    assert torch.equal(mine, ref)
+    out, _, _ = cuda_forward(sc, cam, (0.3, 0.2, 0.1), scale_modifier=0.6)
+    rst = RC.forward(means, sc["opacities"].to(DEV), shs=sc["shs"].to(DEV), scales=sc["scales"].to(DEV),
+                     rotations=sc["rotations"].to(DEV), viewmatrix=rs.viewmatrix, projmatrix=rs.projmatrix,
+                     campos=rs.campos, bg=rs.bg, W=W, H=H, tanfovx=cam["tanfovx"], tanfovy=cam["tanfovy"], sh_degree=3,
+                     scale_modifier=0.6)
+    assert out["num_rendered"] == rst["num_rendered"] and torch.equal(out["radii"], rst["radii"])
+    ref_state = RC.parse_state(rst, P, W, H)
+    assert torch.equal(out["state"]["keys_sorted"], ref_state["keys_sorted"])
+    assert torch.equal(out["color"].detach(), rst["color"])
