@@ -9,7 +9,8 @@ import torch
 
 from helpers import ROOT
 
-FILES = sorted(glob.glob(os.path.join(ROOT, "tests", "golden", "*.npz")))
+FILES = sorted(glob.glob(os.path.join(ROOT, "tests", "golden", "gvol_*.npz")))
+KNN_FILES = sorted(glob.glob(os.path.join(ROOT, "tests", "golden", "knn_*.npz")))
 
 
 def _load(path):
@@ -88,3 +89,24 @@ def test_cuda_path_reproduces_reference_cuda_output(path):
     for key, v in got.items():
         a, b = v.cpu().numpy().reshape(-1).astype(np.float64), z["ref_grad_" + key].reshape(-1).astype(np.float64)
         assert np.abs(a - b).max() <= 1e-4 * np.abs(b).max(), key
+
+
+# ---- distCUDA2 (tests/golden/make_golden_knn.py: the reference's simple-knn build on a B200) ----
+@pytest.mark.skipif(not KNN_FILES, reason="no knn fixtures committed")
+@pytest.mark.parametrize("path", KNN_FILES, ids=[os.path.basename(f) for f in KNN_FILES])
+def test_knn_oracle_reproduces_reference_output(path):
+    """Pins oracle.knn_mean_dist2: bit for bit what SimpleKNN::knn produced."""
+    from oracle import oracle as O
+    z = _load(path)
+    got = O.knn_mean_dist2(z["points"])
+    assert np.array_equal(got.view(np.uint32), z["ref_mean_dist2"].view(np.uint32))
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(not KNN_FILES, reason="no knn fixtures committed")
+@pytest.mark.parametrize("path", KNN_FILES, ids=[os.path.basename(f) for f in KNN_FILES])
+def test_dist_cuda2_reproduces_reference_output(path):
+    from simple_knn._C import distCUDA2
+    z = _load(path)
+    got = distCUDA2(torch.from_numpy(z["points"]).cuda()).cpu().numpy()
+    assert np.array_equal(got.view(np.uint32), z["ref_mean_dist2"].view(np.uint32))
