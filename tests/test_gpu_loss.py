@@ -78,3 +78,22 @@ def test_fused_loss_is_faster_than_the_torch_formulation():
     tf, tp = run(fused), run(plain)
     print(f"fused {tf:.3f} ms  torch {tp:.3f} ms")
     assert tf < tp
+
+
+def test_fused_loss_reproduces_the_reference_code_output():
+    """Golden vectors made by importing the reference's own trainer/losses.py (tests/golden/make_golden_loss.py)."""
+    import glob
+    import os
+    import numpy as np
+    import gsr_loss
+    files = sorted(glob.glob(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "loss_*.npz")))
+    assert files, "loss fixtures missing"
+    for path in files:
+        z = np.load(path)
+        img = torch.from_numpy(z["render"]).to(DEV).requires_grad_(True)
+        gt = torch.from_numpy(z["gt"]).to(DEV)
+        loss = gsr_loss.photometric_loss(img, gt, lambda_dssim=float(z["lam"]), clamp=bool(z["clamp"]))
+        loss.backward()
+        assert abs(float(loss) - float(z["ref_loss"])) <= 1e-5, path
+        ref_g = torch.from_numpy(z["ref_grad"]).to(DEV)
+        assert float((img.grad.double() - ref_g).abs().max()) <= 1e-4 * float(ref_g.abs().max()), path
