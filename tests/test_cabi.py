@@ -3,6 +3,8 @@ import ctypes
 import os
 import re
 
+import pytest
+
 from helpers import ROOT
 
 
@@ -56,3 +58,23 @@ def test_size_queries_need_no_gpu():
     assert lib.gsr_binning_bytes(1000, 640, 360) >= 16 * 1000
     assert lib.gsr_profile_count() == 10
     assert lib.gsr_profile_name(0) == b"preprocess"
+
+
+def test_header_is_plain_c(tmp_path):
+    """include/gsr.h is the boundary a C host binds: it must compile as C99 and link against the library by name."""
+    import shutil
+    import subprocess
+    if shutil.which("gcc") is None:
+        pytest.skip("gcc not available")
+    src = tmp_path / "use_gsr.c"
+    src.write_text('#include "gsr.h"\n#include <stdio.h>\n'
+                   "int main(void) { printf(\"%d %zu\\n\", gsr_version(), gsr_geometry_bytes(1000)); return 0; }\n")
+    inc = os.path.join(ROOT, "include")
+    subprocess.run(["gcc", "-std=c99", "-Wall", "-Werror", "-pedantic", "-I", inc, "-fsyntax-only", str(src)], check=True)
+    lib = os.path.join(ROOT, "cf-3dgs_b200", "libgsr_b200.so")
+    if os.path.exists(lib):
+        exe = tmp_path / "use_gsr"
+        subprocess.run(["gcc", "-std=c99", "-I", inc, str(src), "-o", str(exe), lib, "-Wl,-rpath," + os.path.dirname(lib)],
+                       check=True)
+        out = subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split()
+        assert int(out[0]) >= 1000 and int(out[1]) > 0
