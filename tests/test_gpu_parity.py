@@ -133,6 +133,8 @@ FULL_SIZE = [
     # the bench workload (BASELINE.json metric) and the CF-3DGS local-pair scene, against the live reference build
     ("gvol_1M_1080p_sh3", "gvol", 1_000_000, 1920, 1080, 5, 3),
     ("gpix_518k_960x540_sh0", "gpix", 250_000, 960, 540, 2, 0),
+    # 4K: 32,400 tiles = 15 tile-key bits (8 + 7 bit passes), a ragged last tile row
+    ("gvol_2M_4k_sh3", "gvol", 2_000_000, 3840, 2160, 9, 3),
 ]
 
 
