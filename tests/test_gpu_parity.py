@@ -135,6 +135,8 @@ FULL_SIZE = [
     ("gpix_518k_960x540_sh0", "gpix", 250_000, 960, 540, 2, 0),
     # 4K: 32,400 tiles = 15 tile-key bits (8 + 7 bit passes), a ragged last tile row
     ("gvol_2M_4k_sh3", "gvol", 2_000_000, 3840, 2160, 9, 3),
+    # 8192x4096: 131,072 tiles = 17 tile-key bits, three tile-digit passes (8 + 8 + 1)
+    ("gvol_300k_8k_sh1", "gvol", 300_000, 8192, 4096, 10, 1),
 ]
 
 
