@@ -559,19 +559,46 @@ emit_kernel(const uint32_t* __restrict__ order, const uint32_t* __restrict__ til
     __syncthreads();
     const uint32_t begin = s_off[0];
     const uint32_t end = min(s_off[EMIT_THREADS], cap);   // cap: only the sync-free path can run out of room
-    for (uint32_t p = begin + threadIdx.x; p < end; p += EMIT_THREADS) {
-        // last k in [0, last] with s_off[k] <= p
+    // four consecutive instances per thread: one binary search, then a walk; 16-byte stores when the quad is whole
+    for (uint32_t p0 = (begin & ~3u) + 4u * threadIdx.x; p0 < end; p0 += 4u * EMIT_THREADS) {
+        const uint32_t first = max(p0, begin);
+        // last k in [0, last] with s_off[k] <= first
         int lo = 0, hi = last;
         while (lo < hi) {
             const int mid = (lo + hi + 1) >> 1;
-            if (s_off[mid] <= p) lo = mid; else hi = mid - 1;
+            if (s_off[mid] <= first) lo = mid; else hi = mid - 1;
         }
-        const uint2 q = s_rect[lo];
-        const uint32_t x0 = q.x & 0xffffu, x1 = q.x >> 16, y0 = q.y & 0xffffu;
-        const uint32_t local = p - s_off[lo], w = x1 - x0;
-        const uint32_t row = local / w, col = local - row * w;
-        tile_keys[p] = (y0 + row) * (uint32_t)grid_x + x0 + col;
-        tile_vals[p] = s_gid[lo];
+        uint32_t key[4], val[4];
+        uint32_t next_off = s_off[lo + 1];     // s_off[last + 1] = end of the block's range
+        uint2 q = s_rect[lo];
+        uint32_t gid = s_gid[lo];
+        uint32_t x0 = q.x & 0xffffu, w = (q.x >> 16) - x0, y0 = q.y & 0xffffu;
+        uint32_t local = first - s_off[lo];
+        uint32_t row = local / w, col = local - row * w;
+#pragma unroll
+        for (int c = 0; c < 4; c++) {
+            const uint32_t p = p0 + c;
+            key[c] = 0u; val[c] = 0u;
+            if (p < first || p >= end) continue;
+            while (p >= next_off) {            // next Gaussian with at least one tile (zero-tile ranks repeat the offset)
+                lo++;
+                next_off = s_off[lo + 1];
+                q = s_rect[lo]; gid = s_gid[lo];
+                x0 = q.x & 0xffffu; w = (q.x >> 16) - x0; y0 = q.y & 0xffffu;
+                row = 0; col = 0;
+            }
+            key[c] = (y0 + row) * (uint32_t)grid_x + x0 + col;
+            val[c] = gid;
+            if (++col == w) { col = 0; row++; }
+        }
+        if (p0 >= begin && p0 + 3 < end) {
+            *reinterpret_cast<uint4*>(tile_keys + p0) = make_uint4(key[0], key[1], key[2], key[3]);
+            *reinterpret_cast<uint4*>(tile_vals + p0) = make_uint4(val[0], val[1], val[2], val[3]);
+        } else {
+#pragma unroll
+            for (int c = 0; c < 4; c++)
+                if (p0 + c >= begin && p0 + c < end) { tile_keys[p0 + c] = key[c]; tile_vals[p0 + c] = val[c]; }
+        }
     }
 }
 
