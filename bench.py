@@ -521,7 +521,7 @@ def main():
     line["work"] = {"num_rendered": R, "visible": P_vis, "pairs_in_range": in_range, "pairs_blended": blended,
                     "reference_pairs_no_early_exit": ref_pairs, "tile_rejected_entries": tile_rej}
     depth_passes, tile_passes = 4, (max(1, (tiles - 1).bit_length()) + 7) // 8
-    line["gpu_launches"] = args.steps * (1 + 3 * depth_passes + 3 + 1 + 3 * tile_passes + 1 + 1 + 1 + 1)
+    line["gpu_launches"] = args.steps * (1 + 3 * depth_passes + 2 + 1 + 3 * tile_passes + 1 + 1 + 1 + 1)
     if world == 1 and not args.no_cpu_baseline:
         try:
             line["cpu_baseline"] = cpu_oracle_baseline(S, wl, S.make_camera(W, H))

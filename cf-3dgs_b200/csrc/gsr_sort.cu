@@ -479,22 +479,6 @@ scan_block_sums_kernel(const uint32_t* __restrict__ tiles, const uint32_t* __res
 }
 
 __global__ void __launch_bounds__(SORT_THREADS)
-scan_top_kernel(uint32_t* __restrict__ block_sums, int nblk)
-{
-    __shared__ uint32_t warp_sums[8];
-    const int per = (nblk + SORT_THREADS - 1) / SORT_THREADS;
-    const int lo = threadIdx.x * per, hi = min(nblk, lo + per);
-    uint32_t sum = 0;
-    for (int i = lo; i < hi; i++) sum += block_sums[i];
-    uint32_t run = block_exclusive_scan_256(sum, warp_sums, nullptr);
-    for (int i = lo; i < hi; i++) {
-        const uint32_t v = block_sums[i];
-        block_sums[i] = run;
-        run += v;
-    }
-}
-
-__global__ void __launch_bounds__(SORT_THREADS)
 scan_final_kernel(const uint32_t* __restrict__ tiles, const uint32_t* __restrict__ order, int P,
                   const uint32_t* __restrict__ block_sums, uint32_t* __restrict__ offsets)
 {
@@ -507,7 +491,13 @@ scan_final_kernel(const uint32_t* __restrict__ tiles, const uint32_t* __restrict
         v[i] = (base + i < P) ? tiles[order[base + i]] : 0u;
         sum += v[i];
     }
-    uint32_t run = block_exclusive_scan_256(sum, warp_sums, nullptr) + block_sums[blockIdx.x];
+    // the block's base = sum of the totals of the blocks before it: every block adds those up itself (a few hundred
+    // coalesced words) instead of waiting for a one-block scan kernel in between
+    uint32_t before = 0;
+    for (int i = threadIdx.x; i < (int)blockIdx.x; i += SORT_THREADS) before += block_sums[i];
+    uint32_t block_base;
+    block_exclusive_scan_256(before, warp_sums, &block_base);
+    uint32_t run = block_exclusive_scan_256(sum, warp_sums, nullptr) + block_base;
 #pragma unroll
     for (int i = 0; i < SORT_ITEMS; i++) {
         if (base + i < P) offsets[base + i] = run;
@@ -520,7 +510,6 @@ void launch_offsets_scan(const uint32_t* tiles, const uint32_t* order, uint32_t*
 {
     const int nblk = div_up(P, SORT_CHUNK);
     scan_block_sums_kernel<<<nblk, SORT_THREADS, 0, s>>>(tiles, order, P, block_sums);
-    scan_top_kernel<<<1, SORT_THREADS, 0, s>>>(block_sums, nblk);
     scan_final_kernel<<<nblk, SORT_THREADS, 0, s>>>(tiles, order, P, block_sums, offsets);
 }
 
