@@ -346,12 +346,11 @@ int gsr_backward_rigid(int P, int sh_degree, int M, int W, int H, int64_t num_re
     if (!means3D || !radii || !viewmatrix || !projmatrix || !geometry || !binning || !image || !grad_scratch ||
         !out_alpha || !dL_dout_color || !background)
         return fail(GSR_ERR_INVALID, "required pointer is NULL");
-    if (!dL_dmeans2D || !dL_dopacity || !dL_dmeans3D) return fail(GSR_ERR_INVALID, "required gradient output is NULL");
-    if (colors_precomp && !dL_dcolors) return fail(GSR_ERR_INVALID, "dL_dcolors is required with colors_precomp");
-    if (shs && !dL_dsh) return fail(GSR_ERR_INVALID, "dL_dsh is required with shs");
-    if (scales && (!dL_dscales || !dL_drotations || !rotations))
-        return fail(GSR_ERR_INVALID, "dL_dscales/dL_drotations are required with scales");
-    if (cov3D_precomp && !dL_dcov3D) return fail(GSR_ERR_INVALID, "dL_dcov3D is required with cov3D_precomp");
+    // every gradient output is optional: NULL = not wanted (a pose-only fit passes dL_dpose alone and saves the 236 bytes
+    // per Gaussian the others cost); dL_dscales and dL_drotations come as a pair
+    if (scales && !rotations) return fail(GSR_ERR_INVALID, "rotations are required with scales");
+    if ((dL_dscales == nullptr) != (dL_drotations == nullptr))
+        return fail(GSR_ERR_INVALID, "dL_dscales and dL_drotations are written together: pass both or neither");
     if (dL_dpose && !pose_scratch) return fail(GSR_ERR_INVALID, "pose_scratch is required with dL_dpose");
     GeomView g;
     geom_layout((char*)geometry, P, g);
@@ -377,6 +376,7 @@ int gsr_backward_rigid(int P, int sh_degree, int M, int W, int H, int64_t num_re
     a.dL_dmeans2D = dL_dmeans2D; a.dL_dcolors = colors_precomp ? dL_dcolors : nullptr; a.dL_dopacity = dL_dopacity;
     a.dL_dmeans3D = dL_dmeans3D; a.dL_dcov3D = dL_dcov3D; a.dL_dsh = shs ? dL_dsh : nullptr;
     a.dL_dscales = scales ? dL_dscales : nullptr; a.dL_drotations = scales ? dL_drotations : nullptr;
+    a.dL_dcov3D = cov3D_precomp ? dL_dcov3D : nullptr;
     a.dL_dpose = dL_dpose; a.pose_scratch = (float*)pose_scratch;
     a.rigid = rigid;
     { StageTimer t(ST_PREPROCESS_BWD, s); launch_preprocess_backward(a, g, s); }

@@ -186,7 +186,7 @@ preprocess_backward_kernel(PreprocessBwdArgs a, GeomView g)
                         shd[k] = (k < ncoef) ? (sh[3 * k] * dR + sh[3 * k + 1] * dG + sh[3 * k + 2] * dB) : 0.f;
 #pragma unroll
                     for (int k = 0; k < 16; k++) {
-                        if (k < ncoef) {
+                        if (dsh && k < ncoef) {
                             dsh[3 * k] = basis[k] * dR;
                             dsh[3 * k + 1] = basis[k] * dG;
                             dsh[3 * k + 2] = basis[k] * dB;
@@ -268,11 +268,15 @@ preprocess_backward_kernel(PreprocessBwdArgs a, GeomView g)
             const int first_zero = vis ? ncoef : 0;
             for (int k = first_zero * 3; k < a.M * 3; k++) dsh[k] = 0.f;
         }
-        a.dL_dmeans2D[3 * idx] = dmean2x;
-        a.dL_dmeans2D[3 * idx + 1] = dmean2y;
-        a.dL_dmeans2D[3 * idx + 2] = 0.f;
-        a.dL_dopacity[idx] = dopac;
-        if (a.rigid) {   // gradient w.r.t. the raw point: R^T g  (the pose partials below keep using p' and g)
+        // (a NULL output = the caller does not want that gradient: a pose-only fit asks for dL_dpose alone)
+        if (a.dL_dmeans2D) {
+            a.dL_dmeans2D[3 * idx] = dmean2x;
+            a.dL_dmeans2D[3 * idx + 1] = dmean2y;
+            a.dL_dmeans2D[3 * idx + 2] = 0.f;
+        }
+        if (a.dL_dopacity) a.dL_dopacity[idx] = dopac;
+        if (!a.dL_dmeans3D) {
+        } else if (a.rigid) {   // gradient w.r.t. the raw point: R^T g  (the pose partials below keep using p' and g)
             const float* T = a.rigid;
             a.dL_dmeans3D[3 * idx] = T[0] * gmx + T[4] * gmy + T[8] * gmz;
             a.dL_dmeans3D[3 * idx + 1] = T[1] * gmx + T[5] * gmy + T[9] * gmz;

@@ -201,22 +201,24 @@ def _forward_impl(bg, means3D, colors_precomp, opacities, scales, rotations, sca
 
 def _backward_impl(bg, means3D, radii, colors_precomp, scales, rotations, scale_modifier, cov3Ds_precomp,
                    viewmatrix, projmatrix, tanfovx, tanfovy, grad_color, grad_depth, grad_alpha, sh, degree,
-                   campos, geom, R, binning, img, alpha, debug, want_pose_grad=False, rigid=None):
+                   campos, geom, R, binning, img, alpha, debug, want_pose_grad=False, rigid=None, skip=()):
     """Counterpart of _C.rasterize_gaussians_backward (rasterize_points.cu:121-208).  Returns the same eight
-    gradients (None where the matching input was absent) plus the optional fused pose gradient."""
+    gradients (None where the matching input was absent) plus the optional fused pose gradient.
+    skip: names among {"means2D", "means3D", "opacity", "sh", "colors", "scales", "cov3D"} whose gradients the caller
+    does not need (autograd's needs_input_grad): they are neither allocated nor written ("scales" covers rotations)."""
     dev = means3D.device
     P = means3D.shape[0]
     H, W = grad_color.shape[1], grad_color.shape[2]
     M = sh.shape[1] if sh.numel() != 0 else 0
     f32 = dict(dtype=torch.float32, device=dev)
-    dmeans3D = torch.empty((P, 3), **f32)
-    dmeans2D = torch.empty((P, 3), **f32)
-    dopacity = torch.empty((P, 1), **f32)
-    dcolors = torch.empty((P, 3), **f32) if colors_precomp.numel() else None
-    dsh = torch.empty((P, M, 3), **f32) if sh.numel() else None
-    dscales = torch.empty((P, 3), **f32) if scales.numel() else None
-    drots = torch.empty((P, 4), **f32) if scales.numel() else None
-    dcov3D = torch.empty((P, 6), **f32) if cov3Ds_precomp.numel() else None
+    dmeans3D = torch.empty((P, 3), **f32) if "means3D" not in skip else None
+    dmeans2D = torch.empty((P, 3), **f32) if "means2D" not in skip else None
+    dopacity = torch.empty((P, 1), **f32) if "opacity" not in skip else None
+    dcolors = torch.empty((P, 3), **f32) if colors_precomp.numel() and "colors" not in skip else None
+    dsh = torch.empty((P, M, 3), **f32) if sh.numel() and "sh" not in skip else None
+    dscales = torch.empty((P, 3), **f32) if scales.numel() and "scales" not in skip else None
+    drots = torch.empty((P, 4), **f32) if scales.numel() and "scales" not in skip else None
+    dcov3D = torch.empty((P, 6), **f32) if cov3Ds_precomp.numel() and "cov3D" not in skip else None
     dpose = torch.empty((6,), **f32) if want_pose_grad else None
     if P == 0:
         if dpose is not None:
@@ -234,8 +236,8 @@ def _backward_impl(bg, means3D, radii, colors_precomp, scales, rotations, scale_
             _ptr(colors_precomp), _ptr(scales), _ptr(rotations), float(scale_modifier), _ptr(cov3Ds_precomp),
             _ptr(viewmatrix), _ptr(projmatrix), _ptr(campos), float(tanfovx), float(tanfovy), _ptr(sh),
             alpha.data_ptr(), grad_color.data_ptr(), _ptr(grad_depth), _ptr(grad_alpha), geom.data_ptr(),
-            binning.data_ptr(), img.data_ptr(), scratch.data_ptr(), dmeans2D.data_ptr(), _ptr(dcolors),
-            dopacity.data_ptr(), dmeans3D.data_ptr(), _ptr(dcov3D), _ptr(dsh), _ptr(dscales), _ptr(drots),
+            binning.data_ptr(), img.data_ptr(), scratch.data_ptr(), _ptr(dmeans2D), _ptr(dcolors),
+            _ptr(dopacity), _ptr(dmeans3D), _ptr(dcov3D), _ptr(dsh), _ptr(dscales), _ptr(drots),
             _ptr(dpose), _ptr(pose_scratch), None if rigid is None else rigid.data_ptr(), stream, int(bool(debug))))
     return dmeans2D, dcolors, dopacity, dmeans3D, dcov3D, dsh, dscales, drots, dpose
 

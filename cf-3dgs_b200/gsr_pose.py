@@ -77,12 +77,18 @@ class _PoseRasterize(torch.autograd.Function):
         colors_precomp, xyz, scales, rotations, cov3Ds_precomp, radii, sh, geom, binning, img, alpha, rigid = ctx.saved_tensors
         if grad_color is None:
             grad_color = torch.zeros((3, rs.image_height, rs.image_width), dtype=torch.float32, device=xyz.device)
+        # inputs: xi, xyz, T, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, rs -- a pose-only fit needs
+        # none of the per-Gaussian gradients, and then the kernel does not write them (236 bytes per Gaussian)
+        need = ctx.needs_input_grad
+        skip = {"means2D"} | ({"means3D"} if not need[1] else set()) | ({"sh"} if not need[3] else set()) | \
+               ({"colors"} if not need[4] else set()) | ({"opacity"} if not need[5] else set()) | \
+               ({"scales"} if not (need[6] or need[7]) else set()) | ({"cov3D"} if not need[8] else set())
         res = D._backward_impl(rs.bg, xyz, radii, colors_precomp, scales, rotations, rs.scale_modifier, cov3Ds_precomp,
                                rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, grad_color, grad_depth, grad_alpha,
                                sh, rs.sh_degree, rs.campos, geom, ctx.R, binning, img, alpha, rs.debug, want_pose_grad=True,
-                               rigid=rigid)
+                               rigid=rigid, skip=skip)
         dmeans2D, dcolors, dopacity, dxyz, dcov3D, dsh, dscales, drots, dpose = res
-        return dpose, (dxyz if ctx.needs_input_grad[1] else None), None, dsh, dcolors, dopacity, dscales, drots, dcov3D, None
+        return dpose, dxyz, None, dsh, dcolors, dopacity, dscales, drots, dcov3D, None
 
 
 def rasterize_with_pose(raster_settings, xi, xyz, T, opacities, shs=None, colors_precomp=None, scales=None,
