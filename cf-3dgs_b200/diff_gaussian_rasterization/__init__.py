@@ -280,16 +280,21 @@ class _RasterizeGaussians(torch.autograd.Function):
         args = (rs.bg, means3D, radii, colors_precomp, scales, rotations, rs.scale_modifier, cov3Ds_precomp,
                 rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, grad_color, grad_depth, grad_alpha, sh,
                 rs.sh_degree, rs.campos, geom, ctx.num_rendered, binning, img, alpha, rs.debug)
+        # inputs: means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, settings.  Gradients
+        # autograd does not ask for (frozen parameters) are neither allocated nor written by the kernel.
+        need = ctx.needs_input_grad
+        skip = {n for n, k in (("means3D", need[0]), ("means2D", need[1]), ("sh", need[2]), ("colors", need[3]),
+                               ("opacity", need[4]), ("scales", need[5] or need[6]), ("cov3D", need[7])) if not k}
         if rs.debug:
             cpu_args = cpu_deep_copy_tuple(args)
             try:
-                res = _backward_impl(*args)
+                res = _backward_impl(*args, skip=skip)
             except Exception:
                 torch.save(cpu_args, "snapshot_bw.dump")
                 print("\nAn error occured in backward. Writing snapshot_bw.dump for debugging.\n")
                 raise
         else:
-            res = _backward_impl(*args)
+            res = _backward_impl(*args, skip=skip)
         dmeans2D, dcolors, dopacity, dmeans3D, dcov3D, dsh, dscales, drots, _ = res
         return dmeans3D, dmeans2D, dsh, dcolors, dopacity, dscales, drots, dcov3D, None
 

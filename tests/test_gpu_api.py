@@ -156,3 +156,31 @@ def test_mark_visible_and_scale_modifier_match_the_reference_build():
     ref_state = RC.parse_state(rst, P, W, H)
     assert torch.equal(out["state"]["keys_sorted"], ref_state["keys_sorted"])
     assert torch.equal(out["color"].detach(), rst["color"])
+
+
+def test_frozen_inputs_get_no_gradient_and_the_others_are_unchanged():
+    """needs_input_grad is honoured: gradients of frozen inputs are not produced, the rest are bit-for-bit... equal up to
+    the float atomics of the blend backward."""
+    import diff_gaussian_rasterization as D
+    W, H, P = 200, 120, 9000
+    cam = S.make_camera(W, H)
+    sc = S.make_gvol(P, W, H, seed=41, s0=0.02)
+    rs = cuda_settings(D, cam, (0, 0, 0), 3, DEV)
+    gc = S.cotangents(W, H, seed=42, dense=False)["grad_color"].to(DEV)
+
+    def run(frozen):
+        lv = {k: sc[k].to(DEV).requires_grad_(k not in frozen) for k in ["means3D", "opacities", "shs", "scales", "rotations"]}
+        m2d = torch.zeros(P, 3, device=DEV, requires_grad="means2D" not in frozen)
+        out = D.GaussianRasterizer(rs)(lv["means3D"], m2d, lv["opacities"], shs=lv["shs"], scales=lv["scales"],
+                                       rotations=lv["rotations"])
+        out[0].backward(gc)
+        g = {k: v.grad for k, v in lv.items()}
+        g["means2D"] = m2d.grad
+        return g
+
+    full = run(())
+    part = run(("shs", "scales", "rotations", "means2D"))
+    for k in ("shs", "scales", "rotations", "means2D"):
+        assert part[k] is None
+    for k in ("means3D", "opacities"):
+        assert float((part[k] - full[k]).abs().max()) <= 1e-5 * float(full[k].abs().max())
