@@ -362,8 +362,11 @@ int gsr_backward_rigid(int P, int sh_degree, int M, int W, int H, int64_t num_re
     { StageTimer t(ST_GRAD_ZERO, s); cudaMemsetAsync(grad_scratch, 0, (size_t)P * 12 * sizeof(float), s); }
     if (num_rendered > 0) {
         StageTimer t(ST_RENDER_BWD, s);
+        // opacity / colour partials are needed when their gradients are wanted, or when the colour depends on the
+        // position (SH above degree 0), because the mean gradient then has a term through dL/dRGB
+        const bool want_params = dL_dopacity || dL_dcolors || dL_dsh || (shs && sh_degree > 0);
         launch_render_backward(W, H, iv.ranges, b.vals[0], g, background, out_alpha, iv.n_contrib, dL_dout_color,
-                               dL_dout_depth, dL_dout_alpha, (float*)grad_scratch, s);
+                               dL_dout_depth, dL_dout_alpha, (float*)grad_scratch, s, want_params);
     }
     GSR_STAGE("render backward");
     PreprocessBwdArgs a;

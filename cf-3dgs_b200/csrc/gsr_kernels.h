@@ -62,7 +62,7 @@ void launch_pair_counts(int W, int H, const uint2* ranges, const uint32_t* point
 void launch_render_backward(int W, int H, const uint2* ranges, const uint32_t* point_list, const GeomView& g,
                             const float* bg, const float* out_alpha, const uint32_t* n_contrib,
                             const float* dL_dcolor, const float* dL_ddepth, const float* dL_dalpha,
-                            float* grad_scratch, cudaStream_t s);
+                            float* grad_scratch, cudaStream_t s, bool want_params = true);
 
 struct PreprocessBwdArgs {
     const float* rigid = nullptr;   // same transform as the forward; dL_dmeans3D is then w.r.t. the raw points

@@ -260,7 +260,7 @@ render_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ range
 #define GSR_BWDP_MIN_BLOCKS 6
 #endif
 
-template <bool HAS_DEPTH, bool HAS_ALPHA>
+template <bool HAS_DEPTH, bool HAS_ALPHA, bool PARAMS>
 __global__ void __launch_bounds__(PKB_THREADS, GSR_BWDP_MIN_BLOCKS)
 render_backward_packed_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges,
                               const uint32_t* __restrict__ point_list, GeomView g, const float* __restrict__ bg,
@@ -268,8 +268,11 @@ render_backward_packed_kernel(int W, int H, int grid_x, const uint2* __restrict_
                               const float* __restrict__ dL_dcolor, const float* __restrict__ dL_ddepth,
                               const float* __restrict__ dL_dalpha, float* __restrict__ grad)
 {
-    constexpr int NV = HAS_DEPTH ? 10 : 9;
-    constexpr int ROWS = GROUP * NV;
+    // PARAMS = false: the caller wants no opacity / colour / SH gradient and the colour does not feed the mean gradient
+    // (SH degree 0 or precomputed colours) -- a pose-only fit.  Only the five geometric partials (+ depth) are reduced.
+    constexpr int NV = 5 + (PARAMS ? 4 : 0) + (HAS_DEPTH ? 1 : 0);   // partials per entry that are reduced
+    constexpr int GRP = (32 / NV) < 4 ? (32 / NV) : 4;               // pending entries per slab reduction (8-bit slots in pj)
+    constexpr int ROWS = GRP * NV;
     static_assert(ROWS <= 32, "one lane sums one slab row");
     static_assert(BWD_BATCH <= PKB_THREADS, "one staging / flush thread per entry");
     __shared__ StagedT<BWD_BATCH> sm;
@@ -334,7 +337,9 @@ render_backward_packed_kernel(int W, int H, int grid_x, const uint2* __restrict_
             }
             const float sacc = lo(s2) + hi(s2);
             const int jj = (int)((pj >> (8 * (pending - 1 - my_grp))) & 0xffu);
-            atomicAdd(&acc[jj][my_comp], sacc);
+            // column of the gradient record this partial belongs to: 0-4 geometry, 5 opacity, 6-8 colour, 9 depth
+            const int col = (my_comp < 5 || PARAMS) ? my_comp : 9;
+            atomicAdd(&acc[jj][col], sacc);
         }
         __syncwarp();
         pending = 0;
@@ -450,11 +455,14 @@ render_backward_packed_kernel(int W, int H, int grid_x, const uint2* __restrict_
                 v[9] = HAS_DEPTH ? mul2(aT, dLd) : bc(0.f);
                 {
 #pragma unroll
-                    for (int k = 0; k < NV; k++) park[k * RED_STRIDE] = lo(v[k]) + hi(v[k]);
+                    for (int k = 0; k < NV; k++) {
+                        const f32x2 vk = v[(k < 5 || PARAMS) ? k : 9];
+                        park[k * RED_STRIDE] = lo(vk) + hi(vk);
+                    }
                     park += NV * RED_STRIDE;      // running pointer: next pending entry's rows
                     pj = (pj << 8) | (uint32_t)j;
                     pending++;
-                    if (pending == GROUP) flush_slab();
+                    if (pending == GRP) flush_slab();
                 }
             }
         }
@@ -490,7 +498,7 @@ render_backward_packed_kernel(int W, int H, int grid_x, const uint2* __restrict_
 void launch_render_backward(int W, int H, const uint2* ranges, const uint32_t* point_list, const GeomView& g,
                             const float* bg, const float* out_alpha, const uint32_t* n_contrib,
                             const float* dL_dcolor, const float* dL_ddepth, const float* dL_dalpha,
-                            float* grad_scratch, cudaStream_t s)
+                            float* grad_scratch, cudaStream_t s, bool want_params)
 {
     const int gx = div_up(W, TILE), gy = div_up(H, TILE);
     const dim3 grid(gx * gy), block(BLEND_THREADS);
@@ -498,9 +506,14 @@ void launch_render_backward(int W, int H, const uint2* ranges, const uint32_t* p
 #define GSR_LAUNCH(D, A)                                                                                              \
     do {                                                                                                              \
         if (packed)                                                                                                   \
-            render_backward_packed_kernel<D, A><<<grid, PKB_THREADS, 0, s>>>(                                         \
-                W, H, gx, ranges, point_list, g, bg, out_alpha, n_contrib, dL_dcolor, dL_ddepth, dL_dalpha,           \
-                grad_scratch);                                                                                        \
+            if (want_params)                                                                                          \
+                render_backward_packed_kernel<D, A, true><<<grid, PKB_THREADS, 0, s>>>(                               \
+                    W, H, gx, ranges, point_list, g, bg, out_alpha, n_contrib, dL_dcolor, dL_ddepth, dL_dalpha,       \
+                    grad_scratch);                                                                                    \
+            else                                                                                                      \
+                render_backward_packed_kernel<D, A, false><<<grid, PKB_THREADS, 0, s>>>(                              \
+                    W, H, gx, ranges, point_list, g, bg, out_alpha, n_contrib, dL_dcolor, dL_ddepth, dL_dalpha,       \
+                    grad_scratch);                                                                                    \
         else                                                                                                          \
             render_backward_kernel<D, A><<<grid, block, 0, s>>>(W, H, gx, ranges, point_list, g, bg, out_alpha,       \
                                                                 n_contrib, dL_dcolor, dL_ddepth, dL_dalpha,           \

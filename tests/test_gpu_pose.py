@@ -10,13 +10,17 @@ pytestmark = pytest.mark.gpu
 DEV = "cuda:0"
 
 
-def test_fused_pose_gradient_matches_autograd_through_se3_exp():
+@pytest.mark.parametrize("degree,freeze", [(3, False), (0, False), (0, True)],
+                         ids=["sh3", "sh0", "sh0_pose_only_geometry_kernel"])
+def test_fused_pose_gradient_matches_autograd_through_se3_exp(degree, freeze):
+    """freeze: the points need no gradient either, so with SH degree 0 the backward blend runs its geometry-only variant
+    (no opacity / colour partials) -- the case of CF-3DGS's pose fit."""
     import diff_gaussian_rasterization as D
     import gsr_pose as GP
     W, H, P = 200, 120, 12000
     cam = S.make_camera(W, H)
     sc = S.make_gvol(P, W, H, seed=61, s0=0.02)
-    rs = cuda_settings(D, cam, (0.1, 0.1, 0.1), 3, DEV)
+    rs = cuda_settings(D, cam, (0.1, 0.1, 0.1), degree, DEV)
     t = {k: sc[k].to(DEV) for k in ["means3D", "opacities", "shs", "scales", "rotations"]}
     a = np.deg2rad(3.0)
     T = torch.tensor([[np.cos(a), 0, np.sin(a), 0.03], [0, 1, 0, -0.02], [-np.sin(a), 0, np.cos(a), 0.05], [0, 0, 0, 1]],
@@ -26,7 +30,7 @@ def test_fused_pose_gradient_matches_autograd_through_se3_exp():
 
     # fused: dL/dxi straight from the backward kernel
     xi = torch.zeros(6, device=DEV, requires_grad=True)
-    xyz = t["means3D"].clone().requires_grad_(True)
+    xyz = t["means3D"].clone().requires_grad_(not freeze)
     color, radii, depth, alpha = GP.rasterize_with_pose(rs, xi, xyz, T, t["opacities"], shs=t["shs"], scales=t["scales"],
                                                         rotations=t["rotations"])
     ((color * gc).sum() + (depth * gd).sum() + (alpha * ga).sum()).backward()
@@ -67,6 +71,9 @@ def test_fused_pose_gradient_matches_autograd_through_se3_exp():
     assert np.abs(want).max() > 0
     assert np.abs(got - want).max() <= 1e-4 * np.abs(want).max(), (got, want)
     # gradient w.r.t. the untransformed points is R^T g
+    if freeze:
+        assert xyz.grad is None
+        return
     assert float((xyz.grad - xyz2.grad).abs().max()) <= 1e-4 * float(xyz2.grad.abs().max())
 
 
