@@ -48,6 +48,7 @@ def main():
     ap.add_argument("--sh-degree", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--loss", default=None, choices=["fused", "torch"])
+    ap.add_argument("--profile", action="store_true", help="print the per-stage CUDA-event times of one iteration (ours)")
     ap.add_argument("--graph", action="store_true",
                     help="sync-free forward + one CUDA graph per training view holding the whole iteration (ours, fused model)")
     ap.add_argument("--model", default=None, choices=["fused", "torch"],
@@ -135,6 +136,20 @@ def main():
         opt.step(); opt.zero_grad(set_to_none=True)
         return loss
 
+    if args.profile and args.impl == "ours":
+        import ctypes
+        import diff_gaussian_rasterization as D
+        for k in range(3):
+            iteration(k)
+        n_st = D.lib.gsr_profile_count()
+        acc = [0.0] * n_st
+        D.lib.gsr_profile_enable(1)
+        for k in range(3, 3 + 8):
+            iteration(k)
+            buf = (ctypes.c_float * n_st)(); D.lib.gsr_profile_read(buf, n_st)
+            acc = [a + max(b, 0.0) for a, b in zip(acc, buf[:])]
+        D.lib.gsr_profile_enable(0)
+        print({D.lib.gsr_profile_name(i).decode(): round(acc[i] / 8, 4) for i in range(n_st)}, file=sys.stderr)
     overflow = None
     if args.graph:
         if fused_model is None:

@@ -62,3 +62,24 @@ def test_cpu_deep_copy_tuple():
     t = (torch.ones(2), 3, "s")
     c = D.cpu_deep_copy_tuple(t)
     assert c[1] == 3 and c[2] == "s" and torch.equal(c[0], t[0]) and c[0] is not t[0]
+
+
+def test_the_product_package_never_touches_the_oracle():
+    """oracle/ is the checker: nothing under cf-3dgs_b200/ (the shipped package and its CUDA sources) may import, load or
+    name it.  (tools/ and the `--impl reference` arms of bench.py / examples/ time the reference build beside the product;
+    they are measurement harnesses, not the product path.)"""
+    import os
+    import re
+    root = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "cf-3dgs_b200")
+    # imports, dlopen targets and #includes (comments may cite the oracle by name)
+    pat = re.compile(r"^\s*(from|import)\s+oracle\b|import_module\(.*oracle|CDLL\(.*(oracle|_ref)|#\s*include\s*[\"<].*oracle|"
+                     r"libgsr_oracle|_dgr_ref|_sknn_ref", re.M)
+    offenders = []
+    for d, _, files in os.walk(root):
+        if os.sep + "build" in d or os.sep + "variants" in d:
+            continue
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                if pat.search(open(os.path.join(d, f), errors="ignore").read()):
+                    offenders.append(os.path.join(d, f))
+    assert not offenders, offenders
