@@ -183,4 +183,4 @@ def test_frozen_inputs_get_no_gradient_and_the_others_are_unchanged():
     for k in ("shs", "scales", "rotations", "means2D"):
         assert part[k] is None
     for k in ("means3D", "opacities"):
-        assert float((part[k] - full[k]).abs().max()) <= 1e-5 * float(full[k].abs().max())
+        assert float((part[k] - full[k]).abs().max()) <= 5e-5 * float(full[k].abs().max())

@@ -50,7 +50,7 @@ def test_sync_free_forward_backward_is_bit_identical_to_the_synchronising_path()
         assert torch.equal(a, b)
     for k in ref[4]:
         # backward accumulates with float atomics: equal up to summation order
-        assert float((ref[4][k] - second[4][k]).abs().max()) <= 1e-5 * float(ref[4][k].abs().max())
+        assert float((ref[4][k] - second[4][k]).abs().max()) <= 5e-5 * float(ref[4][k].abs().max())
     assert torch.equal(first[0], ref[0])
 
 
@@ -104,7 +104,7 @@ def test_whole_step_can_be_captured_in_a_cuda_graph():
         g.replay()
     torch.cuda.synchronize()
     assert torch.equal(color.detach(), ref[0])
-    assert float((static["means3D"].grad - ref[4]["means3D"]).abs().max()) <= 1e-5 * float(ref[4]["means3D"].abs().max())
+    assert float((static["means3D"].grad - ref[4]["means3D"]).abs().max()) <= 5e-5 * float(ref[4]["means3D"].abs().max())
     # new parameter values flow through the captured graph
     with torch.no_grad():
         static["opacities"].mul_(0.5)
