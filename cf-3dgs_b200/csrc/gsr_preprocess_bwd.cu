@@ -36,7 +36,7 @@ __device__ __forceinline__ float block_sum_256(float v, float* red)
 
 template <bool SLAB>
 #ifndef GSR_PB_MIN_BLOCKS
-#define GSR_PB_MIN_BLOCKS 5
+#define GSR_PB_MIN_BLOCKS 6
 #endif
 __global__ void __launch_bounds__(PB_THREADS, GSR_PB_MIN_BLOCKS)
 preprocess_backward_kernel(PreprocessBwdArgs a, GeomView g)
