@@ -449,6 +449,8 @@ def main():
                                      "ms_per_step": ar_ms / args.steps, "allreduce_bytes": P * 59 * 4}
     if args.impl == "reference":
         line["impl"] = "reference"
+        line["n_gpus"] = args.gpus          # the run it belongs to; the reference itself runs on rank 0 alone
+        line["ranks_used"] = 1
         line["gpu_launches"] = 0
         line["cpu_baseline"] = {"value": value, "unit": "frames/s", "cores": 0, "kind": "reference",
                                 "sample": "the reference's own CUDA rasterizer (oracle/_ref, unmodified sources, sm_100a) "
