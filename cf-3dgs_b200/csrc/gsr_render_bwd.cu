@@ -255,7 +255,10 @@ render_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ range
 //    difference the opacity gradient needs anyway.
 //  * Factors that depend only on the entry (opacity, -1/2, W/2, H/2) are applied once per (tile, Gaussian) in the
 //    batch flush instead of once per pixel pair.
+//  * What is reduced per entry are the moments of m0 = G * dL/dalpha over the pixel offsets (sum m0, m0 dx, m0 dy, m0 dx^2,
+//    m0 dx dy, m0 dy^2); the mean and conic gradients are linear in them with per-entry coefficients.
 //  * The two pixels of a lane are added before the slab reduction, so that reduction runs once per 64 pixels.
+//  * PARAMS = false (pose-only fits): no opacity / colour partials, five (six with depth) values per entry instead of nine.
 #ifndef GSR_BWDP_MIN_BLOCKS
 #define GSR_BWDP_MIN_BLOCKS 6
 #endif
