@@ -47,6 +47,24 @@ struct StageTimer {
     ~StageTimer() { if (g_prof_on) { cudaEventRecord(g_ev[st][1], s); g_ev_used[st] = true; } }
 };
 
+// The event that marks "num_rendered has landed on the host": one per (host thread, device), created on first use and
+// kept (two threads driving the same device must not record and wait on one shared event).
+cudaError_t count_event(cudaEvent_t* out)
+{
+    constexpr int MAX_DEV = 64;
+    thread_local cudaEvent_t ev[MAX_DEV] = {};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= MAX_DEV) return cudaErrorInvalidDevice;
+    if (!ev[dev]) {
+        e = cudaEventCreateWithFlags(&ev[dev], cudaEventDisableTiming);
+        if (e != cudaSuccess) { ev[dev] = nullptr; return e; }
+    }
+    *out = ev[dev];
+    return cudaSuccess;
+}
+
 int tile_bits(int tiles)
 {
     int bits = 0;
@@ -214,7 +232,7 @@ int gsr_forward_prepare_rigid(int P, int sh_degree, int M, const float* means3D,
     // "how many instances?" travels to the host (8 bytes, into the caller's -- ideally pinned -- word) while
     // the GPU keeps sorting; bit 62 of the counter flags a prefilter violation
     cudaEvent_t ev;
-    cudaError_t e = cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
+    cudaError_t e = count_event(&ev);
     if (e != cudaSuccess) return fail(GSR_ERR_CUDA, "event: %s", cudaGetErrorString(e));
     cudaMemcpyAsync(num_rendered_host, g.counters, sizeof(int64_t), cudaMemcpyDeviceToHost, s);
     cudaEventRecord(ev, s);
@@ -222,7 +240,6 @@ int gsr_forward_prepare_rigid(int P, int sh_degree, int M, const float* means3D,
     depth_sort_and_offsets(P, g, s);   // low 32 key bits (depth) sorted over Gaussians, before duplication
 
     e = cudaEventSynchronize(ev);
-    cudaEventDestroy(ev);
     if (e != cudaSuccess) return fail(GSR_ERR_CUDA, "preprocess/count: %s", cudaGetErrorString(e));
     GSR_STAGE("depth sort + offsets");
     const unsigned long long raw = (unsigned long long)*num_rendered_host;
@@ -283,8 +300,7 @@ int gsr_forward_fused_rigid(int P, int sh_degree, int M, const float* means3D, c
                                       colors_precomp, viewmatrix, projmatrix, campos, W, H, radii, geometry, geometry_bytes);
     if (rc != GSR_OK) return rc;
     if (P == 0) {
-        zero_images(W, H, out_color, out_depth, out_alpha, s);
-        cudaMemsetAsync(status, 0, 2 * sizeof(int64_t), s);
+        zero_images(W, H, out_color, out_depth, out_alpha, s);   // status: nothing to add (count 0, no flag)
         return GSR_OK;
     }
     if (!binning || !image || !background) return fail(GSR_ERR_INVALID, "workspaces and background are required");

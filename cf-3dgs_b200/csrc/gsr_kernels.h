@@ -53,7 +53,6 @@ void launch_render_forward(int W, int H, const uint2* ranges, const uint32_t* po
 size_t knn_scratch_bytes(int P);
 int launch_knn_mean_dist2(int P, const float* points, float* mean_d2, void* scratch, cudaStream_t s);
 
-bool blend_packed();   // false when GSR_BLEND=scalar (one pixel per lane kernels, kept for A/B runs)
 void launch_expf_check(uint32_t first_bits, uint32_t count, unsigned long long* mismatches, cudaStream_t s);
 
 void launch_pair_counts(int W, int H, const uint2* ranges, const uint32_t* point_list, const GeomView& g,

@@ -12,6 +12,7 @@
 // Adam follows torch.optim.Adam (no amsgrad, no weight decay): m = b1 m + (1-b1) g;  v = b2 v + (1-b2) g^2;
 //   p -= (lr / (1 - b1^t)) * m / (sqrt(v) / sqrt(1 - b2^t) + eps).
 #include <cmath>
+#include <cstdint>
 
 #include "../../include/gsr.h"
 #include "gsr_kernels.h"
@@ -182,6 +183,10 @@ static int adam_step_impl(int P, int M, int step, long long* step_state, float b
         set_last_error("gsr_gaussian_adam_step: required pointer is NULL");
         return GSR_ERR_INVALID;
     }
+    if ((((uintptr_t)rot_raw) | ((uintptr_t)d_rot) | ((uintptr_t)state)) & 15) {
+        set_last_error("gsr_gaussian_adam_step: rot_raw, d_rot and state must be 16-byte aligned");
+        return GSR_ERR_INVALID;
+    }
     AdamCfg c;
     c.b1 = beta1; c.b2 = beta2; c.eps = eps;
     c.inv_bias1 = c.inv_sqrt_bias2 = 1.f;
@@ -193,17 +198,19 @@ static int adam_step_impl(int P, int M, int step, long long* step_state, float b
         c.inv_bias1 = (float)(1.0 / (1.0 - std::pow((double)beta1, (double)step)));
         c.inv_sqrt_bias2 = (float)(1.0 / std::sqrt(1.0 - std::pow((double)beta2, (double)step)));
     }
-    // state layout: [m | v] for xyz(3P) opacity(P) scale(3P) rot(4P) features(3MP), in that order
+    // state layout: [m | v] for rot(4P) xyz(3P) opacity(P) scale(3P) features(3MP), in that order.  The rotation moments
+    // come first because the kernel moves them as float4: at 32*P bytes past a 16-byte aligned base everything behind
+    // them may start at any 4-byte boundary (odd P), they may not.
     const size_t n = (size_t)P;
     float* st = state;
     GaussianStepArgs a;
     a.P = P;
     a.xyz = xyz; a.opacity_raw = opacity_raw; a.log_scale = log_scale; a.rot_raw = rot_raw;
     a.d_xyz = d_xyz; a.d_opacity = d_opacity; a.d_scale = d_scale; a.d_rot = d_rot;
+    a.m_rot = st; st += 4 * n; a.v_rot = st; st += 4 * n;
     a.m_xyz = st; st += 3 * n; a.v_xyz = st; st += 3 * n;
     a.m_op = st; st += n; a.v_op = st; st += n;
     a.m_sc = st; st += 3 * n; a.v_sc = st; st += 3 * n;
-    a.m_rot = st; st += 4 * n; a.v_rot = st; st += 4 * n;
     float* m_f = st; st += 3 * (size_t)M * n;
     float* v_f = st;
     a.lr_xyz = lrs_host[0]; a.lr_op = lrs_host[3]; a.lr_sc = lrs_host[4]; a.lr_rot = lrs_host[5];

@@ -25,7 +25,12 @@
 // First call.  The first call on a device resolves the array's device address with cudaGetSymbolAddress
 // (in host code the name `g_pose_partials` is only a stand-in for the symbol, not an address a kernel could
 // use) and caches it.  Make that first call during start-up, with the device you will use current, and before
-// beginning any stream capture.
+// beginning any stream capture.  The address is cached until the process exits: a cudaDeviceReset after the first
+// call leaves a stale address behind (nothing here can notice a reset), so do not reset a device this has run on.
+//
+// Inputs.  means3D are the points the rasterizer saw and dL_dmeans3D the gradient with respect to them.  After the
+// rigid entry points (gsr_backward_rigid with [R | t]) those are p' = R p + t and g' = R g for the g that call
+// returned, not the raw p and g.
 #include <cstdio>
 #include <mutex>
 

@@ -23,225 +23,13 @@
 
 namespace gsr {
 
-#ifndef GSR_BWD_MIN_BLOCKS
-#define GSR_BWD_MIN_BLOCKS 4
-#endif
 #ifndef GSR_BWD_BATCH
 #define GSR_BWD_BATCH 128      // tile-list entries staged per round
 #endif
-#ifndef GSR_BWD_GROUP
-#define GSR_BWD_GROUP 3        // entries whose partials share one slab reduction
-#endif
 constexpr int NGRAD = 12;
 constexpr int BWD_BATCH = GSR_BWD_BATCH;
-constexpr int GROUP = GSR_BWD_GROUP;
 constexpr int PKB_THREADS = 128;   // packed kernel: 4 warps, two pixels per lane
 constexpr int RED_STRIDE = 36;  // floats per value row of the warp slab (32 lanes + pad; 144 B keeps LDS.128 aligned)
-
-template <bool HAS_DEPTH, bool HAS_ALPHA>
-__global__ void __launch_bounds__(BLEND_THREADS, GSR_BWD_MIN_BLOCKS)
-render_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges,
-                       const uint32_t* __restrict__ point_list, GeomView g, const float* __restrict__ bg,
-                       const float* __restrict__ out_alpha, const uint32_t* __restrict__ n_contrib,
-                       const float* __restrict__ dL_dcolor, const float* __restrict__ dL_ddepth,
-                       const float* __restrict__ dL_dalpha, float* __restrict__ grad)
-{
-    constexpr int NV = HAS_DEPTH ? 10 : 9;   // partials per (pixel, Gaussian) pair
-    constexpr int ROWS = GROUP * NV;         // one slab row per (pending entry, partial); ROWS <= 32
-    static_assert(ROWS <= 32, "one lane sums one slab row");
-    __shared__ StagedT<BWD_BATCH> sm;
-    __shared__ uint32_t sm_gid[BWD_BATCH];
-    __shared__ __align__(16) float acc[BWD_BATCH][NGRAD];
-    __shared__ __align__(16) float red[BLEND_THREADS / 32][ROWS * RED_STRIDE];
-
-    const int tile = blockIdx.x;
-    const int tile_x = tile % grid_x, tile_y = tile / grid_x;
-    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int fx0 = tile_x * TILE + (warp & 1) * FOOT_W, fy0 = tile_y * TILE + (warp >> 1) * FOOT_H;
-    const int pix_x = fx0 + (lane & 7), pix_y = fy0 + (lane >> 3);
-    const bool inside = pix_x < W && pix_y < H;
-    const float pxf = (float)pix_x, pyf = (float)pix_y;
-    const float foot_x0 = (float)fx0, foot_y0 = (float)fy0;
-    const float tile_x0 = (float)(tile_x * TILE), tile_y0 = (float)(tile_y * TILE);
-
-    const uint2 range = ranges[tile];
-    const int total = (int)(range.y - range.x);
-    if (total == 0) return;
-
-    const size_t pid = (size_t)W * pix_y + pix_x;
-    const size_t plane = (size_t)W * H;
-    const float T_final = inside ? (1.f - out_alpha[pid]) : 0.f;
-    float T = T_final;
-    const int last_contributor = inside ? (int)n_contrib[pid] : 0;
-    float dLp0 = 0.f, dLp1 = 0.f, dLp2 = 0.f, dLd = 0.f, dLa = 0.f;
-    if (inside) {
-        dLp0 = dL_dcolor[pid];
-        dLp1 = dL_dcolor[plane + pid];
-        dLp2 = dL_dcolor[2 * plane + pid];
-        if (HAS_DEPTH) dLd = dL_ddepth[pid];
-        if (HAS_ALPHA) dLa = dL_dalpha[pid];
-    }
-    const float bg_dot = bg[0] * dLp0 + bg[1] * dLp1 + bg[2] * dLp2;
-    const bool has_bg = (bg[0] != 0.f) || (bg[1] != 0.f) || (bg[2] != 0.f);   // uniform: black background skips a divide
-    float ar0 = 0.f, ar1 = 0.f, ar2 = 0.f, adr = 0.f, aar = 0.f;   // accum_rec colour / depth / alpha
-    float last_alpha = 0.f, lc0 = 0.f, lc1 = 0.f, lc2 = 0.f, last_depth = 0.f;
-    const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
-
-    // entries at list positions >= max(n_contrib) over the tile never contribute: start there
-    __shared__ int s_start;
-    if (threadIdx.x == 0) s_start = 0;
-    __syncthreads();
-    {
-        int m = last_contributor;
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
-        if (lane == 0 && m > 0) atomicMax(&s_start, m);
-    }
-    __syncthreads();
-    const int start = s_start;              // process positions start-1 ... 0
-    const int warp_last = __reduce_max_sync(0xffffffffu, last_contributor);
-
-    // slab bookkeeping: lane L sums slab row L = (pending entry L / NV, partial L % NV)
-    float* const slab = red[warp];
-    const int my_grp = (int)lane / NV, my_comp = (int)lane - my_grp * NV;
-    const float4* const my_row = reinterpret_cast<const float4*>(slab + lane * RED_STRIDE);
-    int pending = 0, pj0 = 0, pj1 = 0, pj2 = 0;
-
-    // sums the rows of the pending entries and adds them into the per-batch table
-    auto flush_slab = [&]() {
-        __syncwarp();
-        if ((int)lane < pending * NV) {
-            float sacc = 0.f;
-#pragma unroll
-            for (int q = 0; q < 8; q += 2) {
-                const float4 a = my_row[q], b = my_row[q + 1];
-                sacc += ((a.x + a.y) + (a.z + a.w)) + ((b.x + b.y) + (b.z + b.w));
-            }
-            const int jj = my_grp == 0 ? pj0 : (my_grp == 1 ? pj1 : pj2);
-            atomicAdd(&acc[jj][my_comp], sacc);
-        }
-        __syncwarp();
-        pending = 0;
-    };
-
-    for (int base = 0; base < start; base += BWD_BATCH) {
-        __syncthreads();   // previous flush finished
-        const int n = min(BWD_BATCH, start - base);
-        // slot j of this round holds list position (start - 1 - base - j)
-        for (int k = threadIdx.x; k < BWD_BATCH * NGRAD / 4; k += BLEND_THREADS)
-            reinterpret_cast<float4*>(&acc[0][0])[k] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if ((int)threadIdx.x < n) {
-            const uint32_t gid = point_list[range.x + (start - 1 - base - threadIdx.x)];
-            sm_gid[threadIdx.x] = gid;
-            stage_entry(sm, threadIdx.x, gid, g, tile_x0, tile_y0);
-        }
-        __syncthreads();
-
-        for (int c0 = 0; c0 < n; c0 += 32) {
-            // positions of this chunk: pos = start-1-base-(c0+lane) ; whole chunk beyond the warp's last?
-            const int chunk_first_pos = start - 1 - base - c0;   // highest position in the chunk
-            if (chunk_first_pos - 31 >= warp_last) continue;
-            const int e = c0 + lane;
-            bool keep = false;
-            if (e < n && (start - 1 - base - e) < warp_last) {
-                const float thr = sm.thr[e];
-                if (!(thr < 0.f)) {
-                    const float4 r0 = sm.rec0[e];
-                    const float4 r1 = sm.rec1[e];
-                    keep = !reject_rect(r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, thr, foot_x0,
-                                        foot_x0 + (FOOT_W - 1), foot_y0, foot_y0 + (FOOT_H - 1));
-                }
-            }
-            unsigned live = __ballot_sync(0xffffffffu, keep);
-            while (live) {
-                const int j = c0 + __ffs(live) - 1;
-                live &= live - 1;
-                const int pos = start - 1 - base - j;
-                const float4 r0 = sm.rec0[j];
-                const float4 r1 = sm.rec1[j];
-                const float dx = __fadd_rn(r0.x, -pxf), dy = __fadd_rn(r0.y, -pyf);
-                const float power = blend_power(dx, dy, r1.x, r1.y, r1.z);
-                const float G = expf(power);
-                const float alpha = fminf(0.99f, __fmul_rn(r1.w, G));
-                const bool contrib = (pos < last_contributor) && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
-                if (!__any_sync(0xffffffffu, contrib)) continue;
-
-                float v[10];
-#pragma unroll
-                for (int k = 0; k < 10; k++) v[k] = 0.f;
-                if (contrib) {
-                    const float4 r2 = sm.rec2[j];
-                    const float one_m = __fadd_rn(1.f, -alpha);
-                    // T / (1 - alpha): reciprocal seed + one residual correction (<= 1 ulp from the IEEE quotient for
-                    // these operand ranges; saves the slow-path checks of the full divide)
-                    {
-                        float rcp;
-                        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rcp) : "f"(one_m));
-                        const float q = T * rcp;
-                        T = __fmaf_rn(__fmaf_rn(-one_m, q, T), rcp, q);
-                    }
-                    const float aT = alpha * T;
-                    float dL_dopa = 0.f;
-                    ar0 = last_alpha * lc0 + (1.f - last_alpha) * ar0; lc0 = r2.x;
-                    dL_dopa += (r2.x - ar0) * dLp0;
-                    ar1 = last_alpha * lc1 + (1.f - last_alpha) * ar1; lc1 = r2.y;
-                    dL_dopa += (r2.y - ar1) * dLp1;
-                    ar2 = last_alpha * lc2 + (1.f - last_alpha) * ar2; lc2 = r2.z;
-                    dL_dopa += (r2.z - ar2) * dLp2;
-                    v[6] = aT * dLp0; v[7] = aT * dLp1; v[8] = aT * dLp2;
-                    if (HAS_DEPTH) {
-                        adr = last_alpha * last_depth + (1.f - last_alpha) * adr;
-                        last_depth = r2.w;
-                        dL_dopa += (r2.w - adr) * dLd;
-                        v[9] = aT * dLd;
-                    }
-                    if (HAS_ALPHA) {
-                        aar = last_alpha + (1.f - last_alpha) * aar;
-                        dL_dopa += (1.f - aar) * dLa;
-                    }
-                    dL_dopa *= T;
-                    last_alpha = alpha;
-                    if (has_bg) dL_dopa += (-T_final / one_m) * bg_dot;
-                    const float dL_dG = r1.w * dL_dopa;
-                    const float gdx = G * dx, gdy = G * dy;
-                    const float dG_ddelx = -gdx * r1.x - gdy * r1.y;
-                    const float dG_ddely = -gdy * r1.z - gdx * r1.y;
-                    v[0] = dL_dG * dG_ddelx * ddelx_dx;
-                    v[1] = dL_dG * dG_ddely * ddely_dy;
-                    v[2] = -0.5f * gdx * dx * dL_dG;
-                    v[3] = -0.5f * gdx * dy * dL_dG;
-                    v[4] = -0.5f * gdy * dy * dL_dG;
-                    v[5] = G * dL_dopa;
-                }
-                // park this entry's partials in the slab; reduce once GROUP entries are pending
-                {
-                    float* dst = slab + pending * (NV * RED_STRIDE) + lane;
-#pragma unroll
-                    for (int k = 0; k < NV; k++) dst[k * RED_STRIDE] = v[k];
-                    if (pending == 0) pj0 = j; else if (pending == 1) pj1 = j; else pj2 = j;
-                    pending++;
-                    if (pending == GROUP) flush_slab();
-                }
-            }
-        }
-        if (pending) flush_slab();
-        __syncthreads();
-        // flush: one record per entry, three 16-byte vector reductions
-        if ((int)threadIdx.x < n) {
-            const float4 a0 = reinterpret_cast<const float4*>(&acc[threadIdx.x][0])[0];
-            const float4 a1 = reinterpret_cast<const float4*>(&acc[threadIdx.x][0])[1];
-            const float4 a2 = reinterpret_cast<const float4*>(&acc[threadIdx.x][0])[2];
-            const bool nz = (a0.x != 0.f) | (a0.y != 0.f) | (a0.z != 0.f) | (a0.w != 0.f) | (a1.x != 0.f) |
-                            (a1.y != 0.f) | (a1.z != 0.f) | (a1.w != 0.f) | (a2.x != 0.f) | (a2.y != 0.f);
-            if (nz) {
-                float4* dst = reinterpret_cast<float4*>(grad + (size_t)sm_gid[threadIdx.x] * NGRAD);
-                atomicAdd(dst, a0);
-                atomicAdd(dst + 1, a1);
-                atomicAdd(dst + 2, a2);
-            }
-        }
-    }
-}
 
 // ---------------------------------------------------------------------------------------------------------------------
 // Packed variant: two pixels per lane, FP32 pairs (gsr_f32x2.cuh), 128 threads per tile, one 8x8 footprint per warp
@@ -504,23 +292,17 @@ void launch_render_backward(int W, int H, const uint2* ranges, const uint32_t* p
                             float* grad_scratch, cudaStream_t s, bool want_params)
 {
     const int gx = div_up(W, TILE), gy = div_up(H, TILE);
-    const dim3 grid(gx * gy), block(BLEND_THREADS);
-    const bool packed = blend_packed();
+    const dim3 grid(gx * gy);
 #define GSR_LAUNCH(D, A)                                                                                              \
     do {                                                                                                              \
-        if (packed)                                                                                                   \
-            if (want_params)                                                                                          \
-                render_backward_packed_kernel<D, A, true><<<grid, PKB_THREADS, 0, s>>>(                               \
-                    W, H, gx, ranges, point_list, g, bg, out_alpha, n_contrib, dL_dcolor, dL_ddepth, dL_dalpha,       \
-                    grad_scratch);                                                                                    \
-            else                                                                                                      \
-                render_backward_packed_kernel<D, A, false><<<grid, PKB_THREADS, 0, s>>>(                              \
-                    W, H, gx, ranges, point_list, g, bg, out_alpha, n_contrib, dL_dcolor, dL_ddepth, dL_dalpha,       \
-                    grad_scratch);                                                                                    \
+        if (want_params)                                                                                              \
+            render_backward_packed_kernel<D, A, true><<<grid, PKB_THREADS, 0, s>>>(                                   \
+                W, H, gx, ranges, point_list, g, bg, out_alpha, n_contrib, dL_dcolor, dL_ddepth, dL_dalpha,           \
+                grad_scratch);                                                                                        \
         else                                                                                                          \
-            render_backward_kernel<D, A><<<grid, block, 0, s>>>(W, H, gx, ranges, point_list, g, bg, out_alpha,       \
-                                                                n_contrib, dL_dcolor, dL_ddepth, dL_dalpha,           \
-                                                                grad_scratch);                                        \
+            render_backward_packed_kernel<D, A, false><<<grid, PKB_THREADS, 0, s>>>(                                  \
+                W, H, gx, ranges, point_list, g, bg, out_alpha, n_contrib, dL_dcolor, dL_ddepth, dL_dalpha,           \
+                grad_scratch);                                                                                        \
     } while (0)
     if (dL_ddepth && dL_dalpha) GSR_LAUNCH(true, true);
     else if (dL_ddepth) GSR_LAUNCH(true, false);

@@ -14,116 +14,9 @@
 #include "gsr_f32x2.cuh"
 #include "gsr_kernels.h"
 
-#include <cstdlib>
-#include <cstring>
-
 namespace gsr {
 
-// GSR_BLEND=scalar selects the one-pixel-per-lane kernels (kept for A/B measurements); default: packed pairs.
-bool blend_packed()
-{
-    static const bool packed = [] {
-        const char* e = getenv("GSR_BLEND");
-        return !(e && strcmp(e, "scalar") == 0);
-    }();
-    return packed;
-}
-
-#ifndef GSR_FWD_MIN_BLOCKS
-#define GSR_FWD_MIN_BLOCKS 6
-#endif
-__global__ void __launch_bounds__(BLEND_THREADS, GSR_FWD_MIN_BLOCKS)
-render_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges,
-                      const uint32_t* __restrict__ point_list, GeomView g, const float* __restrict__ bg,
-                      float* __restrict__ out_color, float* __restrict__ out_depth, float* __restrict__ out_alpha,
-                      uint32_t* __restrict__ n_contrib)
-{
-    __shared__ Staged sm;
-    const int tile = blockIdx.x;
-    const int tile_x = tile % grid_x, tile_y = tile / grid_x;
-    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int fx0 = tile_x * TILE + (warp & 1) * FOOT_W, fy0 = tile_y * TILE + (warp >> 1) * FOOT_H;
-    const int pix_x = fx0 + (lane & 7), pix_y = fy0 + (lane >> 3);
-    const bool inside = pix_x < W && pix_y < H;
-    const float pxf = (float)pix_x, pyf = (float)pix_y;
-    const float foot_x0 = (float)fx0, foot_y0 = (float)fy0;
-    const float tile_x0 = (float)(tile_x * TILE), tile_y0 = (float)(tile_y * TILE);
-
-    const uint2 range = ranges[tile];
-    const int total = (int)(range.y - range.x);
-    // A finished pixel (outside the image, or T*(1-alpha) < 1e-4 reached) is encoded as T = 0: every later entry then
-    // fails the same T test on its own, so the hot loop needs no separate "done" flag or branch.  The transmittance
-    // the pixel ended with is kept in T_out for the background term.
-    float T = inside ? 1.0f : 0.0f, T_out = 1.0f;
-    float C0 = 0.f, C1 = 0.f, C2 = 0.f, weight = 0.f, Dacc = 0.f;
-    uint32_t last_contributor = 0;
-
-    for (int base = 0; base < total; base += BATCH) {
-        // whole tile finished? (also protects the staging buffers of the previous round)
-        if (__syncthreads_count(T == 0.f) == BLEND_THREADS) break;
-        const int n = min(BATCH, total - base);
-        if ((int)threadIdx.x < n) stage_entry(sm, threadIdx.x, point_list[range.x + base + threadIdx.x], g, tile_x0, tile_y0);
-        __syncthreads();
-
-        for (int c0 = 0; c0 < n; c0 += 32) {
-            if (__all_sync(0xffffffffu, T == 0.f)) break;
-            // one lane per entry: can this entry matter anywhere in the warp's footprint?
-            const int e = c0 + lane;
-            bool keep = false;
-            if (e < n) {
-                const float thr = sm.thr[e];
-                if (!(thr < 0.f)) {
-                    const float4 r0 = sm.rec0[e];
-                    const float4 r1 = sm.rec1[e];
-                    keep = !reject_rect(r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, thr, foot_x0,
-                                        foot_x0 + (FOOT_W - 1), foot_y0, foot_y0 + (FOOT_H - 1));
-                }
-            }
-            unsigned live = __ballot_sync(0xffffffffu, keep);
-            const uint32_t pos0 = (uint32_t)(base + c0 + 1);
-            while (live) {
-                const int b = __ffs(live) - 1;
-                live &= live - 1;
-                const int j = c0 + b;
-                const float4 r0 = sm.rec0[j];
-                const float4 r1 = sm.rec1[j];
-                const float dx = __fadd_rn(r0.x, -pxf), dy = __fadd_rn(r0.y, -pyf);
-                const float power = blend_power(dx, dy, r1.x, r1.y, r1.z);
-                if (power > 0.0f) continue;
-                const float alpha = fminf(0.99f, __fmul_rn(r1.w, expf(power)));
-                if (alpha < 1.0f / 255.0f) continue;
-                const float test_T = __fmul_rn(T, __fadd_rn(1.f, -alpha));
-                if (test_T < 0.0001f) {
-                    if (T != 0.f) { T_out = T; T = 0.f; }   // this pixel is done (forward.cu:352-356)
-                    continue;
-                }
-                const float4 r2 = sm.rec2[j];
-                C0 = __fmaf_rn(T, __fmul_rn(alpha, r2.x), C0);
-                C1 = __fmaf_rn(T, __fmul_rn(alpha, r2.y), C1);
-                C2 = __fmaf_rn(T, __fmul_rn(alpha, r2.z), C2);
-                weight = __fmaf_rn(T, alpha, weight);
-                Dacc = __fmaf_rn(T, __fmul_rn(alpha, r2.w), Dacc);
-                T = test_T;
-                last_contributor = pos0 + (uint32_t)b;
-            }
-        }
-    }
-
-    if (inside) {
-        const float Tf = (T == 0.f) ? T_out : T;
-        const size_t pid = (size_t)W * pix_y + pix_x;
-        const size_t plane = (size_t)W * H;
-        n_contrib[pid] = last_contributor;
-        out_color[pid] = __fmaf_rn(bg[0], Tf, C0);
-        out_color[plane + pid] = __fmaf_rn(bg[1], Tf, C1);
-        out_color[2 * plane + pid] = __fmaf_rn(bg[2], Tf, C2);
-        out_alpha[pid] = weight;
-        out_depth[pid] = Dacc;
-    }
-}
-
-// ---------------------------------------------------------------------------------------------------------------------
-// Packed variant: two pixels per lane, FP32 pairs (gsr_f32x2.cuh).  128 threads per tile; each warp owns an 8x8
+// Two pixels per lane, FP32 pairs (gsr_f32x2.cuh).  128 threads per tile; each warp owns an 8x8
 // footprint and lane (lx, ly) blends pixels (lx, ly) and (lx, ly + 4) of it.  The entry walk, the record loads, dx and
 // the scalar factors dx*A, dx*B are shared by the two pixels; dy, the exponent, alpha, the transmittance and the five
 // accumulators are FFMA2 / FMUL2 / FADD2 pairs.  Per-pixel control flow becomes selects: a pixel that skips an entry
@@ -133,10 +26,7 @@ render_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges
 #ifndef GSR_FWDP_MIN_BLOCKS
 #define GSR_FWDP_MIN_BLOCKS 8
 #endif
-#ifndef GSR_FWDP_WARPS
-#define GSR_FWDP_WARPS 4      // 4: one CTA per tile; 2: one CTA per 16x8 half tile (experiment)
-#endif
-constexpr int PK_WARPS = GSR_FWDP_WARPS;
+constexpr int PK_WARPS = 4;
 constexpr int PK_THREADS = 32 * PK_WARPS;
 constexpr int PK_FOOT = 8;
 
@@ -147,18 +37,15 @@ render_forward_packed_kernel(int W, int H, int grid_x, const uint2* __restrict__
                              float* __restrict__ out_alpha, uint32_t* __restrict__ n_contrib)
 {
     __shared__ Staged sm;
-    constexpr int PARTS = 4 / PK_WARPS;                 // CTAs per tile
-    const int tile = blockIdx.x / PARTS, part = blockIdx.x % PARTS;
+    const int tile = blockIdx.x;
     const int tile_x = tile % grid_x, tile_y = tile / grid_x;
-    const unsigned lane = threadIdx.x & 31, warp = (threadIdx.x >> 5) + part * PK_WARPS;   // footprint index 0..3
+    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;   // footprint index 0..3
     const int fx0 = tile_x * TILE + (warp & 1) * PK_FOOT, fy0 = tile_y * TILE + (warp >> 1) * PK_FOOT;
     const int pix_x = fx0 + (lane & 7), pix_ya = fy0 + (lane >> 3), pix_yb = pix_ya + 4;
     const float pxf = (float)pix_x;
     const f32x2 py2 = pk((float)pix_ya, (float)pix_yb);
     const float foot_x0 = (float)fx0, foot_y0 = (float)fy0;
-    // the rectangle this CTA covers: the whole tile, or its upper / lower half
-    const float tile_x0 = (float)(tile_x * TILE), tile_y0 = (float)(tile_y * TILE + part * (TILE / PARTS));
-    const float rect_h = (float)(TILE / PARTS - 1);
+    const float tile_x0 = (float)(tile_x * TILE), tile_y0 = (float)(tile_y * TILE);
 
     const uint2 range = ranges[tile];
     const int total = (int)(range.y - range.x);
@@ -175,7 +62,7 @@ render_forward_packed_kernel(int W, int H, int grid_x, const uint2* __restrict__
         if (__syncthreads_count(all_done()) == PK_THREADS) break;
         const int n = min(BATCH, total - base);
         for (int k = threadIdx.x; k < n; k += PK_THREADS)
-            stage_entry(sm, k, point_list[range.x + base + k], g, tile_x0, tile_y0, rect_h);
+            stage_entry(sm, k, point_list[range.x + base + k], g, tile_x0, tile_y0);
         __syncthreads();
 
         for (int c0 = 0; c0 < n; c0 += 32) {
@@ -323,40 +210,6 @@ pair_counts_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges, c
     atomicAdd(&counts[1], blended);
     if (threadIdx.x == 0) atomicAdd(&counts[2], (unsigned long long)total * TILE_PIX);
     atomicAdd(&counts[3], tile_rej);
-#ifdef GSR_FOOTPRINT_STATS
-    // experiment: warp iterations with one entry stream per warp (8x4) vs one per half-warp (two 4x4) vs per quarter (4x2)
-    {
-        const int wfx = tile_x * TILE + (warp & 1) * FOOT_W, wfy = tile_y * TILE + (warp >> 1) * FOOT_H;
-        unsigned long long u = 0, h = 0, qd = 0;
-        const int wl = __reduce_max_sync(0xffffffffu, last);
-        for (int base = 0; base < total; base += BATCH) {
-            __syncthreads();
-            const int n = min(BATCH, total - base);
-            if ((int)threadIdx.x < n)
-                stage_entry(sm, threadIdx.x, point_list[range.x + base + threadIdx.x], g, (float)(tile_x * TILE), (float)(tile_y * TILE));
-            __syncthreads();
-            for (int c0 = 0; c0 < n; c0 += 32) {
-                const int e = c0 + lane;
-                bool k8 = false, ka = false, kb = false, q0 = false, q1 = false, q2 = false, q3 = false;
-                if (e < n && base + e < wl && !(sm.thr[e] < 0.f)) {
-                    const float4 r0 = sm.rec0[e]; const float4 r1 = sm.rec1[e]; const float thr = sm.thr[e];
-                    auto rj = [&](float x0, float x1, float y0, float y1) {
-                        return !reject_rect(r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, thr, x0, x1, y0, y1); };
-                    k8 = rj(wfx, wfx + 7, wfy, wfy + 3);
-                    ka = rj(wfx, wfx + 3, wfy, wfy + 3); kb = rj(wfx + 4, wfx + 7, wfy, wfy + 3);
-                    q0 = rj(wfx, wfx + 3, wfy, wfy + 1); q1 = rj(wfx + 4, wfx + 7, wfy, wfy + 1);
-                    q2 = rj(wfx, wfx + 3, wfy + 2, wfy + 3); q3 = rj(wfx + 4, wfx + 7, wfy + 2, wfy + 3);
-                }
-                const int pu = __popc(__ballot_sync(0xffffffffu, k8));
-                const int pa = __popc(__ballot_sync(0xffffffffu, ka)), pb = __popc(__ballot_sync(0xffffffffu, kb));
-                const int p0 = __popc(__ballot_sync(0xffffffffu, q0)), p1 = __popc(__ballot_sync(0xffffffffu, q1));
-                const int p2 = __popc(__ballot_sync(0xffffffffu, q2)), p3 = __popc(__ballot_sync(0xffffffffu, q3));
-                u += pu; h += max(pa, pb); qd += max(max(p0, p1), max(p2, p3));
-            }
-        }
-        if (lane == 0) { atomicAdd(&counts[4], u); atomicAdd(&counts[5], h); atomicAdd(&counts[6], qd); }
-    }
-#endif
 }
 
 void launch_pair_counts(int W, int H, const uint2* ranges, const uint32_t* point_list, const GeomView& g,
@@ -364,9 +217,6 @@ void launch_pair_counts(int W, int H, const uint2* ranges, const uint32_t* point
 {
     const int gx = div_up(W, TILE), gy = div_up(H, TILE);
     cudaMemsetAsync(counts, 0, 4 * sizeof(unsigned long long), s);
-#ifdef GSR_FOOTPRINT_STATS
-    cudaMemsetAsync(counts, 0, 8 * sizeof(unsigned long long), s);
-#endif
     pair_counts_kernel<<<gx * gy, BLEND_THREADS, 0, s>>>(W, H, gx, ranges, point_list, g, n_contrib, counts);
 }
 
@@ -375,12 +225,8 @@ void launch_render_forward(int W, int H, const uint2* ranges, const uint32_t* po
                            uint32_t* n_contrib, cudaStream_t s)
 {
     const int gx = div_up(W, TILE), gy = div_up(H, TILE);
-    if (blend_packed())
-        render_forward_packed_kernel<<<gx * gy * (4 / PK_WARPS), PK_THREADS, 0, s>>>(W, H, gx, ranges, point_list, g, bg, out_color,
-                                                                    out_depth, out_alpha, n_contrib);
-    else
-        render_forward_kernel<<<gx * gy, BLEND_THREADS, 0, s>>>(W, H, gx, ranges, point_list, g, bg, out_color,
-                                                                out_depth, out_alpha, n_contrib);
+    render_forward_packed_kernel<<<gx * gy, PK_THREADS, 0, s>>>(W, H, gx, ranges, point_list, g, bg, out_color, out_depth,
+                                                                out_alpha, n_contrib);
 }
 
 }  // namespace gsr

@@ -15,13 +15,8 @@
 // group's lowest lane bumps a warp-private counter, and popc(mask & lanemask_lt) orders the lanes; warp counters
 // are then scanned across the 8 warps.  Items leave through shared memory in block-sorted order so a warp's
 // stores form a few contiguous runs.
-// A single-kernel "onesweep" pass (global digit histograms from one read of the keys, decoupled look-back over
-// blocks that took earlier atomic tickets, bounded wait that traps instead of hanging) is implemented below and
-// selectable with GSR_SORT=onesweep; on B200 at these sizes (1M keys / 6M instances) it measured 5-15 % slower
-// than the three-kernel pass (look-back latency dominates 2048-item chunks), so it is not the default.
-#include <cstdlib>
-#include <cstring>
-
+// (A single-kernel "onesweep" pass with decoupled look-back measured 5-15 % slower on B200 at these sizes -- 1M keys /
+// 6M instances, look-back latency dominates 2048-item chunks -- and was removed.)
 #include "gsr_kernels.h"
 
 namespace gsr {
@@ -232,169 +227,6 @@ radix_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __res
     }
 }
 
-// ---- onesweep ---------------------------------------------------------------------------------
-constexpr uint32_t ST_EMPTY = 0u, ST_AGG = 1u << 30, ST_PREFIX = 2u << 30, ST_MASK = 3u << 30;
-constexpr int AUX_TICKET = RADIX * SORT_MAX_PASSES;      // + pass
-constexpr int AUX_ERROR = RADIX * SORT_MAX_PASSES + 16;
-
-// global digit histograms of up to SORT_MAX_PASSES digits in one read of the keys
-__global__ void __launch_bounds__(SORT_THREADS)
-radix_global_hist_kernel(const uint32_t* __restrict__ keys, int64_t n, int begin_bit, int end_bit,
-                         uint32_t* __restrict__ aux)
-{
-    __shared__ uint32_t sh[SORT_MAX_PASSES][RADIX];
-    for (int i = threadIdx.x; i < SORT_MAX_PASSES * RADIX; i += SORT_THREADS) (&sh[0][0])[i] = 0;
-    __syncthreads();
-    const unsigned lane = threadIdx.x & 31;
-    const int npass = (end_bit - begin_bit + RADIX_BITS - 1) / RADIX_BITS;
-    for (int64_t base = (int64_t)blockIdx.x * SORT_THREADS; base < n; base += (int64_t)gridDim.x * SORT_THREADS) {
-        const int64_t idx = base + threadIdx.x;
-        const bool act = idx < n;
-        const uint32_t k = act ? keys[idx] : 0u;
-        for (int p = 0; p < npass; p++) {
-            const int shift = begin_bit + p * RADIX_BITS;
-            const uint32_t mask = (1u << min(RADIX_BITS, end_bit - shift)) - 1u;
-            const uint32_t d = act ? ((k >> shift) & mask) : (uint32_t)RADIX;
-            const uint32_t d0 = __shfl_sync(0xffffffffu, d, 0);
-            if (__all_sync(0xffffffffu, d == d0)) {
-                if (lane == 0 && d0 < (uint32_t)RADIX) atomicAdd(&sh[p][d0], 32u);
-            } else if (act) {
-                atomicAdd(&sh[p][d], 1u);
-            }
-        }
-    }
-    __syncthreads();
-    for (int i = threadIdx.x; i < npass * RADIX; i += SORT_THREADS) {
-        const uint32_t c = (&sh[0][0])[i];
-        if (c) atomicAdd(&aux[i], c);
-    }
-}
-
-__global__ void __launch_bounds__(SORT_THREADS)
-radix_onesweep_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
-                      uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int64_t n, int shift,
-                      uint32_t mask, volatile uint32_t* __restrict__ status, uint32_t* __restrict__ aux, int pass)
-{
-    __shared__ uint32_t wcount[SORT_THREADS / 32][RADIX + 1];
-    __shared__ uint32_t goff[RADIX];
-    __shared__ uint32_t warp_sums[8];
-    __shared__ uint32_t skey[SORT_CHUNK], sval[SORT_CHUNK];
-    __shared__ uint32_t s_ticket;
-    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    if (threadIdx.x == 0) s_ticket = atomicAdd(&aux[AUX_TICKET + pass], 1u);
-    for (int i = threadIdx.x; i < (SORT_THREADS / 32) * (RADIX + 1); i += SORT_THREADS) (&wcount[0][0])[i] = 0;
-    // exclusive scan of this pass's global digit histogram
-    const uint32_t dig_base = block_exclusive_scan_256(aux[pass * RADIX + threadIdx.x], warp_sums, nullptr);
-    const uint32_t bid = s_ticket;
-    const int64_t block_base = (int64_t)bid * SORT_CHUNK;
-    const int64_t wbase = block_base + (int64_t)warp * (SORT_ITEMS * 32);
-    uint32_t key[SORT_ITEMS], val[SORT_ITEMS], rank[SORT_ITEMS];
-#pragma unroll
-    for (int i = 0; i < SORT_ITEMS; i++) {
-        const int64_t idx = wbase + i * 32 + lane;
-        const bool act = idx < n;
-        key[i] = act ? keys_in[idx] : 0u;
-        val[i] = act ? vals_in[idx] : 0u;
-    }
-#pragma unroll
-    for (int i = 0; i < SORT_ITEMS; i++) {
-        const bool act = (wbase + i * 32 + lane) < n;
-        const uint32_t d = act ? ((key[i] >> shift) & mask) : (uint32_t)RADIX;
-        const unsigned m = __match_any_sync(0xffffffffu, d);
-        const int leader = __ffs(m) - 1;
-        uint32_t prev = 0;
-        if (lane == (unsigned)leader) {
-            prev = wcount[warp][d];
-            wcount[warp][d] = prev + (uint32_t)__popc(m);
-        }
-        prev = __shfl_sync(0xffffffffu, prev, leader);
-        rank[i] = prev + (uint32_t)__popc(m & ((1u << lane) - 1u));
-        __syncwarp();
-    }
-    __syncthreads();
-    {
-        // thread d owns digit d: block total, publish, look back, then warp bases
-        uint32_t total = 0;
-#pragma unroll
-        for (int w = 0; w < SORT_THREADS / 32; w++) total += wcount[w][threadIdx.x];
-        volatile uint32_t* mine = status + (size_t)bid * RADIX + threadIdx.x;
-        uint32_t excl = 0;
-        if (bid == 0) {
-            *mine = ST_PREFIX | total;
-        } else {
-            *mine = ST_AGG | total;
-            int64_t prev = (int64_t)bid - 1;
-            while (true) {
-                uint32_t v = status[(size_t)prev * RADIX + threadIdx.x];
-                uint32_t spins = 0;
-                while ((v & ST_MASK) == ST_EMPTY) {
-                    if (++spins > (1u << 24)) {   // ~1 s: never hang the GPU, fail loudly instead
-                        atomicExch(&aux[AUX_ERROR], 1u);
-                        asm volatile("trap;");
-                    }
-                    __nanosleep(32);
-                    v = status[(size_t)prev * RADIX + threadIdx.x];
-                }
-                excl += v & ~ST_MASK;
-                if ((v & ST_MASK) != ST_AGG || prev == 0) break;
-                prev--;
-            }
-            *mine = ST_PREFIX | (excl + total);
-        }
-        uint32_t run = block_exclusive_scan_256(total, warp_sums, nullptr);
-        goff[threadIdx.x] = dig_base + excl - run;
-#pragma unroll
-        for (int w = 0; w < SORT_THREADS / 32; w++) {
-            const uint32_t c = wcount[w][threadIdx.x];
-            wcount[w][threadIdx.x] = run;
-            run += c;
-        }
-    }
-    __syncthreads();
-#pragma unroll
-    for (int i = 0; i < SORT_ITEMS; i++) {
-        if ((wbase + i * 32 + lane) < n) {
-            const uint32_t d = (key[i] >> shift) & mask;
-            const uint32_t lp = wcount[warp][d] + rank[i];
-            skey[lp] = key[i];
-            sval[lp] = val[i];
-        }
-    }
-    __syncthreads();
-    const int count = (int)max((int64_t)0, min((int64_t)SORT_CHUNK, n - block_base));
-#pragma unroll
-    for (int i = 0; i < SORT_ITEMS; i++) {
-        const int t = i * SORT_THREADS + threadIdx.x;
-        if (t < count) {
-            const uint32_t k = skey[t];
-            const uint32_t pos = goff[(k >> shift) & mask] + (uint32_t)t;
-            keys_out[pos] = k;
-            vals_out[pos] = sval[t];
-        }
-    }
-}
-
-// GSR_RANK=match|ballot forces one grouping method for every pass (default: chosen per digit)
-static int rank_mode()
-{
-    static int v = -1;
-    if (v < 0) {
-        const char* e = getenv("GSR_RANK");
-        v = !e ? 0 : (strcmp(e, "match") == 0 ? 1 : (strcmp(e, "ballot") == 0 ? 2 : 0));
-    }
-    return v;
-}
-
-static bool use_classic_sort()
-{
-    static int v = -1;
-    if (v < 0) {
-        const char* e = getenv("GSR_SORT");
-        v = (e && strcmp(e, "onesweep") == 0) ? 0 : 1;   // measured on B200: the three-kernel pass is faster at these sizes
-    }
-    return v == 1;
-}
-
 int radix_sort_pairs(uint32_t* keys[2], uint32_t* vals[2], int64_t n, int begin_bit, int end_bit,
                      uint32_t* hist, uint32_t* digit_total, cudaStream_t s, const unsigned long long* n_dev,
                      const uint32_t* first_keys)
@@ -402,43 +234,26 @@ int radix_sort_pairs(uint32_t* keys[2], uint32_t* vals[2], int64_t n, int begin_
     int cur = 0;
     if (n <= 0) return cur;
     const int nblk = div_up(n, SORT_CHUNK);
-    const int npass = (end_bit - begin_bit + RADIX_BITS - 1) / RADIX_BITS;
-    if (first_keys || n_dev || use_classic_sort() || n >= ((int64_t)1 << 30) || npass > SORT_MAX_PASSES) {
-        for (int shift = begin_bit; shift < end_bit; shift += RADIX_BITS) {
-            const int bits = min(RADIX_BITS, end_bit - shift);
-            const uint32_t mask = (1u << bits) - 1u;
-            // first_keys: the first pass reads its keys there and takes the item index as the value, so the caller
-            // does not have to materialise (key, iota) pairs first
-            const bool first = first_keys && shift == begin_bit;
-            const uint32_t* kin = first ? first_keys : keys[cur];
-            const uint32_t* vin = first ? nullptr : vals[cur];
-            radix_hist_kernel<<<nblk, SORT_THREADS, 0, s>>>(kin, n, n_dev, shift, mask, hist, nblk);
-            radix_rowscan_kernel<<<RADIX, SORT_THREADS, 0, s>>>(hist, nblk, digit_total);
-            // the sign/exponent byte of a depth takes few distinct values (MATCH is cheap there); every other digit is
-            // close to all-distinct within a warp
-            const int mode = rank_mode();
-            const bool ballots = mode == 2 || (mode == 0 && !(shift == 24 && end_bit == 32));
+    for (int shift = begin_bit; shift < end_bit; shift += RADIX_BITS) {
+        const int bits = min(RADIX_BITS, end_bit - shift);
+        const uint32_t mask = (1u << bits) - 1u;
+        // first_keys: the first pass reads its keys there and takes the item index as the value, so the caller
+        // does not have to materialise (key, iota) pairs first
+        const bool first = first_keys && shift == begin_bit;
+        const uint32_t* kin = first ? first_keys : keys[cur];
+        const uint32_t* vin = first ? nullptr : vals[cur];
+        radix_hist_kernel<<<nblk, SORT_THREADS, 0, s>>>(kin, n, n_dev, shift, mask, hist, nblk);
+        radix_rowscan_kernel<<<RADIX, SORT_THREADS, 0, s>>>(hist, nblk, digit_total);
+        // the sign/exponent byte of a depth takes few distinct values (MATCH is cheap there); every other digit is
+        // close to all-distinct within a warp
+        const bool ballots = !(shift == 24 && end_bit == 32);
 #define GSR_SCATTER(B)                                                                                                \
     radix_scatter_kernel<B><<<nblk, SORT_THREADS, 0, s>>>(kin, vin, keys[cur ^ 1], vals[cur ^ 1], n, n_dev, shift, mask, \
                                                           hist, nblk, digit_total)
-            if (!ballots) GSR_SCATTER(0);
-            else if (bits <= 5) GSR_SCATTER(5);
-            else GSR_SCATTER(8);
+        if (!ballots) GSR_SCATTER(0);
+        else if (bits <= 5) GSR_SCATTER(5);
+        else GSR_SCATTER(8);
 #undef GSR_SCATTER
-            cur ^= 1;
-        }
-        return cur;
-    }
-    uint32_t* aux = digit_total;
-    cudaMemsetAsync(aux, 0, sizeof(uint32_t) * SORT_AUX_WORDS, s);
-    radix_global_hist_kernel<<<min(nblk, 148 * 8), SORT_THREADS, 0, s>>>(keys[cur], n, begin_bit, end_bit, aux);
-    for (int p = 0; p < npass; p++) {
-        const int shift = begin_bit + p * RADIX_BITS;
-        const int bits = min(RADIX_BITS, end_bit - shift);
-        const uint32_t mask = (1u << bits) - 1u;
-        cudaMemsetAsync(hist, 0, sizeof(uint32_t) * (size_t)RADIX * nblk, s);   // look-back status words
-        radix_onesweep_kernel<<<nblk, SORT_THREADS, 0, s>>>(keys[cur], vals[cur], keys[cur ^ 1], vals[cur ^ 1], n, shift,
-                                                            mask, hist, aux, p);
         cur ^= 1;
     }
     return cur;
@@ -638,13 +453,17 @@ void launch_tile_ranges(const uint32_t* sorted_tiles, int64_t R, uint2* ranges, 
     if (R > 0) tile_ranges_kernel<<<div_up(div_up(R, 4), 256), 256, 0, s>>>(sorted_tiles, R, n_dev, ranges);
 }
 
-// sync-free forward: publish (count, overflow) for the host to look at whenever it likes
+// sync-free forward: publish (count, overflow) for the host to look at whenever it likes.  The status words only ever
+// grow: the count is max-ed and the flags are OR-ed in, so a status buffer shared by many calls (several views, graph
+// replays) still shows an overflow of any one of them until the caller zeroes it.  Calls are stream-ordered, so plain
+// read-modify-write is enough for calls on one stream; atomics make concurrent streams safe as well.
 __global__ void publish_status_kernel(const unsigned long long* __restrict__ counters, long long cap, long long* __restrict__ status)
 {
     const unsigned long long raw = counters[0];
     const unsigned long long n = raw & ((1ull << 62) - 1ull);
-    status[0] = (long long)n;
-    status[1] = (n > (unsigned long long)cap ? 1 : 0) | ((raw >> 62) ? 2 : 0);
+    atomicMax(reinterpret_cast<unsigned long long*>(status), n);
+    const unsigned long long flags = (n > (unsigned long long)cap ? 1ull : 0ull) | ((raw >> 62) ? 2ull : 0ull);
+    if (flags) atomicOr(reinterpret_cast<unsigned long long*>(status + 1), flags);
 }
 
 void launch_publish_status(const unsigned long long* counters, int64_t cap, long long* status, cudaStream_t s)

@@ -53,9 +53,11 @@ class _SyncFree:
     enabled = False
     slack = 1.5
     capacity = {}      # device index -> instances the binning workspace is sized for
-    pending = {}       # device index -> (event, pinned status, device status)
-    last_status = {}   # device index -> (num_rendered, flags) of the most recent checked call
-    device_status = {}  # device index -> status tensor written by the most recent sync-free forward (also under capture)
+    pending = {}       # device index -> (event, pinned copy of the status) of a look that is in flight
+    last_status = {}   # device index -> (num_rendered, overflowed) of the most recent look
+    warned = set()     # devices whose sticky overflow flag has been reported by an in-flight look already
+    device_status = {}  # device index -> the ONE status buffer of that device: every sync-free forward (eager, captured
+    #                     or replayed, any view) max-es its count and ORs its flags into it; only a look clears it
 
 
 def set_sync_free(enabled: bool, slack: float = 1.5, capacity: Optional[int] = None, device: Optional[int] = None) -> None:
@@ -70,29 +72,43 @@ def set_sync_free(enabled: bool, slack: float = 1.5, capacity: Optional[int] = N
 
 
 def sync_free_status(device: Optional[int] = None):
-    """(num_rendered, overflowed) of the latest sync-free forward on `device` -- including one that ran inside a
-    replayed CUDA graph; synchronises.  Call it after graph replays to make sure the capacity was never exceeded."""
+    """(largest num_rendered, overflowed) over every sync-free forward on `device` since the previous look -- eager
+    calls, captured calls and every replay of a captured graph, whichever view they rendered; synchronises and clears
+    the device-side record.  Call it after graph replays: `overflowed` means at least one of those renders was
+    incomplete (its farthest instances were dropped) and has to be repeated with the capacity this call has raised."""
     dev = torch.cuda.current_device() if device is None else device
-    p = _SyncFree.pending.pop(dev, None)
+    _SyncFree.pending.pop(dev, None)
     st = _SyncFree.device_status.get(dev)
     if st is not None:
-        vals = st.cpu()
+        with torch.cuda.device(dev):
+            vals = st.cpu()
+            st.zero_()
+        _SyncFree.warned.discard(dev)
         _absorb_values(dev, int(vals[0]), int(vals[1]))
-    elif p is not None:
-        p[0].synchronize()
-        _absorb_values(dev, int(p[1][0]), int(p[1][1]))
+        _SyncFree.warned.discard(dev)
     return _SyncFree.last_status.get(dev)
 
 
+def _status_buffer(dev: int, device: torch.device) -> torch.Tensor:
+    st = _SyncFree.device_status.get(dev)
+    if st is None:
+        st = torch.zeros(2, dtype=torch.int64, device=device)
+        _SyncFree.device_status[dev] = st
+    return st
+
+
 def _absorb_status(dev: int) -> None:
-    ev, pinned, _ = _SyncFree.pending.pop(dev)
-    _absorb_values(dev, int(pinned[0]), int(pinned[1]))
+    ev, pinned = _SyncFree.pending.pop(dev)
+    # the overflow flag is sticky on the device until sync_free_status() clears it (renders queued behind this look may
+    # have overflowed too and must not be lost): warn once, keep raising the capacity
+    _absorb_values(dev, int(pinned[0]), int(pinned[1]), quiet=dev in _SyncFree.warned)
 
 
-def _absorb_values(dev: int, R: int, flags: int) -> None:
+def _absorb_values(dev: int, R: int, flags: int, quiet: bool = False) -> None:
     _SyncFree.last_status[dev] = (R, bool(flags & 1))
     want = int(R * _SyncFree.slack) + 1024
-    if flags & 1:
+    if flags & 1 and not quiet:
+        _SyncFree.warned.add(dev)
         import warnings
         warnings.warn(f"sync-free rasterizer: {R} tile instances exceeded the binning capacity "
                       f"{_SyncFree.capacity.get(dev)}; that render was incomplete, capacity raised to {want}")
@@ -165,7 +181,7 @@ def _forward_impl(bg, means3D, colors_precomp, opacities, scales, rotations, sca
                 _absorb_status(di)
             cap = _SyncFree.capacity[di]
             binning = torch.empty(lib.gsr_binning_bytes(cap, W, H), **u8)
-            status = torch.empty(2, dtype=torch.int64, device=dev)
+            status = _status_buffer(di, dev)
             check(lib.gsr_forward_fused_rigid(
                 P, int(degree), int(M), _ptr(means3D), _ptr(scales), float(scale_modifier), _ptr(rotations),
                 _ptr(opacities), _ptr(sh), _ptr(cov3Ds_precomp), _ptr(colors_precomp), _ptr(viewmatrix),
@@ -173,13 +189,12 @@ def _forward_impl(bg, means3D, colors_precomp, opacities, scales, rotations, sca
                 radii.data_ptr(), geom.data_ptr(), geom.numel(), binning.data_ptr(), binning.numel(), cap,
                 img.data_ptr(), color.data_ptr(), depth.data_ptr(), alpha.data_ptr(), status.data_ptr(),
                 None if rigid is None else rigid.data_ptr(), stream, int(bool(debug))))
-            _SyncFree.device_status[di] = status
             if not capturing and di not in _SyncFree.pending:
                 pinned = torch.empty(2, dtype=torch.int64).pin_memory()
                 pinned.copy_(status, non_blocking=True)
                 ev = torch.cuda.Event()
                 ev.record()
-                _SyncFree.pending[di] = (ev, pinned, status)
+                _SyncFree.pending[di] = (ev, pinned)
             return cap, color, depth, alpha, radii, geom, binning, img
         word = _count_word(dev)
         check(lib.gsr_forward_prepare_rigid(

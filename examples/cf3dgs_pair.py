@@ -341,6 +341,11 @@ def main():
     res = [run_pair(p, args, dev, backend) for p in mine]
     torch.cuda.synchronize(dev)
     local_s = time.time() - t0
+    overflow = None
+    if args.impl == "ours" and (args.graph or args.sync_free):
+        # every sync-free render of the run (eager, captured, replayed) has OR-ed into the device's status buffer
+        st = D.sync_free_status()
+        overflow = bool(st[1]) if st else False
     rel = GPar.gather_relative_poses({r["pair"]: r["T"] for r in res}, args.pairs) if world > 1 else [r["T"] for r in res]
     poses = GPar.compose_poses(rel)
     if world > 1:
@@ -363,10 +368,14 @@ def main():
                 "gaussian_fit_iters_per_s_aggregate": args.pairs * args.fit_iters / fit_s if fit_s > 0 else None,
                 "max_pose_err_t": err_t, "max_pose_err_r_deg": err_r, "n_poses": len(poses),
                 "fit_loss": res[0]["fit_loss"] if res else None, "pose_loss": res[0]["pose_loss"] if res else None}
+        if overflow is not None:
+            line["binning_overflow"] = overflow
         os.write(real_stdout, (json.dumps(line) + "\n").encode())
     if world > 1:
         import torch.distributed as dist
         dist.destroy_process_group()
+    if overflow:
+        raise SystemExit("a sync-free render ran out of binning capacity: its image was incomplete, the timing is void")
 
 
 if __name__ == "__main__":

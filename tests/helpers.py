@@ -92,3 +92,36 @@ def add_alt_inputs(sc, cam):
 def rel_to_max(a, b):
     a = np.asarray(a, np.float64).reshape(-1); b = np.asarray(b, np.float64).reshape(-1)
     return float(np.abs(a - b).max() / (np.abs(b).max() + 1e-30))
+
+
+def rel_elementwise(a, b, floor_frac=1e-3):
+    """Largest element-wise relative difference |a - b| / max(|b|, floor), floor = floor_frac x the tensor's largest
+    entry: entries below a thousandth of the largest one are compared on the floor's scale (they are sums of float32
+    atomics whose own run-to-run spread is of that size), everything above it gets a true relative comparison."""
+    a = np.asarray(a, np.float64).reshape(-1); b = np.asarray(b, np.float64).reshape(-1)
+    floor = floor_frac * (np.abs(b).max() + 1e-30)
+    return float((np.abs(a - b) / np.maximum(np.abs(b), floor)).max())
+
+
+def diag(msg: str) -> None:
+    """Diagnostics that are reported, not asserted (e.g. how many image values are bit-equal to the reference build):
+    printed (visible with -s / on failure) and appended to gpurun_out/diagnostics.log, which travels back from the box."""
+    print("[diag] " + msg)
+    try:
+        d = os.path.join(ROOT, "gpurun_out")
+        os.makedirs(d, exist_ok=True)
+        with open(os.path.join(d, "diagnostics.log"), "a") as f:
+            f.write(msg + "\n")
+    except OSError:
+        pass
+
+
+def bit_report(name: str, mine, ref) -> None:
+    """How far two float32 images are from bit-equality (diagnostic)."""
+    a = mine.detach().contiguous().view(torch.int32).long().reshape(-1)
+    b = ref.detach().contiguous().view(torch.int32).long().reshape(-1)
+    ne = a != b
+    n = int(ne.sum())
+    worst = int((a - b).abs()[ne].max()) if n else 0
+    diag(f"{name}: {n} of {a.numel()} values differ in bits (largest distance {worst} ulp, "
+         f"max abs {float((mine.detach() - ref.detach()).abs().max()):.3e})")

@@ -51,35 +51,6 @@ def test_fused_loss_matches_reference_formulation(shape, clamp):
     assert err <= 1e-4, err
 
 
-def test_fused_loss_is_faster_than_the_torch_formulation():
-    import gsr_loss
-    img = torch.rand(3, 540, 960, device=DEV)
-    gt = torch.rand(3, 540, 960, device=DEV)
-
-    def run(fn, n=20):
-        for _ in range(3):
-            fn()
-        torch.cuda.synchronize()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for _ in range(n):
-            fn()
-        e1.record(); torch.cuda.synchronize()
-        return e0.elapsed_time(e1) / n
-
-    def fused():
-        a = img.clone().requires_grad_(True)
-        gsr_loss.photometric_loss(a, gt, 0.2, clamp=True).backward()
-
-    def plain():
-        a = img.clone().requires_grad_(True)
-        _ref_loss(a, gt, 0.2, True)[0].backward()
-
-    tf, tp = run(fused), run(plain)
-    print(f"fused {tf:.3f} ms  torch {tp:.3f} ms")
-    assert tf < tp
-
-
 def test_fused_loss_reproduces_the_reference_code_output():
     """Golden vectors made by importing the reference's own trainer/losses.py (tests/golden/make_golden_loss.py)."""
     import glob

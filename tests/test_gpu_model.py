@@ -9,10 +9,11 @@ DEV = "cuda:0"
 LRS = dict(xyz=1.6e-4, f_dc=2.5e-3, f_rest=1.25e-4, opacity=0.05, scaling=5e-3, rotation=1e-3)
 
 
-def test_fused_model_step_matches_torch_adam_through_the_activations():
+@pytest.mark.parametrize("P", [5000, 4999, 1])     # odd counts: every sub-array of the moment buffer then starts off 16 bytes
+def test_fused_model_step_matches_torch_adam_through_the_activations(P):
     import gsr_model
     g = torch.Generator().manual_seed(9)
-    P, M = 5000, 16
+    M = 16
     xyz = torch.randn(P, 3, generator=g).to(DEV)
     feat = (0.3 * torch.randn(P, M, 3, generator=g)).to(DEV)
     opa = torch.randn(P, 1, generator=g).to(DEV)

@@ -16,7 +16,9 @@ def _restore_mode():
     import diff_gaussian_rasterization as D
     yield
     D.set_sync_free(False)
-    D._SyncFree.capacity.clear(); D._SyncFree.pending.clear(); D._SyncFree.last_status.clear()
+    D._SyncFree.capacity.clear(); D._SyncFree.pending.clear(); D._SyncFree.last_status.clear(); D._SyncFree.warned.clear()
+    for st in D._SyncFree.device_status.values():
+        st.zero_()
 
 
 def _scene(P=30000, W=320, H=180, seed=81):
@@ -73,6 +75,46 @@ def test_sync_free_overflow_is_flagged_and_harmless():
     D.set_sync_free(False)
     ref = _step(D, rs, t, gc)
     assert torch.equal(ok[0], ref[0])
+
+
+def test_overflow_of_an_earlier_view_or_replay_is_not_lost():
+    """One status buffer per device, only ever OR-ed / max-ed into by the kernels: an overflowing render followed by
+    renders that fit (another view, later replays of captured graphs) is still reported by the next look."""
+    import diff_gaussian_rasterization as D
+    cam, big = _scene(P=20000)
+    _, small = _scene(P=300, seed=85)
+    rs = cuda_settings(D, cam, (0, 0, 0), 3, DEV)
+    gc = S.cotangents(cam["W"], cam["H"], seed=83, dense=False)["grad_color"].to(DEV)
+    D.set_sync_free(True, capacity=6000)
+    D._SyncFree.slack = 0.0                       # keep the capacity where it is: the graphs below are sized for it
+
+    def fwd(t):
+        return D.GaussianRasterizer(rs)(t["means3D"], torch.zeros_like(t["means3D"]), t["opacities"], shs=t["shs"],
+                                        scales=t["scales"], rotations=t["rotations"])[0]
+
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        fwd(small)
+    torch.cuda.current_stream().wait_stream(side)
+    assert not D.sync_free_status()[1]
+    g_big, g_small = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g_big):
+        fwd(big)
+    with torch.cuda.graph(g_small):
+        fwd(small)
+    g_small.replay(); g_small.replay()
+    R, overflow = D.sync_free_status()
+    assert not overflow and 0 < R <= 6000
+    g_big.replay()                                # needs far more than 6000 instances
+    g_small.replay(); g_small.replay()            # later renders that fit must not hide it
+    with warnings.catch_warnings(record=True):
+        warnings.simplefilter("always")
+        R, overflow = D.sync_free_status()
+    assert overflow and R > 6000
+    g_small.replay()
+    R, overflow = D.sync_free_status()            # the look cleared the record
+    assert not overflow and R <= 6000
 
 
 def test_whole_step_can_be_captured_in_a_cuda_graph():

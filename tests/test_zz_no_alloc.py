@@ -72,6 +72,36 @@ def test_static_scratch_pose_gradient_matches_gsr_backward_twice():
         assert err64 <= 1e-4, (P, err64)
 
 
+def test_static_scratch_after_the_rigid_entry_points_needs_the_moved_points():
+    """gsr_backward_rigid hands back dL/dxyz in the frame of the raw points (R^T g').  The static entry point wants
+    the points the rasterizer saw, p' = R p + t, and the gradient with respect to them, g' = R g; with those it
+    reproduces the rigid call's own dL_dpose for a transform that is not the identity."""
+    import diff_gaussian_rasterization as D
+    import gsr_pose
+    P, W, H = 20000, 200, 120
+    cam = S.make_camera(W, H)
+    sc = S.make_gvol(P, W, H, seed=73, s0=0.02)
+    rs = cuda_settings(D, cam, (0.0, 0.0, 0.0), 3, DEV)
+    T = gsr_pose.se3_exp(torch.tensor([0.05, -0.03, 0.02, 0.02, -0.04, 0.03], dtype=torch.float64)).float().to(DEV)
+    xyz = sc["means3D"].to(DEV).requires_grad_(True)
+    xi = torch.zeros(6, device=DEV, requires_grad=True)
+    color, radii, depth, alpha = gsr_pose.rasterize_with_pose(
+        rs, xi, xyz, T, sc["opacities"].to(DEV), shs=sc["shs"].to(DEV), scales=sc["scales"].to(DEV),
+        rotations=sc["rotations"].to(DEV))
+    ct = S.cotangents(W, H, seed=74, dense=True)
+    ((color * ct["grad_color"].to(DEV)).sum() + (depth * ct["grad_depth"].to(DEV)).sum()).backward()
+    R, t = T[:3, :3], T[:3, 3]
+    moved = (xyz.detach() @ R.T + t).contiguous()
+    g_moved = (xyz.grad @ R.T).contiguous()
+    got = _static_pose_gradient(moved, g_moved)
+    want = xi.grad
+    err = float((got - want).abs().max()) / (float(want.abs().max()) + 1e-30)
+    assert err <= 1e-4, (err, got.tolist(), want.tolist())
+    # the raw points and gradient give something else
+    wrong = _static_pose_gradient(xyz.detach().contiguous(), xyz.grad.contiguous())
+    assert float((wrong - want).abs().max()) / (float(want.abs().max()) + 1e-30) > 1e-3
+
+
 def test_static_scratch_rejects_oversized_and_handles_empty():
     from diff_gaussian_rasterization import _cabi
     out = torch.zeros(6, device=DEV)
