@@ -6,6 +6,7 @@
 
 #include "../../include/gsr.h"
 #include "gsr_kernels.h"
+#include "gsr_launch.cuh"
 
 using namespace gsr;
 
@@ -43,8 +44,9 @@ bool g_ev_used[ST_COUNT];
 
 struct StageTimer {
     int st; cudaStream_t s;
-    StageTimer(int st_, cudaStream_t s_) : st(st_), s(s_) { if (g_prof_on) cudaEventRecord(g_ev[st][0], s); }
-    ~StageTimer() { if (g_prof_on) { cudaEventRecord(g_ev[st][1], s); g_ev_used[st] = true; } }
+    // (an event record is a stream operation of its own: while profiling, stages do not overlap programmatically)
+    StageTimer(int st_, cudaStream_t s_) : st(st_), s(s_) { if (g_prof_on) { cudaEventRecord(g_ev[st][0], s); chain_break(); } }
+    ~StageTimer() { if (g_prof_on) { cudaEventRecord(g_ev[st][1], s); g_ev_used[st] = true; chain_break(); } }
 };
 
 // The event that marks "num_rendered has landed on the host": one per (host thread, device), created on first use and
@@ -75,6 +77,11 @@ int tile_bits(int tiles)
 }  // namespace
 
 namespace gsr {
+bool& pdl_chain_flag()
+{
+    thread_local bool chained = false;
+    return chained;
+}
 // lets other translation units of the library report through gsr_last_error()
 void set_last_error(const char* msg) { snprintf(g_err, sizeof(g_err), "%s", msg ? msg : ""); }
 }  // namespace gsr
@@ -140,8 +147,10 @@ static int depth_sort_and_offsets(int P, const GeomView& g, cudaStream_t s)
         uint32_t* vals[2] = {g.sort_vals[0], g.sort_vals[1]};
         // first pass straight from the depth keys preprocess wrote, values = Gaussian index
         const int cur = radix_sort_pairs(keys, vals, P, 0, 32, g.hist, g.digit_total, s, nullptr, g.depth_key);
-        if (cur != 0)  // keep the invariant "sort_vals[0] holds the depth order"
+        if (cur != 0) {  // keep the invariant "sort_vals[0] holds the depth order"
             cudaMemcpyAsync(g.sort_vals[0], g.sort_vals[1], sizeof(uint32_t) * (size_t)P, cudaMemcpyDeviceToDevice, s);
+            chain_break();
+        }
     }
     { StageTimer t(ST_OFFSETS, s); launch_offsets_scan(g.tiles, g.sort_vals[0], g.offsets, g.block_sums, P, s); }
     return GSR_OK;
@@ -150,7 +159,7 @@ static int depth_sort_and_offsets(int P, const GeomView& g, cudaStream_t s)
 // stages 4-7.  n_layout sizes the binning workspace; with n_dev != nullptr the real count is read on the device.
 static int bin_and_render(int P, int W, int H, int64_t n_layout, const unsigned long long* n_dev, const float* background,
                           void* geometry, void* binning, void* image, float* out_color, float* out_depth,
-                          float* out_alpha, cudaStream_t s, int debug)
+                          float* out_alpha, cudaStream_t s, int debug, bool ranges_zeroed)
 {
     GeomView g;
     geom_layout((char*)geometry, P, g);
@@ -159,6 +168,9 @@ static int bin_and_render(int P, int W, int H, int64_t n_layout, const unsigned 
     BinView b;
     bin_layout((char*)binning, n_layout, b);
     const int gx = div_up(W, TILE), gy = div_up(H, TILE), tiles = gx * gy;
+    // memsets are ordinary stream operations: one between two kernels would undo their programmatic overlap, so the
+    // tile ranges are cleared ahead of the kernel chain
+    if (!ranges_zeroed) cudaMemsetAsync(iv.ranges, 0, sizeof(uint2) * (size_t)tiles, s);
     if (n_layout > 0) {
         { StageTimer t(ST_EMIT, s); launch_emit(g, g.sort_vals[0], P, gx, b.keys[0], b.vals[0], n_layout, s); }
         GSR_STAGE("emit");
@@ -167,7 +179,9 @@ static int bin_and_render(int P, int W, int H, int64_t n_layout, const unsigned 
             const int cur = radix_sort_pairs(b.keys, b.vals, n_layout, 0, tile_bits(tiles), b.hist, b.digit_total, s, n_dev);
             if (cur != 0) {  // invariant: keys[0]/vals[0] hold the sorted list
                 cudaMemcpyAsync(b.keys[0], b.keys[1], sizeof(uint32_t) * (size_t)n_layout, cudaMemcpyDeviceToDevice, s);
+                chain_break();
                 cudaMemcpyAsync(b.vals[0], b.vals[1], sizeof(uint32_t) * (size_t)n_layout, cudaMemcpyDeviceToDevice, s);
+                chain_break();
             }
         }
         GSR_STAGE("tile sort");
@@ -185,8 +199,11 @@ static int bin_and_render(int P, int W, int H, int64_t n_layout, const unsigned 
 static void zero_images(int W, int H, float* out_color, float* out_depth, float* out_alpha, cudaStream_t s)
 {
     cudaMemsetAsync(out_color, 0, sizeof(float) * 3 * (size_t)W * H, s);
+    chain_break();
     cudaMemsetAsync(out_depth, 0, sizeof(float) * (size_t)W * H, s);
+    chain_break();
     cudaMemsetAsync(out_alpha, 0, sizeof(float) * (size_t)W * H, s);
+    chain_break();
 }
 
 int gsr_forward_prepare(int P, int sh_degree, int M, const float* means3D, const float* scales,
@@ -209,6 +226,7 @@ int gsr_forward_prepare_rigid(int P, int sh_degree, int M, const float* means3D,
                               size_t geometry_bytes, int64_t* num_rendered_host, const float* rigid, void* stream,
                               int debug)
 {
+    chain_break();   // whatever ran before this call on the stream is not ours to overlap with
     cudaStream_t s = (cudaStream_t)stream;
     if (!num_rendered_host) return fail(GSR_ERR_INVALID, "num_rendered_host is NULL");
     *num_rendered_host = 0;
@@ -235,7 +253,9 @@ int gsr_forward_prepare_rigid(int P, int sh_degree, int M, const float* means3D,
     cudaError_t e = count_event(&ev);
     if (e != cudaSuccess) return fail(GSR_ERR_CUDA, "event: %s", cudaGetErrorString(e));
     cudaMemcpyAsync(num_rendered_host, g.counters, sizeof(int64_t), cudaMemcpyDeviceToHost, s);
+    chain_break();
     cudaEventRecord(ev, s);
+    chain_break();
 
     depth_sort_and_offsets(P, g, s);   // low 32 key bits (depth) sorted over Gaussians, before duplication
 
@@ -254,6 +274,7 @@ int gsr_forward_render(int P, int W, int H, int64_t num_rendered, const float* b
                        const float* colors_precomp, void* geometry, void* binning, size_t binning_bytes,
                        void* image, float* out_color, float* out_depth, float* out_alpha, void* stream, int debug)
 {
+    chain_break();   // whatever ran before this call on the stream is not ours to overlap with
     cudaStream_t s = (cudaStream_t)stream;
     (void)colors_precomp;
     if (W <= 0 || H <= 0) return fail(GSR_ERR_INVALID, "bad image size");
@@ -268,7 +289,7 @@ int gsr_forward_render(int P, int W, int H, int64_t num_rendered, const float* b
         return fail(GSR_ERR_WORKSPACE, "binning workspace too small: %zu < %zu", binning_bytes,
                     gsr_binning_bytes(num_rendered, W, H));
     return bin_and_render(P, W, H, num_rendered, nullptr, background, geometry, binning, image, out_color, out_depth,
-                          out_alpha, s, debug);
+                          out_alpha, s, debug, false);
 }
 
 int gsr_forward_fused(int P, int sh_degree, int M, const float* means3D, const float* scales, float scale_modifier,
@@ -293,6 +314,7 @@ int gsr_forward_fused_rigid(int P, int sh_degree, int M, const float* means3D, c
                             size_t binning_bytes, int64_t capacity, void* image, float* out_color, float* out_depth,
                             float* out_alpha, int64_t* status, const float* rigid, void* stream, int debug)
 {
+    chain_break();   // whatever ran before this call on the stream is not ours to overlap with
     cudaStream_t s = (cudaStream_t)stream;
     if (!out_color || !out_depth || !out_alpha || !status) return fail(GSR_ERR_INVALID, "outputs and status are required");
     if (capacity < 1 || capacity > 0x7fffffffll) return fail(GSR_ERR_INVALID, "capacity out of range");
@@ -316,13 +338,19 @@ int gsr_forward_fused_rigid(int P, int sh_degree, int M, const float* means3D, c
     a.viewmatrix = viewmatrix; a.projmatrix = projmatrix; a.campos = campos ? campos : viewmatrix;
     a.W = W; a.H = H; a.tanfovx = tanfovx; a.tanfovy = tanfovy; a.prefiltered = 0; a.radii = radii;
     a.rigid = rigid;
+    {
+        ImageView iv;
+        image_layout((char*)image, W, H, iv);
+        cudaMemsetAsync(iv.ranges, 0, sizeof(uint2) * (size_t)div_up(W, TILE) * div_up(H, TILE), s);
+        chain_break();
+    }
     { StageTimer t(ST_PREPROCESS, s); launch_preprocess(a, g, s); }
     GSR_STAGE("preprocess");
     launch_publish_status(g.counters, capacity, (long long*)status, s);
     depth_sort_and_offsets(P, g, s);
     GSR_STAGE("depth sort + offsets");
     return bin_and_render(P, W, H, capacity, g.counters, background, geometry, binning, image, out_color, out_depth,
-                          out_alpha, s, debug);
+                          out_alpha, s, debug, true);
 }
 
 int gsr_backward(int P, int sh_degree, int M, int W, int H, int64_t num_rendered, const float* background,
@@ -354,6 +382,7 @@ int gsr_backward_rigid(int P, int sh_degree, int M, int W, int H, int64_t num_re
                        float* dL_dscales, float* dL_drotations, float* dL_dpose, void* pose_scratch,
                        const float* rigid, void* stream, int debug)
 {
+    chain_break();   // whatever ran before this call on the stream is not ours to overlap with
     cudaStream_t s = (cudaStream_t)stream;
     if (P == 0) {
         if (dL_dpose) cudaMemsetAsync(dL_dpose, 0, 6 * sizeof(float), s);
@@ -406,6 +435,7 @@ int gsr_backward_rigid(int P, int sh_degree, int M, int W, int H, int64_t num_re
 int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
                      uint8_t* present, void* stream)
 {
+    chain_break();   // whatever ran before this call on the stream is not ours to overlap with
     (void)projmatrix;
     cudaStream_t s = (cudaStream_t)stream;
     const int debug = 0;
@@ -450,6 +480,7 @@ int gsr_debug_dump(int P, int W, int H, int64_t num_rendered, const void* geomet
                    uint32_t* n_contrib, float* depths, float* means2D, float* conic_opacity, float* rgb,
                    uint32_t* tiles_touched, uint8_t* clamped, void* stream)
 {
+    chain_break();   // whatever ran before this call on the stream is not ours to overlap with
     cudaStream_t s = (cudaStream_t)stream;
     const int debug = 1;
     if (P == 0) return GSR_OK;
@@ -463,6 +494,7 @@ int gsr_debug_dump(int P, int W, int H, int64_t num_rendered, const void* geomet
     if (keys_sorted && num_rendered > 0) launch_build_keys(b.keys[0], b.vals[0], g.depth_key, num_rendered, g.counters, keys_sorted, s);
     if (point_list && num_rendered > 0)
         cudaMemcpyAsync(point_list, b.vals[0], sizeof(uint32_t) * (size_t)num_rendered, cudaMemcpyDeviceToDevice, s);
+        chain_break();
     if (ranges) cudaMemcpyAsync(ranges, iv.ranges, sizeof(uint2) * (size_t)tiles, cudaMemcpyDeviceToDevice, s);
     if (n_contrib) cudaMemcpyAsync(n_contrib, iv.n_contrib, sizeof(uint32_t) * (size_t)W * H, cudaMemcpyDeviceToDevice, s);
     unpack_geom_kernel<<<div_up(P, 256), 256, 0, s>>>(P, g, depths, means2D, conic_opacity, rgb, tiles_touched, clamped);
@@ -505,6 +537,7 @@ int gsr_profile_read(float* ms_out, int capacity)
 int gsr_debug_pair_counts(int P, int W, int H, int64_t num_rendered, const void* geometry, const void* binning,
                           const void* image, uint64_t* counts, void* stream)
 {
+    chain_break();   // whatever ran before this call on the stream is not ours to overlap with
     cudaStream_t s = (cudaStream_t)stream;
     const int debug = 1;
     if (!counts) return fail(GSR_ERR_INVALID, "counts is NULL");
@@ -524,6 +557,7 @@ size_t gsr_knn_scratch_bytes(int P) { return knn_scratch_bytes(P); }
 
 int gsr_knn_mean_dist2(int P, const float* points, float* mean_dist2, void* scratch, size_t scratch_bytes, void* stream)
 {
+    chain_break();   // whatever ran before this call on the stream is not ours to overlap with
     cudaStream_t s = (cudaStream_t)stream;
     const int debug = 0;
     if (P < 0) return fail(GSR_ERR_INVALID, "P < 0");
@@ -538,6 +572,7 @@ int gsr_knn_mean_dist2(int P, const float* points, float* mean_dist2, void* scra
 
 int gsr_debug_expf_check(uint32_t first_bits, uint32_t count, uint64_t* mismatches, void* stream)
 {
+    chain_break();   // whatever ran before this call on the stream is not ours to overlap with
     cudaStream_t s = (cudaStream_t)stream;
     const int debug = 1;
     if (!mismatches) return fail(GSR_ERR_INVALID, "mismatches is NULL");

@@ -5,6 +5,10 @@
 // instance count (block reduction + one 64-bit atomic per block) so no separate scan is needed to
 // learn num_rendered.
 #include "gsr_kernels.h"
+#ifdef GSR_NO_PDL_PRE
+#define GSR_PDL_OFF_HERE
+#endif
+#include "gsr_launch.cuh"
 #include "gsr_math.cuh"
 
 namespace gsr {
@@ -25,6 +29,8 @@ preprocess_kernel(PreprocessArgs a, GeomView g)
     __shared__ float sV[16], sP[16], sCam[3];
     __shared__ uint32_t warp_sums[PRE_THREADS / 32];
     __shared__ float4 slab[SLAB ? PRE_THREADS * PRE_ROW4 : 1];
+    pdl_wait();
+    pdl_trigger();
     if (SLAB) {
         const int first = blockIdx.x * PRE_THREADS;
         const int rows = min(PRE_THREADS, a.P - first);
@@ -166,9 +172,10 @@ preprocess_kernel(PreprocessArgs a, GeomView g)
 void launch_preprocess(const PreprocessArgs& a, const GeomView& g, cudaStream_t s)
 {
     cudaMemsetAsync(g.counters, 0, 4 * sizeof(unsigned long long), s);
+    chain_break();   // the kernel must not start before the counters are cleared
     const bool slab = a.shs && !a.colors_precomp && a.M == 16 && a.D >= 1 && (((uintptr_t)a.shs) & 15) == 0;
-    if (slab) preprocess_kernel<true><<<div_up(a.P, PRE_THREADS), PRE_THREADS, 0, s>>>(a, g);
-    else preprocess_kernel<false><<<div_up(a.P, PRE_THREADS), PRE_THREADS, 0, s>>>(a, g);
+    if (slab) launch_pdl(preprocess_kernel<true>, div_up(a.P, PRE_THREADS), PRE_THREADS, 0, s, a, g);
+    else launch_pdl(preprocess_kernel<false>, div_up(a.P, PRE_THREADS), PRE_THREADS, 0, s, a, g);
 }
 
 __global__ void mark_visible_kernel(int P, const float* __restrict__ means, const float* __restrict__ view,

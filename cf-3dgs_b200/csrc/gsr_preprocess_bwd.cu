@@ -8,6 +8,10 @@
 // instead of being stored by the forward (saves 48 B/Gaussian of traffic).  Optionally reduces the rigid
 // pose gradient (sum g, sum p x g) per block -- row N1 of SURVEY.md section 8a.
 #include "gsr_kernels.h"
+#ifdef GSR_NO_PDL_PREB
+#define GSR_PDL_OFF_HERE
+#endif
+#include "gsr_launch.cuh"
 #include "gsr_math.cuh"
 
 namespace gsr {
@@ -44,6 +48,8 @@ preprocess_backward_kernel(PreprocessBwdArgs a, GeomView g)
     __shared__ float sV[16], sP[16], sCam[3];
     __shared__ float red[PB_THREADS / 32];
     __shared__ float4 slab[SLAB ? PB_THREADS * SLAB_ROW4 : 1];
+    pdl_wait();
+    pdl_trigger();
     if (SLAB) {
         // coalesced copy-in of this block's SH rows
         const int first = blockIdx.x * PB_THREADS;
@@ -333,6 +339,8 @@ preprocess_backward_kernel(PreprocessBwdArgs a, GeomView g)
 __global__ void __launch_bounds__(256) pose_reduce_kernel(const float* __restrict__ partial, int nblk, float* __restrict__ out)
 {
     __shared__ double red[8];
+    pdl_wait();
+    pdl_trigger();
     for (int c = 0; c < 6; c++) {
         double v = 0.0;
         for (int i = threadIdx.x; i < nblk; i += 256) v += (double)partial[(size_t)i * 6 + c];
@@ -354,9 +362,9 @@ void launch_preprocess_backward(const PreprocessBwdArgs& a, const GeomView& g, c
     const int nblk = div_up(a.P, PB_THREADS);
     // slab path: (P,16,3) coefficients with 16-byte aligned base pointers
     const bool slab = a.shs && a.dL_dsh && a.M == 16 && (((uintptr_t)a.shs | (uintptr_t)a.dL_dsh) & 15) == 0;
-    if (slab) preprocess_backward_kernel<true><<<nblk, PB_THREADS, 0, s>>>(a, g);
-    else preprocess_backward_kernel<false><<<nblk, PB_THREADS, 0, s>>>(a, g);
-    if (a.dL_dpose) pose_reduce_kernel<<<1, 256, 0, s>>>(a.pose_scratch, nblk, a.dL_dpose);
+    if (slab) launch_pdl(preprocess_backward_kernel<true>, nblk, PB_THREADS, 0, s, a, g);
+    else launch_pdl(preprocess_backward_kernel<false>, nblk, PB_THREADS, 0, s, a, g);
+    if (a.dL_dpose) launch_pdl(pose_reduce_kernel, 1, 256, 0, s, (const float*)a.pose_scratch, nblk, a.dL_dpose);
 }
 
 }  // namespace gsr

@@ -20,6 +20,10 @@
 #include "gsr_blend.cuh"
 #include "gsr_f32x2.cuh"
 #include "gsr_kernels.h"
+#ifdef GSR_NO_PDL_BWD
+#define GSR_PDL_OFF_HERE
+#endif
+#include "gsr_launch.cuh"
 
 namespace gsr {
 
@@ -83,6 +87,8 @@ render_backward_packed_kernel(int W, int H, int grid_x, const uint2* __restrict_
     const float foot_x0 = (float)fx0, foot_y0 = (float)fy0;
     const float tile_x0 = (float)(tile_x * TILE), tile_y0 = (float)(tile_y * TILE);
 
+    pdl_wait();
+    pdl_trigger();
     const uint2 range = ranges[tile];
     const int total = (int)(range.y - range.x);
     if (total == 0) return;
@@ -296,11 +302,11 @@ void launch_render_backward(int W, int H, const uint2* ranges, const uint32_t* p
 #define GSR_LAUNCH(D, A)                                                                                              \
     do {                                                                                                              \
         if (want_params)                                                                                              \
-            render_backward_packed_kernel<D, A, true><<<grid, PKB_THREADS, 0, s>>>(                                   \
+            launch_pdl(render_backward_packed_kernel<D, A, true>, grid, PKB_THREADS, 0, s,                            \
                 W, H, gx, ranges, point_list, g, bg, out_alpha, n_contrib, dL_dcolor, dL_ddepth, dL_dalpha,           \
                 grad_scratch);                                                                                        \
         else                                                                                                          \
-            render_backward_packed_kernel<D, A, false><<<grid, PKB_THREADS, 0, s>>>(                                  \
+            launch_pdl(render_backward_packed_kernel<D, A, false>, grid, PKB_THREADS, 0, s,                           \
                 W, H, gx, ranges, point_list, g, bg, out_alpha, n_contrib, dL_dcolor, dL_ddepth, dL_dalpha,           \
                 grad_scratch);                                                                                        \
     } while (0)

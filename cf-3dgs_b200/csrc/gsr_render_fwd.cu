@@ -13,6 +13,10 @@
 #include "gsr_blend.cuh"
 #include "gsr_f32x2.cuh"
 #include "gsr_kernels.h"
+#ifdef GSR_NO_PDL_FWD
+#define GSR_PDL_OFF_HERE
+#endif
+#include "gsr_launch.cuh"
 
 namespace gsr {
 
@@ -47,6 +51,8 @@ render_forward_packed_kernel(int W, int H, int grid_x, const uint2* __restrict__
     const float foot_x0 = (float)fx0, foot_y0 = (float)fy0;
     const float tile_x0 = (float)(tile_x * TILE), tile_y0 = (float)(tile_y * TILE);
 
+    pdl_wait();
+    pdl_trigger();
     const uint2 range = ranges[tile];
     const int total = (int)(range.y - range.x);
     const bool inside_a = pix_x < W && pix_ya < H, inside_b = pix_x < W && pix_yb < H;
@@ -225,8 +231,8 @@ void launch_render_forward(int W, int H, const uint2* ranges, const uint32_t* po
                            uint32_t* n_contrib, cudaStream_t s)
 {
     const int gx = div_up(W, TILE), gy = div_up(H, TILE);
-    render_forward_packed_kernel<<<gx * gy, PK_THREADS, 0, s>>>(W, H, gx, ranges, point_list, g, bg, out_color, out_depth,
-                                                                out_alpha, n_contrib);
+    launch_pdl(render_forward_packed_kernel, gx * gy, PK_THREADS, 0, s, W, H, gx, ranges, point_list, g, bg, out_color,
+               out_depth, out_alpha, n_contrib);
 }
 
 }  // namespace gsr

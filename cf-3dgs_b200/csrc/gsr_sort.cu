@@ -18,6 +18,10 @@
 // (A single-kernel "onesweep" pass with decoupled look-back measured 5-15 % slower on B200 at these sizes -- 1M keys /
 // 6M instances, look-back latency dominates 2048-item chunks -- and was removed.)
 #include "gsr_kernels.h"
+#ifdef GSR_NO_PDL_SORT
+#define GSR_PDL_OFF_HERE
+#endif
+#include "gsr_launch.cuh"
 
 namespace gsr {
 
@@ -37,8 +41,10 @@ radix_hist_kernel(const uint32_t* __restrict__ keys, int64_t n_cap, const unsign
                   int shift, uint32_t mask, uint32_t* __restrict__ hist, int nblk)
 {
     __shared__ uint32_t sh[RADIX];
-    const int64_t n = device_count(n_dev, n_cap);
     sh[threadIdx.x] = 0;
+    pdl_wait();
+    pdl_trigger();
+    const int64_t n = device_count(n_dev, n_cap);
     __syncthreads();
     const int64_t base = (int64_t)blockIdx.x * SORT_CHUNK;
     const unsigned lane = threadIdx.x & 31;
@@ -74,6 +80,8 @@ __global__ void __launch_bounds__(SORT_THREADS)
 radix_rowscan_kernel(uint32_t* __restrict__ hist, int nblk, uint32_t* __restrict__ digit_total)
 {
     __shared__ uint32_t warp_sums[8];
+    pdl_wait();
+    pdl_trigger();
     uint32_t* row = hist + (size_t)blockIdx.x * nblk;
     // rows start at multiples of nblk words: 16-byte accesses only when that keeps them aligned
     const bool vec = (nblk & 3) == 0;
@@ -125,11 +133,13 @@ radix_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __res
 {
     __shared__ uint32_t wcount[SORT_THREADS / 32][RADIX + 1];
     __shared__ uint32_t goff[RADIX];   // global base of digit d for this block minus its block-local start
-    const int64_t n = device_count(n_dev, n_cap);
     __shared__ uint32_t warp_sums[8];
     __shared__ uint32_t skey[SORT_CHUNK], sval[SORT_CHUNK];
     const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (int i = threadIdx.x; i < (SORT_THREADS / 32) * (RADIX + 1); i += SORT_THREADS) (&wcount[0][0])[i] = 0;
+    pdl_wait();
+    pdl_trigger();
+    const int64_t n = device_count(n_dev, n_cap);
     // global base of each digit for this block = exclusive scan of digit totals + row prefix
     uint32_t my_gbase;
     {
@@ -242,14 +252,14 @@ int radix_sort_pairs(uint32_t* keys[2], uint32_t* vals[2], int64_t n, int begin_
         const bool first = first_keys && shift == begin_bit;
         const uint32_t* kin = first ? first_keys : keys[cur];
         const uint32_t* vin = first ? nullptr : vals[cur];
-        radix_hist_kernel<<<nblk, SORT_THREADS, 0, s>>>(kin, n, n_dev, shift, mask, hist, nblk);
-        radix_rowscan_kernel<<<RADIX, SORT_THREADS, 0, s>>>(hist, nblk, digit_total);
+        launch_pdl(radix_hist_kernel, nblk, SORT_THREADS, 0, s, kin, n, n_dev, shift, mask, hist, nblk);
+        launch_pdl(radix_rowscan_kernel, RADIX, SORT_THREADS, 0, s, hist, nblk, digit_total);
         // the sign/exponent byte of a depth takes few distinct values (MATCH is cheap there); every other digit is
         // close to all-distinct within a warp
         const bool ballots = !(shift == 24 && end_bit == 32);
 #define GSR_SCATTER(B)                                                                                                \
-    radix_scatter_kernel<B><<<nblk, SORT_THREADS, 0, s>>>(kin, vin, keys[cur ^ 1], vals[cur ^ 1], n, n_dev, shift, mask, \
-                                                          hist, nblk, digit_total)
+    launch_pdl(radix_scatter_kernel<B>, nblk, SORT_THREADS, 0, s, kin, vin, keys[cur ^ 1], vals[cur ^ 1], n, n_dev, shift, \
+               mask, (const uint32_t*)hist, nblk, (const uint32_t*)digit_total)
         if (!ballots) GSR_SCATTER(0);
         else if (bits <= 5) GSR_SCATTER(5);
         else GSR_SCATTER(8);
@@ -285,6 +295,8 @@ scan_block_sums_kernel(const uint32_t* __restrict__ tiles, const uint32_t* __res
     __shared__ uint32_t warp_sums[8];
     const int base = blockIdx.x * SORT_CHUNK + threadIdx.x * SORT_ITEMS;
     uint32_t sum = 0;
+    pdl_wait();
+    pdl_trigger();
 #pragma unroll
     for (int i = 0; i < SORT_ITEMS; i++)
         if (base + i < P) sum += tiles[order[base + i]];
@@ -301,6 +313,8 @@ scan_final_kernel(const uint32_t* __restrict__ tiles, const uint32_t* __restrict
     const int base = blockIdx.x * SORT_CHUNK + threadIdx.x * SORT_ITEMS;
     uint32_t v[SORT_ITEMS];
     uint32_t sum = 0;
+    pdl_wait();
+    pdl_trigger();
 #pragma unroll
     for (int i = 0; i < SORT_ITEMS; i++) {
         v[i] = (base + i < P) ? tiles[order[base + i]] : 0u;
@@ -324,8 +338,8 @@ void launch_offsets_scan(const uint32_t* tiles, const uint32_t* order, uint32_t*
                          int P, cudaStream_t s)
 {
     const int nblk = div_up(P, SORT_CHUNK);
-    scan_block_sums_kernel<<<nblk, SORT_THREADS, 0, s>>>(tiles, order, P, block_sums);
-    scan_final_kernel<<<nblk, SORT_THREADS, 0, s>>>(tiles, order, P, block_sums, offsets);
+    launch_pdl(scan_block_sums_kernel, nblk, SORT_THREADS, 0, s, tiles, order, P, block_sums);
+    launch_pdl(scan_final_kernel, nblk, SORT_THREADS, 0, s, tiles, order, P, (const uint32_t*)block_sums, offsets);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -348,6 +362,8 @@ emit_kernel(const uint32_t* __restrict__ order, const uint32_t* __restrict__ til
     const int r = blockIdx.x * EMIT_THREADS + threadIdx.x;
     uint32_t off = 0xffffffffu, gid = 0, n = 0;
     uint2 rc = make_uint2(0u, 0u);
+    pdl_wait();
+    pdl_trigger();
     if (r < P) {
         gid = order[r];
         off = offsets[r];
@@ -409,8 +425,8 @@ emit_kernel(const uint32_t* __restrict__ order, const uint32_t* __restrict__ til
 void launch_emit(const GeomView& g, const uint32_t* order, int P, int grid_x, uint32_t* tile_keys,
                  uint32_t* tile_vals, int64_t cap, cudaStream_t s)
 {
-    emit_kernel<<<div_up(P, EMIT_THREADS), EMIT_THREADS, 0, s>>>(order, g.tiles, g.offsets, g.rect, P, grid_x, tile_keys,
-                                                                 tile_vals, (uint32_t)cap);
+    launch_pdl(emit_kernel, div_up(P, EMIT_THREADS), EMIT_THREADS, 0, s, order, (const uint32_t*)g.tiles,
+               (const uint32_t*)g.offsets, (const uint2*)g.rect, P, grid_x, tile_keys, tile_vals, (uint32_t)cap);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -420,6 +436,8 @@ tile_ranges_kernel(const uint32_t* __restrict__ sorted_tiles, int64_t R_cap,
                    const unsigned long long* __restrict__ n_dev, uint2* __restrict__ ranges)
 {
     // four consecutive entries per thread (one 16-byte load) plus the entry before them
+    pdl_wait();
+    pdl_trigger();
     const int64_t R = device_count(n_dev, R_cap);
     const int64_t i0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
     if (i0 >= R) return;
@@ -449,8 +467,8 @@ tile_ranges_kernel(const uint32_t* __restrict__ sorted_tiles, int64_t R_cap,
 void launch_tile_ranges(const uint32_t* sorted_tiles, int64_t R, uint2* ranges, int tiles, cudaStream_t s,
                         const unsigned long long* n_dev)
 {
-    cudaMemsetAsync(ranges, 0, sizeof(uint2) * (size_t)tiles, s);
-    if (R > 0) tile_ranges_kernel<<<div_up(div_up(R, 4), 256), 256, 0, s>>>(sorted_tiles, R, n_dev, ranges);
+    (void)tiles;   // the caller has zeroed ranges (empty tiles read (0,0), rasterizer_impl.cu:311)
+    if (R > 0) launch_pdl(tile_ranges_kernel, div_up(div_up(R, 4), 256), 256, 0, s, sorted_tiles, R, n_dev, ranges);
 }
 
 // sync-free forward: publish (count, overflow) for the host to look at whenever it likes.  The status words only ever
@@ -459,6 +477,8 @@ void launch_tile_ranges(const uint32_t* sorted_tiles, int64_t R, uint2* ranges, 
 // read-modify-write is enough for calls on one stream; atomics make concurrent streams safe as well.
 __global__ void publish_status_kernel(const unsigned long long* __restrict__ counters, long long cap, long long* __restrict__ status)
 {
+    pdl_wait();
+    pdl_trigger();
     const unsigned long long raw = counters[0];
     const unsigned long long n = raw & ((1ull << 62) - 1ull);
     atomicMax(reinterpret_cast<unsigned long long*>(status), n);
@@ -468,7 +488,7 @@ __global__ void publish_status_kernel(const unsigned long long* __restrict__ cou
 
 void launch_publish_status(const unsigned long long* counters, int64_t cap, long long* status, cudaStream_t s)
 {
-    publish_status_kernel<<<1, 1, 0, s>>>(counters, (long long)cap, status);
+    launch_pdl(publish_status_kernel, 1, 1, 0, s, counters, (long long)cap, status);
 }
 
 __global__ void build_keys_kernel(const uint32_t* __restrict__ sorted_tiles, const uint32_t* __restrict__ point_list,
