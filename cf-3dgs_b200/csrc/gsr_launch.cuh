@@ -45,11 +45,7 @@ inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, s
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
-#ifdef GSR_PDL_OFF_HERE
-    cfg.numAttrs = 0;
-#else
     cfg.numAttrs = overlap ? 1 : 0;
-#endif
     return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 

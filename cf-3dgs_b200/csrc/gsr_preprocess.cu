@@ -5,9 +5,6 @@
 // instance count (block reduction + one 64-bit atomic per block) so no separate scan is needed to
 // learn num_rendered.
 #include "gsr_kernels.h"
-#ifdef GSR_NO_PDL_PRE
-#define GSR_PDL_OFF_HERE
-#endif
 #include "gsr_launch.cuh"
 #include "gsr_math.cuh"
 

@@ -8,9 +8,6 @@
 // instead of being stored by the forward (saves 48 B/Gaussian of traffic).  Optionally reduces the rigid
 // pose gradient (sum g, sum p x g) per block -- row N1 of SURVEY.md section 8a.
 #include "gsr_kernels.h"
-#ifdef GSR_NO_PDL_PREB
-#define GSR_PDL_OFF_HERE
-#endif
 #include "gsr_launch.cuh"
 #include "gsr_math.cuh"
 

@@ -20,9 +20,6 @@
 #include "gsr_blend.cuh"
 #include "gsr_f32x2.cuh"
 #include "gsr_kernels.h"
-#ifdef GSR_NO_PDL_BWD
-#define GSR_PDL_OFF_HERE
-#endif
 #include "gsr_launch.cuh"
 
 namespace gsr {

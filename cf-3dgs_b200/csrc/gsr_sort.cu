@@ -18,9 +18,6 @@
 // (A single-kernel "onesweep" pass with decoupled look-back measured 5-15 % slower on B200 at these sizes -- 1M keys /
 // 6M instances, look-back latency dominates 2048-item chunks -- and was removed.)
 #include "gsr_kernels.h"
-#ifdef GSR_NO_PDL_SORT
-#define GSR_PDL_OFF_HERE
-#endif
 #include "gsr_launch.cuh"
 
 namespace gsr {
