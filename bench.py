@@ -7,8 +7,14 @@ one fwd+bwd rasterization per step through the reference-shaped API (GaussianRas
 C ABI -> sm_100a kernels), colour cotangent only (CF-3DGS default: depth/alpha losses off).
 N>1 (one process per GPU, weak scaling): `value` is the sharded form north_star asks near-linear scaling of -- independent
 frame pairs, every rank renders its own view of its own model replica with NO data-path collective (SURVEY.md 8e (i));
-value = N * frames / max-over-ranks time.  The same run also times the batched-views form (8e (ii)): the same step
-followed by one NCCL all-reduce of the flat 59-float/Gaussian gradient, reported as `allreduce_variant`.
+value = N * frames / max-over-ranks time.  The same run measures the second half of BASELINE.json's metric and the form
+that does communicate, as top-level numeric fields of the same JSON line:
+  pose_opt_iters_per_s          CF-3DGS frame pairs sharded over the ranks (2 pairs per GPU, examples/cf3dgs_pair.py),
+  gaussian_fit_iters_per_s      the local Gaussian fits of the same pairs,
+  global_views_iters_per_s_sh0 / _sh3 and global_views_per_s_sh0 / _sh3
+                                batched global views (8e (ii), examples/cf3dgs_global.py --batched): replicated 1.04 M-
+                                Gaussian model, one view per rank per optimiser step, gradients written into one flat
+                                buffer and all-reduced over NCCL (only the active SH bands), fused Adam on every rank.
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
 
@@ -40,6 +46,10 @@ PARAM_KEYS = ["means3D", "opacities", "shs", "scales", "rotations"]
 # DRAM bytes per launch of the kernels that can dominate, from the committed ncu capture of this workload
 NCU_TRAFFIC_BYTES = {"render_backward": 150.8e6 + 17.5e6, "render_forward": 66.8e6 + 29.3e6,
                      "preprocess": 253.4e6 + 40.2e6, "preprocess_backward": 284.3e6 + 198.6e6}
+# warp instructions per launch of the two blend kernels on this workload (smsp__inst_executed.sum, same ncu capture):
+# what their issue-slot utilisation is computed from
+NCU_WARP_INSTRUCTIONS = {"render_backward": 659.25e6, "render_forward": 392.0e6}
+NCU_SOURCE = "profiles/r01_ncu_packed_summary.txt"
 
 
 def load_peaks():
@@ -58,8 +68,9 @@ class ClockSampler:
 
     def __init__(self, index):
         self.index = index
-        self.rows = []
+        self.rows = []       # (host time the row was read, row)
         self.proc = None
+        self.marks = {}
 
     def start(self):
         try:
@@ -73,20 +84,28 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append(line.strip())
+            self.rows.append((time.time(), line.strip()))
+
+    def mark(self, name):
+        self.marks[name] = time.time()
 
     def stop(self):
+        """Clocks over [load_begin, load_end] -- the timed K steps plus the same step repeated right after them for long
+        enough to collect samples -- with the number of samples that fell inside the timed K steps themselves."""
         if self.proc is None:
             return None
-        time.sleep(0.15)
         self.proc.terminate()
         try:
             self.proc.wait(timeout=2)
         except Exception:
             self.proc.kill()
-        sm, mx, reasons = [], [], set()
+        lo, hi = self.marks.get("load_begin", 0.0), self.marks.get("load_end", float("inf"))
+        t0, t1 = self.marks.get("timed_begin", lo), self.marks.get("timed_end", hi)
+        sm, mx, reasons, inside = [], [], set(), 0
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
+        for ts, r in self.rows:
+            if not (lo <= ts <= hi + 0.03):
+                continue
             parts = [x.strip() for x in r.split(",")]
             if len(parts) < 7:
                 continue
@@ -94,12 +113,15 @@ class ClockSampler:
                 sm.append(float(parts[0])); mx.append(float(parts[1]))
             except ValueError:
                 continue
+            inside += int(t0 <= ts <= t1 + 0.03)
             for n, v in zip(names, parts[3:7]):
                 if v.lower().startswith("active"):
                     reasons.add(n)
         if not sm:
             return None
-        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
+        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm),
+                "samples_inside_timed_steps": inside,
+                "window": "the timed steps plus the same step repeated for >= 0.5 s directly after them (under load throughout)"}
 
 
 def dist_setup(n_gpus, init=True):
@@ -133,21 +155,36 @@ def timed(step, K, warm, world, dev, clock_index=None):
     for _ in range(warm):
         step()
     sampler = ClockSampler(clock_index) if clock_index is not None else None
+    if sampler:
+        sampler.start()
+        time.sleep(0.05)
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize(dev)
     if sampler:
-        sampler.start()
+        sampler.mark("load_begin"); sampler.mark("timed_begin")
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(K):
         step()
     e1.record()
     torch.cuda.synchronize(dev)
+    if sampler:
+        sampler.mark("timed_end")
     if world > 1:
         dist.barrier()
     ms = e0.elapsed_time(e1)
-    clocks = sampler.stop() if sampler else None
+    clocks = None
+    if sampler:
+        # nvidia-smi samples every 20 ms and the K timed steps may last less than that: keep the same load on the GPU
+        # until the sampler has seen it for half a second, so the clock record speaks about this workload
+        t_end = time.time() + max(0.5 - ms / 1000.0, 0.1)
+        while time.time() < t_end:
+            for _ in range(10):
+                step()
+            torch.cuda.synchronize(dev)
+        sampler.mark("load_end")
+        clocks = sampler.stop()
     if world > 1:
         t = torch.tensor([ms], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -191,6 +228,48 @@ def torch_cpu_baseline(S):
                       "not the 1M/1080p workload"}
 
 
+def run_loops(dev, rank, world):
+    """The second half of BASELINE.json's metric ("pose-opt iters/s at 1/2/4/8 GPU") and the batched-global-views form,
+    measured in the same process right after the frames/s numbers (all ranks take part).  Returns a flat dict of numeric
+    top-level fields for the JSON line."""
+    sys.path.insert(0, os.path.join(ROOT, "examples"))
+    import cf3dgs_pair as CP
+    import cf3dgs_global as CG
+    import diff_gaussian_rasterization as D
+    out = {}
+    # (i) CF-3DGS frame pairs, 2 per GPU: local Gaussian fit (200 iterations) + pose fit (300 iterations, the reference's
+    # count, trainer/cf3dgs_trainer.py:262-285), each loop one replayed CUDA graph; no data-path collective
+    pargs = CP.default_args(pairs=2 * world, fit_iters=200, pose_iters=300, graph=True)
+    line, overflow = CP.run_sharded(pargs, dev, rank, world)
+    D.sync_free_status(); D.set_sync_free(False)
+    D._SyncFree.capacity.clear()
+    if rank == 0:
+        out["pose_opt_iters_per_s"] = line["pose_opt_iters_per_s_aggregate"]
+        out["gaussian_fit_iters_per_s"] = line["gaussian_fit_iters_per_s_aggregate"]
+        out["pair_loop"] = {"pairs": line["pairs"], "P": line["P"], "W": line["W"], "H": line["H"], "fit_iters": 200,
+                            "pose_iters": 300, "max_pose_err_t": line["max_pose_err_t"],
+                            "max_pose_err_r_deg": line["max_pose_err_r_deg"], "binning_overflow": bool(overflow),
+                            "what": "examples/cf3dgs_pair.py --graph: 518 k-Gaussian local models at 960x540, 2 pairs per GPU, "
+                                    "pairs sharded over the ranks, one gather of the relative poses at the end"}
+    # (ii) batched global views: replicated 1.04 M-Gaussian model, one view per rank per optimiser step, NCCL all-reduce of
+    # the flat gradient (only the active SH bands), fused Adam on every rank; at SH degree 0 and 3
+    for deg in (0, 3):
+        gargs = CG.default_config(frames=8, points_per_frame=130_000, iters=100, sh_degree=deg, batched=True, warmup=10)
+        g = CG.run_global(gargs, dev, rank, world)
+        if rank == 0:
+            out[f"global_views_iters_per_s_sh{deg}"] = g["iters_per_s"]
+            out[f"global_views_per_s_sh{deg}"] = g["views_per_s"]
+            out.setdefault("global_views_loop", {})[f"sh{deg}"] = {
+                "P": g["P"], "allreduce_bytes": g["allreduce_bytes"] if world > 1 else 0,
+                "floats_per_gaussian": g["allreduce_floats_per_gaussian"], "replicas_bit_identical": g["replicas_bit_identical"],
+                "ms_per_iter": g["ms_per_iter"], "last_loss": g["last_loss"]}
+    if rank == 0:
+        out["global_views_loop"]["what"] = ("examples/cf3dgs_global.py --batched: full iteration (activations, render, fused "
+                                            "L1+SSIM, backward into the flat buffer, all-reduce in 1 + 4 pieces overlapped with the "
+                                            "fused Adam parts, densification statistics), 960x540, 8 training views")
+    return out
+
+
 _REAL_STDOUT = None
 
 
@@ -216,6 +295,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="run the end-to-end step eagerly instead of replaying a CUDA graph")
+    ap.add_argument("--no-loops", action="store_true", help="skip the CF-3DGS pair / global-views loops (pose_opt_iters_per_s ...)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     world, rank, local = dist_setup(args.gpus, init=(args.impl == "ours"))
@@ -253,9 +333,19 @@ def main():
     flat_grad = torch.empty(P * 59, device=dev) if world > 1 else None
     state = {}
 
+    peaks = None
     if args.impl == "ours":
         import diff_gaussian_rasterization as D
         lib = D.lib
+        if rank == 0:
+            # measured ceilings for the blend kernels (FFMA, FFMA2, MUFU.EX2, LDS), before anything is timed
+            import ctypes
+            buf4 = (ctypes.c_double * 4)()
+            if lib.gsr_measure_peaks(buf4, torch.cuda.current_stream().cuda_stream) == 0:
+                peaks = {"ffma_tflops": buf4[0] / 1e12, "ffma2_tflops": buf4[1] / 1e12, "mufu_ex2_gops": buf4[2] / 1e9,
+                         "lds_gbs": buf4[3] / 1e9, "issue_gwarp_inst_per_s": buf4[0] / 64.0 / 1e9,
+                         "how": "gsr_measure_peaks (csrc/gsr_peaks.cu): 8 CTAs x 256 threads per SM, best of 3 after a warm-up "
+                                "run, CUDA events; issue ceiling = FFMA warp instructions per second"}
         rs = D.GaussianRasterizationSettings(image_height=H, image_width=W, tanfovx=cam["tanfovx"], tanfovy=cam["tanfovy"],
                                              bg=bg, scale_modifier=1.0, viewmatrix=view, projmatrix=proj,
                                              sh_degree=wl["sh_degree"], campos=campos, prefiltered=False, debug=False)
@@ -425,6 +515,9 @@ def main():
         if ovf is not None and ovf[1]:
             raise SystemExit("bench: sync-free binning capacity overflowed; the e2e number would be invalid")
 
+    loops = {}
+    if args.impl == "ours" and not args.no_loops:
+        loops = run_loops(dev, rank, world)
     if rank != 0:
         return 0
     line = {"metric": "fwd+bwd rendered frames/s at 1080p", "value": value, "unit": "frames/s", "n_gpus": world,
@@ -438,6 +531,9 @@ def main():
                     "what": "per step: camera + target image H2D from pinned memory (double-buffered on a copy stream), "
                             "render + L1 loss + backward (" + ("one CUDA graph replay, sync-free forward" if use_graph else "eager") +
                             "), loss D2H + sync"}}
+    line.update(loops)
+    if peaks is not None:
+        line["measured_peaks"] = peaks
     if two_stream is not None:
         line["two_stream_variant"] = {"what": "two views in flight on two CUDA streams (batched views on one GPU): one view's "
                                               "latency-bound binning overlaps the other's blend kernels",
@@ -451,6 +547,7 @@ def main():
         line["impl"] = "reference"
         line["n_gpus"] = args.gpus          # the run it belongs to; the reference itself runs on rank 0 alone
         line["ranks_used"] = 1
+        line["comparable_n"] = 1            # one GPU's worth of work: compare with the N = 1 line of the other arm only
         line["gpu_launches"] = 0
         line["cpu_baseline"] = {"value": value, "unit": "frames/s", "cores": 0, "kind": "reference",
                                 "sample": "the reference's own CUDA rasterizer (oracle/_ref, unmodified sources, sm_100a) "
@@ -487,7 +584,12 @@ def main():
     tiles = ((W + 15) // 16) * ((H + 15) // 16)
     sm_mhz = (clocks or {}).get("sm_mhz") or 1500.0
     n_sm = torch.cuda.get_device_properties(dev).multi_processor_count
-    fp32_peak = n_sm * 128 * 2 * sm_mhz * 1e6 / 1e12
+    if peaks is not None:
+        fp32_peak = peaks["ffma_tflops"]
+        fp32_source = "measured FFMA peak of this GPU in this run (gsr_measure_peaks, csrc/gsr_peaks.cu)"
+    else:
+        fp32_peak = n_sm * 128 * 2 * sm_mhz * 1e6 / 1e12
+        fp32_source = f"derived FP32 FMA peak {n_sm} SMs x 128 lanes x 2 x {sm_mhz:.0f} MHz (the microbenchmark did not run)"
     # algorithmic work: bytes for the HBM-bound stages, flops for the blend kernels
     alg = {
         "preprocess": ("hbm", (P_vis * 311 + (P - P_vis) * 20) / 1e9),
@@ -509,6 +611,12 @@ def main():
         peak = hbm_peak if bound == "hbm" else fp32_peak
         stages[n] = {"ms": t, "bound": bound, "achieved": ach, "unit": "GB/s" if bound == "hbm" else "TFLOP/s",
                      "frac": ach / peak}
+        if n in NCU_WARP_INSTRUCTIONS and peaks is not None:
+            # an issue-bound kernel is also judged against the issue-slot ceiling: warp instructions per second
+            rate = NCU_WARP_INSTRUCTIONS[n] / (t / 1000.0) / 1e9
+            stages[n]["issue"] = {"achieved_gwarp_inst_per_s": rate, "peak_gwarp_inst_per_s": peaks["issue_gwarp_inst_per_s"],
+                                  "frac": rate / peaks["issue_gwarp_inst_per_s"],
+                                  "warp_instructions_per_launch": NCU_WARP_INSTRUCTIONS[n], "source": NCU_SOURCE}
     dom = max(stages, key=lambda k: stages[k]["ms"])
     d = stages[dom]
     line["roofline"] = {"kernel": dom, "bound": d["bound"], "achieved": d["achieved"],
@@ -516,9 +624,9 @@ def main():
                         "traffic": NCU_TRAFFIC_BYTES.get(dom), "ms": d["ms"],
                         "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full, "
                                           "profiles/r01_ncu_packed_summary.txt (same workload)",
-                        "peak_source": (f"{peak_kind} HBM copy" if d["bound"] == "hbm" else
-                                        f"derived FP32 FMA peak {n_sm} SMs x 128 lanes x 2 x {sm_mhz:.0f} MHz (median SM clock "
-                                        "under load); MEASURED_PEAKS.json holds no FP32 figure")}
+                        "peak_source": (f"{peak_kind} HBM copy" if d["bound"] == "hbm" else fp32_source)}
+    if "issue" in d:
+        line["roofline"]["issue_slot_frac"] = d["issue"]["frac"]
     line["stages"] = stages
     line["work"] = {"num_rendered": R, "visible": P_vis, "pairs_in_range": in_range, "pairs_blended": blended,
                     "reference_pairs_no_early_exit": ref_pairs, "tile_rejected_entries": tile_rej}

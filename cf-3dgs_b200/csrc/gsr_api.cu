@@ -367,7 +367,7 @@ int gsr_backward(int P, int sh_degree, int M, int W, int H, int64_t num_rendered
     return gsr_backward_rigid(P, sh_degree, M, W, H, num_rendered, background, means3D, radii, colors_precomp, scales,
                               rotations, scale_modifier, cov3D_precomp, viewmatrix, projmatrix, campos, tanfovx, tanfovy,
                               shs, out_alpha, dL_dout_color, dL_dout_depth, dL_dout_alpha, geometry, binning, image,
-                              grad_scratch, dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh,
+                              grad_scratch, dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, M,
                               dL_dscales, dL_drotations, dL_dpose, pose_scratch, nullptr, stream, debug);
 }
 
@@ -379,7 +379,7 @@ int gsr_backward_rigid(int P, int sh_degree, int M, int W, int H, int64_t num_re
                        const float* dL_dout_depth, const float* dL_dout_alpha, const void* geometry,
                        const void* binning, const void* image, void* grad_scratch, float* dL_dmeans2D,
                        float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh,
-                       float* dL_dscales, float* dL_drotations, float* dL_dpose, void* pose_scratch,
+                       int dsh_M, float* dL_dscales, float* dL_drotations, float* dL_dpose, void* pose_scratch,
                        const float* rigid, void* stream, int debug)
 {
     chain_break();   // whatever ran before this call on the stream is not ours to overlap with
@@ -397,6 +397,9 @@ int gsr_backward_rigid(int P, int sh_degree, int M, int W, int H, int64_t num_re
     if ((dL_dscales == nullptr) != (dL_drotations == nullptr))
         return fail(GSR_ERR_INVALID, "dL_dscales and dL_drotations are written together: pass both or neither");
     if (dL_dpose && !pose_scratch) return fail(GSR_ERR_INVALID, "pose_scratch is required with dL_dpose");
+    if (shs && dL_dsh && (dsh_M < (sh_degree + 1) * (sh_degree + 1) || dsh_M > M))
+        return fail(GSR_ERR_INVALID, "dsh_M=%d must hold the %d active coefficients and not exceed M=%d", dsh_M,
+                    (sh_degree + 1) * (sh_degree + 1), M);
     GeomView g;
     geom_layout((char*)geometry, P, g);
     ImageView iv;
@@ -422,7 +425,7 @@ int gsr_backward_rigid(int P, int sh_degree, int M, int W, int H, int64_t num_re
     a.W = W; a.H = H; a.tanfovx = tanfovx; a.tanfovy = tanfovy;
     a.grad_scratch = (const float*)grad_scratch;
     a.dL_dmeans2D = dL_dmeans2D; a.dL_dcolors = colors_precomp ? dL_dcolors : nullptr; a.dL_dopacity = dL_dopacity;
-    a.dL_dmeans3D = dL_dmeans3D; a.dL_dcov3D = dL_dcov3D; a.dL_dsh = shs ? dL_dsh : nullptr;
+    a.dL_dmeans3D = dL_dmeans3D; a.dL_dcov3D = dL_dcov3D; a.dL_dsh = shs ? dL_dsh : nullptr; a.dsh_M = dsh_M;
     a.dL_dscales = scales ? dL_dscales : nullptr; a.dL_drotations = scales ? dL_drotations : nullptr;
     a.dL_dcov3D = cov3D_precomp ? dL_dcov3D : nullptr;
     a.dL_dpose = dL_dpose; a.pose_scratch = (float*)pose_scratch;

@@ -86,6 +86,7 @@ struct PreprocessBwdArgs {
     float* dL_dmeans3D;
     float* dL_dcov3D;
     float* dL_dsh;
+    int dsh_M;            // coefficients per Gaussian in dL_dsh (row stride / 3); >= (D+1)^2, == M unless the caller packs
     float* dL_dscales;
     float* dL_drotations;
     float* dL_dpose;      // optional [6]

@@ -51,16 +51,22 @@ __global__ void gaussian_activate_kernel(int P, const float* __restrict__ opacit
     reinterpret_cast<float4*>(rot)[i] = make_float4(q.x / n, q.y / n, q.z / n, q.w / n);
 }
 
-__global__ void adam_features_kernel(size_t n, int floats_per_gaussian, float* __restrict__ p, const float* __restrict__ g,
-                                     float* __restrict__ m, float* __restrict__ v, float lr_dc, float lr_rest, AdamCfg c,
-                                     const float* __restrict__ bias_dev)
+// One thread per SH float of the rows [first, first + n / floats_per_gaussian).  The gradient may be packed to its
+// first grad_floats floats per Gaussian (the active bands): the rest of a row then has gradient zero, which still
+// decays its moments and moves the parameter by whatever the moments hold, exactly like torch.optim.Adam on a zero grad.
+__global__ void adam_features_kernel(size_t first, size_t n, int floats_per_gaussian, int grad_floats, float* __restrict__ p,
+                                     const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v, float lr_dc,
+                                     float lr_rest, AdamCfg c, const float* __restrict__ bias_dev)
 {
-    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
+    i += first;
     if (bias_dev) { c.inv_bias1 = bias_dev[0]; c.inv_sqrt_bias2 = bias_dev[1]; }
-    const int k = (int)(i % (size_t)floats_per_gaussian);
+    const size_t row = i / (size_t)floats_per_gaussian;
+    const int k = (int)(i - row * (size_t)floats_per_gaussian);
+    const float gi = k < grad_floats ? g[row * (size_t)grad_floats + k] : 0.f;
     float mm = m[i], vv = v[i];
-    p[i] = adam_update(p[i], g[i], mm, vv, k < 3 ? lr_dc : lr_rest, c);
+    p[i] = adam_update(p[i], gi, mm, vv, k < 3 ? lr_dc : lr_rest, c);
     m[i] = mm; v[i] = vv;
 }
 
@@ -169,7 +175,10 @@ __global__ void adam_tick_kernel(long long* step_state, float b1, float b2)
     f[1] = (float)(1.0 / sqrt(1.0 - pow((double)b2, (double)t)));
 }
 
-static int adam_step_impl(int P, int M, int step, long long* step_state, float beta1, float beta2, float eps,
+// what: bit 0 = the per-Gaussian block (xyz, opacity, scale, rotation, statistics), bit 1 = SH rows [row0, row0 + rows).
+// tick: advance the device-side step counter first (once per optimiser step).
+static int adam_step_impl(int P, int M, int M_grad, int what, int row0, int rows, int tick, int step, long long* step_state,
+                          float beta1, float beta2, float eps,
                           const float* lrs_host, float* xyz, float* features, float* opacity_raw, float* log_scale,
                           float* rot_raw, const float* d_xyz, const float* d_features, const float* d_opacity,
                           const float* d_scale, const float* d_rot, float* state, const float* d_means2D,
@@ -177,6 +186,10 @@ static int adam_step_impl(int P, int M, int step, long long* step_state, float b
 {
     cudaStream_t s = (cudaStream_t)stream;
     if (P < 0 || M < 0 || (!step_state && step < 1) || !lrs_host) { set_last_error("gsr_gaussian_adam_step: bad argument"); return GSR_ERR_INVALID; }
+    if (M_grad < 0 || M_grad > M || row0 < 0 || rows < 0 || (long long)row0 + rows > P) {
+        set_last_error("gsr_gaussian_adam_step: M_grad / row range out of bounds");
+        return GSR_ERR_INVALID;
+    }
     if (P == 0) return GSR_OK;
     if (!xyz || !opacity_raw || !log_scale || !rot_raw || !d_xyz || !d_opacity || !d_scale || !d_rot || !state ||
         (M > 0 && (!features || !d_features))) {
@@ -192,7 +205,7 @@ static int adam_step_impl(int P, int M, int step, long long* step_state, float b
     c.inv_bias1 = c.inv_sqrt_bias2 = 1.f;
     const float* bias_dev = nullptr;
     if (step_state) {   // the step number lives on the device (the call can be captured in a CUDA graph and replayed)
-        adam_tick_kernel<<<1, 1, 0, s>>>(step_state, beta1, beta2);
+        if (tick) adam_tick_kernel<<<1, 1, 0, s>>>(step_state, beta1, beta2);
         bias_dev = reinterpret_cast<const float*>(step_state + 1);
     } else {
         c.inv_bias1 = (float)(1.0 / (1.0 - std::pow((double)beta1, (double)step)));
@@ -216,10 +229,11 @@ static int adam_step_impl(int P, int M, int step, long long* step_state, float b
     a.lr_xyz = lrs_host[0]; a.lr_op = lrs_host[3]; a.lr_sc = lrs_host[4]; a.lr_rot = lrs_host[5];
     a.d_means2D = d_means2D; a.radii = radii; a.grad_accum = (d_means2D && radii && denom) ? grad_accum : nullptr;
     a.denom = denom; a.max_radii2D = max_radii2D;
-    adam_gaussians_kernel<<<div_up(P, 256), 256, 0, s>>>(a, c, bias_dev);
-    if (M > 0) {
-        const size_t nf = (size_t)3 * M * n;
-        adam_features_kernel<<<(unsigned)((nf + 255) / 256), 256, 0, s>>>(nf, 3 * M, features, d_features, m_f, v_f, lrs_host[1],
+    if (what & 1) adam_gaussians_kernel<<<div_up(P, 256), 256, 0, s>>>(a, c, bias_dev);
+    if ((what & 2) && M > 0 && rows > 0) {
+        const size_t nf = (size_t)3 * M * (size_t)rows;
+        adam_features_kernel<<<(unsigned)((nf + 255) / 256), 256, 0, s>>>((size_t)3 * M * (size_t)row0, nf, 3 * M, 3 * M_grad,
+                                                                      features, d_features, m_f, v_f, lrs_host[1],
                                                                       lrs_host[2], c, bias_dev);
     }
     cudaError_t e = cudaGetLastError();
@@ -233,7 +247,7 @@ extern "C" int gsr_gaussian_adam_step(int P, int M, int step, float beta1, float
                                       const float* d_scale, const float* d_rot, float* state, const float* d_means2D,
                                       const int* radii, float* grad_accum, float* denom, float* max_radii2D, void* stream)
 {
-    return adam_step_impl(P, M, step, nullptr, beta1, beta2, eps, lrs_host, xyz, features, opacity_raw, log_scale, rot_raw,
+    return adam_step_impl(P, M, M, 3, 0, P, 1, step, nullptr, beta1, beta2, eps, lrs_host, xyz, features, opacity_raw, log_scale, rot_raw,
                           d_xyz, d_features, d_opacity, d_scale, d_rot, state, d_means2D, radii, grad_accum, denom,
                           max_radii2D, stream);
 }
@@ -246,9 +260,23 @@ extern "C" int gsr_gaussian_adam_step_dev(int P, int M, int64_t* step_state, flo
                                           float* max_radii2D, void* stream)
 {
     if (!step_state) { set_last_error("gsr_gaussian_adam_step_dev: step_state is NULL"); return GSR_ERR_INVALID; }
-    return adam_step_impl(P, M, 0, reinterpret_cast<long long*>(step_state), beta1, beta2, eps, lrs_host, xyz, features,
+    return adam_step_impl(P, M, M, 3, 0, P, 1, 0, reinterpret_cast<long long*>(step_state), beta1, beta2, eps, lrs_host, xyz, features,
                           opacity_raw, log_scale, rot_raw, d_xyz, d_features, d_opacity, d_scale, d_rot, state, d_means2D,
                           radii, grad_accum, denom, max_radii2D, stream);
+}
+
+extern "C" int gsr_gaussian_adam_step_part(int P, int M, int M_grad, int what, int row0, int rows, int tick,
+                                           int64_t* step_state, float beta1, float beta2, float eps, const float* lrs_host,
+                                           float* xyz, float* features, float* opacity_raw, float* log_scale, float* rot_raw,
+                                           const float* d_xyz, const float* d_features, const float* d_opacity,
+                                           const float* d_scale, const float* d_rot, float* state, const float* d_means2D,
+                                           const int* radii, float* grad_accum, float* denom, float* max_radii2D,
+                                           void* stream)
+{
+    if (!step_state) { set_last_error("gsr_gaussian_adam_step_part: step_state is NULL"); return GSR_ERR_INVALID; }
+    return adam_step_impl(P, M, M_grad, what, row0, rows, tick, 0, reinterpret_cast<long long*>(step_state), beta1, beta2, eps,
+                          lrs_host, xyz, features, opacity_raw, log_scale, rot_raw, d_xyz, d_features, d_opacity, d_scale,
+                          d_rot, state, d_means2D, radii, grad_accum, denom, max_radii2D, stream);
 }
 
 extern "C" size_t gsr_gaussian_adam_state_floats(int P, int M)

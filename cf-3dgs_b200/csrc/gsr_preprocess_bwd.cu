@@ -77,7 +77,7 @@ preprocess_backward_kernel(PreprocessBwdArgs a, GeomView g)
         float dscale[3] = {0.f, 0.f, 0.f};
         float4 drot = make_float4(0.f, 0.f, 0.f, 0.f);
         const int ncoef = (a.D + 1) * (a.D + 1);
-        float* dsh = a.dL_dsh ? a.dL_dsh + (size_t)idx * a.M * 3 : nullptr;
+        float* dsh = a.dL_dsh ? a.dL_dsh + (size_t)idx * a.dsh_M * 3 : nullptr;
         if (vis) {
             const float4* rec = reinterpret_cast<const float4*>(a.grad_scratch + (size_t)idx * 12);
             const float4 q0 = rec[0], q1 = rec[1], q2 = rec[2];
@@ -269,7 +269,7 @@ preprocess_backward_kernel(PreprocessBwdArgs a, GeomView g)
         // ---- write every output exactly once ----
         if (dsh && !SLAB) {
             const int first_zero = vis ? ncoef : 0;
-            for (int k = first_zero * 3; k < a.M * 3; k++) dsh[k] = 0.f;
+            for (int k = first_zero * 3; k < a.dsh_M * 3; k++) dsh[k] = 0.f;
         }
         // (a NULL output = the caller does not want that gradient: a pose-only fit asks for dL_dpose alone)
         if (a.dL_dmeans2D) {
@@ -358,7 +358,7 @@ void launch_preprocess_backward(const PreprocessBwdArgs& a, const GeomView& g, c
 {
     const int nblk = div_up(a.P, PB_THREADS);
     // slab path: (P,16,3) coefficients with 16-byte aligned base pointers
-    const bool slab = a.shs && a.dL_dsh && a.M == 16 && (((uintptr_t)a.shs | (uintptr_t)a.dL_dsh) & 15) == 0;
+    const bool slab = a.shs && a.dL_dsh && a.M == 16 && a.dsh_M == 16 && (((uintptr_t)a.shs | (uintptr_t)a.dL_dsh) & 15) == 0;
     if (slab) launch_pdl(preprocess_backward_kernel<true>, nblk, PB_THREADS, 0, s, a, g);
     else launch_pdl(preprocess_backward_kernel<false>, nblk, PB_THREADS, 0, s, a, g);
     if (a.dL_dpose) launch_pdl(pose_reduce_kernel, 1, 256, 0, s, (const float*)a.pose_scratch, nblk, a.dL_dpose);

@@ -216,23 +216,39 @@ def _forward_impl(bg, means3D, colors_precomp, opacities, scales, rotations, sca
 
 def _backward_impl(bg, means3D, radii, colors_precomp, scales, rotations, scale_modifier, cov3Ds_precomp,
                    viewmatrix, projmatrix, tanfovx, tanfovy, grad_color, grad_depth, grad_alpha, sh, degree,
-                   campos, geom, R, binning, img, alpha, debug, want_pose_grad=False, rigid=None, skip=()):
+                   campos, geom, R, binning, img, alpha, debug, want_pose_grad=False, rigid=None, skip=(), out=None,
+                   dsh_M=None):
     """Counterpart of _C.rasterize_gaussians_backward (rasterize_points.cu:121-208).  Returns the same eight
     gradients (None where the matching input was absent) plus the optional fused pose gradient.
     skip: names among {"means2D", "means3D", "opacity", "sh", "colors", "scales", "cov3D"} whose gradients the caller
-    does not need (autograd's needs_input_grad): they are neither allocated nor written ("scales" covers rotations)."""
+    does not need (autograd's needs_input_grad): they are neither allocated nor written ("scales" covers rotations).
+    out: optional dict of preallocated, contiguous float32 tensors the kernel writes straight into instead of fresh
+    ones -- keys "means3D" (P,3), "means2D" (P,3), "opacity" (P,1), "sh" (P,dsh_M,3), "scales" (P,3), "rotations" (P,4):
+    slices of one flat buffer in the batched-views loop, so the collective needs no packing copy.
+    dsh_M: coefficients per Gaussian in the SH gradient (default M; (degree+1)^2 packs away the inactive bands)."""
     dev = means3D.device
     P = means3D.shape[0]
     H, W = grad_color.shape[1], grad_color.shape[2]
     M = sh.shape[1] if sh.numel() != 0 else 0
     f32 = dict(dtype=torch.float32, device=dev)
-    dmeans3D = torch.empty((P, 3), **f32) if "means3D" not in skip else None
-    dmeans2D = torch.empty((P, 3), **f32) if "means2D" not in skip else None
-    dopacity = torch.empty((P, 1), **f32) if "opacity" not in skip else None
+    out = out or {}
+    dsh_M = M if dsh_M is None else int(dsh_M)
+
+    def _new(name, shape):
+        t = out.get(name)
+        if t is None:
+            return torch.empty(shape, **f32)
+        if tuple(t.shape) != tuple(shape) or t.dtype != torch.float32 or not t.is_contiguous() or t.device != dev:
+            raise RuntimeError(f"out[{name!r}] must be a contiguous float32 tensor of shape {tuple(shape)} on {dev}")
+        return t
+
+    dmeans3D = _new("means3D", (P, 3)) if "means3D" not in skip else None
+    dmeans2D = _new("means2D", (P, 3)) if "means2D" not in skip else None
+    dopacity = _new("opacity", (P, 1)) if "opacity" not in skip else None
     dcolors = torch.empty((P, 3), **f32) if colors_precomp.numel() and "colors" not in skip else None
-    dsh = torch.empty((P, M, 3), **f32) if sh.numel() and "sh" not in skip else None
-    dscales = torch.empty((P, 3), **f32) if scales.numel() and "scales" not in skip else None
-    drots = torch.empty((P, 4), **f32) if scales.numel() and "scales" not in skip else None
+    dsh = _new("sh", (P, dsh_M, 3)) if sh.numel() and "sh" not in skip else None
+    dscales = _new("scales", (P, 3)) if scales.numel() and "scales" not in skip else None
+    drots = _new("rotations", (P, 4)) if scales.numel() and "scales" not in skip else None
     dcov3D = torch.empty((P, 6), **f32) if cov3Ds_precomp.numel() and "cov3D" not in skip else None
     dpose = torch.empty((6,), **f32) if want_pose_grad else None
     if P == 0:
@@ -252,7 +268,7 @@ def _backward_impl(bg, means3D, radii, colors_precomp, scales, rotations, scale_
             _ptr(viewmatrix), _ptr(projmatrix), _ptr(campos), float(tanfovx), float(tanfovy), _ptr(sh),
             alpha.data_ptr(), grad_color.data_ptr(), _ptr(grad_depth), _ptr(grad_alpha), geom.data_ptr(),
             binning.data_ptr(), img.data_ptr(), scratch.data_ptr(), _ptr(dmeans2D), _ptr(dcolors),
-            _ptr(dopacity), _ptr(dmeans3D), _ptr(dcov3D), _ptr(dsh), _ptr(dscales), _ptr(drots),
+            _ptr(dopacity), _ptr(dmeans3D), _ptr(dcov3D), _ptr(dsh), dsh_M, _ptr(dscales), _ptr(drots),
             _ptr(dpose), _ptr(pose_scratch), None if rigid is None else rigid.data_ptr(), stream, int(bool(debug))))
     return dmeans2D, dcolors, dopacity, dmeans3D, dcov3D, dsh, dscales, drots, dpose
 

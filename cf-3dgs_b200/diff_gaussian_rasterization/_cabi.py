@@ -33,7 +33,7 @@ SIGNATURES = {
                                         _P, _P, c_int]),
     "gsr_backward_rigid": (c_int, [c_int, c_int, c_int, c_int, c_int, c_int64, _P, _P, _P, _P, _P, _P, c_float, _P, _P,
                                    _P, _P, c_float, c_float, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P,
-                                   _P, _P, _P, _P, _P, _P, c_int]),
+                                   c_int, _P, _P, _P, _P, _P, _P, c_int]),
     "gsr_pose_scratch_bytes": (c_size_t, [c_int]),
     "gsr_backward": (c_int, [c_int, c_int, c_int, c_int, c_int, c_int64, _P, _P, _P, _P, _P, _P, c_float, _P, _P,
                              _P, _P, c_float, c_float, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P,
@@ -48,12 +48,15 @@ SIGNATURES = {
                                        _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "gsr_gaussian_adam_step_dev": (c_int, [c_int, c_int, _P, c_float, c_float, c_float, _P, _P, _P, _P, _P, _P, _P, _P, _P,
                                            _P, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "gsr_gaussian_adam_step_part": (c_int, [c_int, c_int, c_int, c_int, c_int, c_int, c_int, _P, c_float, c_float, c_float,
+                                            _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "gsr_mark_visible": (c_int, [c_int, _P, _P, _P, _P, _P]),
     "gsr_debug_dump": (c_int, [c_int, c_int, c_int, c_int64, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "gsr_profile_enable": (c_int, [c_int]),
     "gsr_profile_count": (c_int, []),
     "gsr_profile_name": (c_char_p, [c_int]),
     "gsr_profile_read": (c_int, [_P, c_int]),
+    "gsr_measure_peaks": (c_int, [_P, _P]),
     "gsr_debug_pair_counts": (c_int, [c_int, c_int, c_int, c_int64, _P, _P, _P, _P, _P]),
     "gsr_knn_scratch_bytes": (c_size_t, [c_int]),
     "gsr_knn_mean_dist2": (c_int, [c_int, _P, _P, _P, c_size_t, _P]),

@@ -70,3 +70,26 @@ class FusedGaussianModel:
             else:
                 check(lib.gsr_gaussian_adam_step(self.P, self.M, self.step_count, float(self.betas[0]),
                                                  float(self.betas[1]), float(self.eps), lr, *tail))
+
+    def step_part(self, what: int, grads: Dict[str, torch.Tensor], M_grad: int, row0: int = 0, rows: Optional[int] = None,
+                  tick: bool = False, d_means2D: Optional[torch.Tensor] = None, radii: Optional[torch.Tensor] = None) -> None:
+        """A part of one optimiser step (gsr_gaussian_adam_step_part): what & 1 = the per-Gaussian block, what & 2 = the
+        SH rows [row0, row0 + rows).  grads: "means3D" (P,3), "sh" (P,M_grad,3), "opacity" (P,1), "scales" (P,3),
+        "rotations" (P,4) -- typically views into one flat, all-reduced buffer.  Needs device_step=True."""
+        if self.step_state is None:
+            raise RuntimeError("step_part needs device_step=True (the step counter lives on the device)")
+        rows = self.P if rows is None else rows
+        if tick:
+            self.step_count += 1
+        lr = (ctypes.c_float * 6)(*[float(self.lrs[k]) for k in LR_ORDER])
+        stats = bool(what & 1) and d_means2D is not None and radii is not None
+        with torch.cuda.device(self.xyz.device):
+            check(lib.gsr_gaussian_adam_step_part(
+                self.P, self.M, int(M_grad), int(what), int(row0), int(rows), int(bool(tick)), self.step_state.data_ptr(),
+                float(self.betas[0]), float(self.betas[1]), float(self.eps), lr,
+                self.xyz.data_ptr(), self.features.data_ptr(), self.opacity_raw.data_ptr(), self.log_scales.data_ptr(),
+                self.rot_raw.data_ptr(), grads["means3D"].data_ptr(), grads["sh"].data_ptr(), grads["opacity"].data_ptr(),
+                grads["scales"].data_ptr(), grads["rotations"].data_ptr(), self.state.data_ptr(),
+                d_means2D.data_ptr() if stats else None, radii.data_ptr() if stats else None,
+                self.xyz_gradient_accum.data_ptr() if stats else None, self.denom.data_ptr() if stats else None,
+                self.max_radii2D.data_ptr() if stats else None, torch.cuda.current_stream().cuda_stream))

@@ -19,6 +19,142 @@ import torch.distributed as dist
 GRAD_ORDER = ("means3D", "shs", "opacities", "scales", "rotations")
 
 
+# ---- batched global views: layout of the flat gradient buffer and the pieces it is all-reduced in --------------------
+def flat_layout(P: int, M_grad: int) -> Dict[str, tuple]:
+    """Offsets (in floats) and shapes of the gradient slices inside the ONE flat buffer the rasterizer backward writes
+    and NCCL reduces: rotations first (the model step reads them as float4, so their slice starts 16-byte aligned for
+    any P), then means3D, opacity, scales -- the 11 floats per Gaussian of the geometry block -- then the SH gradient
+    packed to its M_grad active coefficients.  (11 + 3 M_grad) P floats in all: 14 P at SH degree 0, 59 P at degree 3
+    (scene/gaussian_model_cf.py:254-266 lists the parameter groups these belong to)."""
+    out, off = {}, 0
+    for name, shape in (("rotations", (P, 4)), ("means3D", (P, 3)), ("opacity", (P, 1)), ("scales", (P, 3)),
+                        ("sh", (P, M_grad, 3))):
+        if name == "sh":
+            off = _sh_offset(P)      # 16-byte aligned for any P: the kernels move whole SH rows as float4 when they can
+        n = 1
+        for d in shape:
+            n *= d
+        out[name] = (off, shape)
+        off += n
+    out["_geometry_floats"] = (11 * P, ())
+    out["_total_floats"] = (off, ())
+    return out
+
+
+def _sh_offset(P: int) -> int:
+    return (11 * P + 3) // 4 * 4
+
+
+def comm_pieces(P: int, M_grad: int, sh_chunks: int) -> List[tuple]:
+    """(float offset, float count, what, row0, rows) of the pieces the flat gradient is all-reduced in, in issue order:
+    the geometry block, then the SH rows in `sh_chunks` row ranges.  The model step for a piece (`what`, rows) can run
+    as soon as that piece has arrived, while the next one is still on the wire."""
+    pieces = [(0, 11 * P, 1, 0, 0)]
+    sh_chunks = max(1, min(int(sh_chunks), P)) if P > 0 else 1
+    per = -(-P // sh_chunks)
+    r0 = 0
+    while r0 < P:
+        rows = min(per, P - r0)
+        pieces.append((_sh_offset(P) + 3 * M_grad * r0, 3 * M_grad * rows, 2, r0, rows))
+        r0 += rows
+    return pieces
+
+
+def params_checksum(tensors: Sequence[torch.Tensor]) -> torch.Tensor:
+    """Order-independent integer checksum of float32 tensors (sum of their bit patterns as int64): equal parameters give
+    equal checksums on every rank, any single differing bit changes it."""
+    acc = torch.zeros((), dtype=torch.int64, device=tensors[0].device)
+    for t in tensors:
+        acc = acc + t.detach().contiguous().view(torch.int32).to(torch.int64).sum()
+    return acc
+
+
+def assert_replicas_identical(tensors: Sequence[torch.Tensor]) -> bool:
+    """True when every rank holds bit-identical copies (compares the checksum's max and min over the ranks)."""
+    c = params_checksum(tensors)
+    if not (dist.is_initialized() and dist.get_world_size() > 1):
+        return True
+    hi, lo = c.clone(), c.clone()
+    dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+    dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+    return bool(hi == lo)
+
+
+class BatchedViewsStep:
+    """One optimiser step of the batched-global-views form: every rank holds a replica of the
+    global Gaussian model (gsr_model.FusedGaussianModel, device_step=True), renders ITS view, and the gradients of all
+    views are summed before the identical Adam step on every rank.
+
+    * the rasterizer backward writes its gradients straight into slices of one flat buffer (no packing copies);
+    * only the active SH bands travel (the packed gradient, dsh_M = (degree+1)^2): 14 floats per Gaussian at degree 0
+      instead of 59;
+    * the buffer is all-reduced in pieces -- geometry block, then SH row ranges -- on NCCL's own stream, and the model
+      step for a piece starts when that piece has arrived, so the optimiser overlaps the rest of the collective;
+    * the densification statistics are per view and stay local (sum / sum / max over ranks when they are read:
+      allreduce_densify_stats).
+    The sum over views is not divided by the number of ranks: Adam's update is invariant to the gradient's scale (up to
+    eps = 1e-15).  With world size 1 the same code runs without a collective."""
+
+    def __init__(self, model, sh_chunks: int = 4):
+        self.model = model
+        self.sh_chunks = sh_chunks
+        self._flat = None
+        self._key = None
+
+    def buffers(self, M_grad: int):
+        m = self.model
+        key = (m.P, M_grad)
+        if self._key != key:
+            lay = flat_layout(m.P, M_grad)
+            flat = torch.empty(lay["_total_floats"][0], dtype=torch.float32, device=m.xyz.device)
+            views = {}
+            for name in ("rotations", "means3D", "opacity", "scales", "sh"):
+                off, shape = lay[name]
+                n = 1
+                for d in shape:
+                    n *= d
+                views[name] = flat[off:off + n].view(shape)
+            self._flat, self._views, self._key = flat, views, key
+            self._m2d = torch.empty((m.P, 3), dtype=torch.float32, device=m.xyz.device)
+            self._pieces = comm_pieces(m.P, M_grad, self.sh_chunks)
+        return self._flat, self._views
+
+    def __call__(self, settings, target, loss_fn, window=None):
+        """settings: GaussianRasterizationSettings of this rank's view; target: its image; returns this rank's loss."""
+        import diff_gaussian_rasterization as D
+        m = self.model
+        deg = int(settings.sh_degree)
+        M_grad = (deg + 1) * (deg + 1)
+        flat, g = self.buffers(M_grad)
+        act = m.activated()
+        e = torch.Tensor([])
+        rs = settings
+        R, color, depth, alpha, radii, geom, binning, img = D._forward_impl(
+            rs.bg, m.xyz, e, act["opacities"], act["scales"], act["rotations"], rs.scale_modifier, e, rs.viewmatrix,
+            rs.projmatrix, rs.tanfovx, rs.tanfovy, rs.image_height, rs.image_width, m.features, deg, rs.campos, False, False)
+        leaf = color.requires_grad_(True)
+        loss = loss_fn(leaf, target, window)
+        loss.backward()
+        D._backward_impl(rs.bg, m.xyz, radii, e, act["scales"], act["rotations"], rs.scale_modifier, e, rs.viewmatrix,
+                         rs.projmatrix, rs.tanfovx, rs.tanfovy, leaf.grad, None, None, m.features, deg, rs.campos, geom, R,
+                         binning, img, alpha, False,
+                         out=dict(means3D=g["means3D"], means2D=self._m2d, opacity=g["opacity"], sh=g["sh"],
+                                  scales=g["scales"], rotations=g["rotations"]), dsh_M=M_grad)
+        multi = dist.is_initialized() and dist.get_world_size() > 1
+        works = []
+        if multi:
+            for off, n, _, _, _ in self._pieces:
+                works.append(dist.all_reduce(flat[off:off + n], async_op=True))
+        first = True
+        for i, (off, n, what, row0, rows) in enumerate(self._pieces):
+            if multi:
+                works[i].wait()        # the compute stream waits for this piece; the host does not
+            m.step_part(what, g, M_grad, row0=row0, rows=rows, tick=first,
+                        d_means2D=self._m2d if what & 1 else None, radii=radii if what & 1 else None)
+            first = False
+        return loss.detach()
+
+
 def shard_pairs(n_pairs: int, rank: int, world: int) -> List[int]:
     """Frame pairs (i-1, i) owned by this rank: round-robin so early and late frames mix."""
     return [i for i in range(n_pairs) if i % world == rank]

@@ -293,39 +293,20 @@ def make_backend(impl, dev):
     return dict(settings=settings, render=render)
 
 
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--pairs", type=int, default=1)
-    ap.add_argument("--fit-iters", type=int, default=200)
-    ap.add_argument("--pose-iters", type=int, default=300)
-    ap.add_argument("--points", type=int, default=250_000)
-    ap.add_argument("--width", type=int, default=960)
-    ap.add_argument("--height", type=int, default=540)
-    ap.add_argument("--pose-lr", type=float, default=1e-3)
-    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--graph", action="store_true",
-                    help="sync-free forward + the pose iteration captured as one CUDA graph (ours only)")
-    ap.add_argument("--sync-free", action="store_true", help="sync-free forward without graph capture (ours only)")
-    ap.add_argument("--model", default=None, choices=["fused", "torch"],
-                    help="Gaussian fit: the library's fused model step (default for ours) or PyTorch activations + Adam")
-    ap.add_argument("--loss", default=None, choices=["fused", "torch"],
-                    help="fused CUDA L1+SSIM (default for --impl ours) or the PyTorch formulation (default for reference)")
-    args = ap.parse_args()
-    if args.loss is None:
-        args.loss = "fused" if args.impl == "ours" else "torch"
-    if args.model is None:
-        args.model = "fused" if args.impl == "ours" else "torch"
-    if args.model == "fused" and args.impl != "ours":
-        raise SystemExit("--model fused needs --impl ours")
-    world = int(os.environ.get("WORLD_SIZE", "1")); rank = int(os.environ.get("RANK", "0")); local = int(os.environ.get("LOCAL_RANK", "0"))
-    real_stdout = os.dup(1); os.dup2(2, 1)
-    if world > 1:
-        import datetime
-        import torch.distributed as dist
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1"); os.environ.setdefault("MASTER_PORT", "29500")
-        dist.init_process_group("nccl", rank=rank, world_size=world, timeout=datetime.timedelta(seconds=300))
-    dev = torch.device("cuda", local)
-    torch.cuda.set_device(dev)
+def default_args(**kw):
+    d = dict(pairs=1, fit_iters=200, pose_iters=300, points=250_000, width=960, height=540, pose_lr=1e-3, impl="ours",
+             graph=False, sync_free=False, model=None, loss=None)
+    d.update(kw)
+    if d["loss"] is None:
+        d["loss"] = "fused" if d["impl"] == "ours" else "torch"
+    if d["model"] is None:
+        d["model"] = "fused" if d["impl"] == "ours" else "torch"
+    return argparse.Namespace(**d)
+
+
+def run_sharded(args, dev, rank=0, world=1):
+    """Frame pairs sharded over the ranks (pair p on rank p mod world, no data-path collective), then one gather of
+    the relative poses.  Returns (result dict on rank 0 / None elsewhere, binning overflow flag)."""
     import gsr_parallel as GPar
     backend = make_backend(args.impl, dev)
     if args.impl == "ours" and (args.graph or args.sync_free):
@@ -370,6 +351,46 @@ def main():
                 "fit_loss": res[0]["fit_loss"] if res else None, "pose_loss": res[0]["pose_loss"] if res else None}
         if overflow is not None:
             line["binning_overflow"] = overflow
+        return line, overflow
+    return None, overflow
+
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--pairs", type=int, default=1)
+    ap.add_argument("--fit-iters", type=int, default=200)
+    ap.add_argument("--pose-iters", type=int, default=300)
+    ap.add_argument("--points", type=int, default=250_000)
+    ap.add_argument("--width", type=int, default=960)
+    ap.add_argument("--height", type=int, default=540)
+    ap.add_argument("--pose-lr", type=float, default=1e-3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--graph", action="store_true",
+                    help="sync-free forward + the pose iteration captured as one CUDA graph (ours only)")
+    ap.add_argument("--sync-free", action="store_true", help="sync-free forward without graph capture (ours only)")
+    ap.add_argument("--model", default=None, choices=["fused", "torch"],
+                    help="Gaussian fit: the library's fused model step (default for ours) or PyTorch activations + Adam")
+    ap.add_argument("--loss", default=None, choices=["fused", "torch"],
+                    help="fused CUDA L1+SSIM (default for --impl ours) or the PyTorch formulation (default for reference)")
+    args = ap.parse_args()
+    if args.loss is None:
+        args.loss = "fused" if args.impl == "ours" else "torch"
+    if args.model is None:
+        args.model = "fused" if args.impl == "ours" else "torch"
+    if args.model == "fused" and args.impl != "ours":
+        raise SystemExit("--model fused needs --impl ours")
+    world = int(os.environ.get("WORLD_SIZE", "1")); rank = int(os.environ.get("RANK", "0")); local = int(os.environ.get("LOCAL_RANK", "0"))
+    real_stdout = os.dup(1); os.dup2(2, 1)
+    if world > 1:
+        import datetime
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1"); os.environ.setdefault("MASTER_PORT", "29500")
+        dist.init_process_group("nccl", rank=rank, world_size=world, timeout=datetime.timedelta(seconds=300))
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    line, overflow = run_sharded(args, dev, rank, world)
+    if rank == 0:
         os.write(real_stdout, (json.dumps(line) + "\n").encode())
     if world > 1:
         import torch.distributed as dist

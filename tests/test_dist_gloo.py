@@ -51,6 +51,29 @@ def _worker(rank, world, port, q):
         rel = GP.gather_relative_poses(local, n_pairs)
         poses = GP.compose_poses(rel)
         ok &= len(poses) == n_pairs + 1 and abs(float(poses[-1][0, 3]) - 15.0) < 1e-6
+        # batched global views: the flat gradient reduced in pieces equals the buffer reduced whole, and the pieces tile it
+        for M_grad in (1, 16):
+            lay = GP.flat_layout(P, M_grad)
+            total = lay["_total_floats"][0]
+            pieces = GP.comm_pieces(P, M_grad, sh_chunks=3)
+            covered = torch.zeros(total, dtype=torch.int32)
+            gg = torch.Generator().manual_seed(200 + rank)
+            flat = torch.randn(total, generator=gg)
+            whole = flat.clone()
+            dist.all_reduce(whole)
+            works = [dist.all_reduce(flat[off:off + n], async_op=True) for off, n, _, _, _ in pieces]
+            for w, (off, n, what, row0, rows) in zip(works, pieces):
+                w.wait()
+                covered[off:off + n] += 1
+                ok &= (what == 1 and off == 0 and n == 11 * P) or (what == 2 and n == 3 * M_grad * rows)
+            used = torch.ones(total, dtype=torch.bool)
+            used[11 * P:lay["sh"][0]] = False                  # alignment padding between the two blocks
+            ok &= bool((covered[used] == 1).all()) and bool((covered[~used] == 0).all())
+            ok &= torch.equal(flat[used], whole[used])
+            ok &= lay["sh"][0] % 4 == 0 and lay["rotations"][0] == 0
+        same = GP.assert_replicas_identical([torch.arange(10, dtype=torch.float32)])
+        differ = GP.assert_replicas_identical([torch.full((3,), float(rank))])
+        ok &= same and not differ
         q.put((rank, bool(ok), mine))
     finally:
         dist.destroy_process_group()
