@@ -237,6 +237,8 @@ def run_loops(dev, rank, world):
     import cf3dgs_global as CG
     import diff_gaussian_rasterization as D
     out = {}
+    D.set_sync_free(False)
+    D._SyncFree.capacity.clear()      # the 1080p capacity of the frames/s part would oversize every launch of the 540p loops
     # (i) CF-3DGS frame pairs, 2 per GPU: local Gaussian fit (200 iterations) + pose fit (300 iterations, the reference's
     # count, trainer/cf3dgs_trainer.py:262-285), each loop one replayed CUDA graph; no data-path collective
     pargs = CP.default_args(pairs=2 * world, fit_iters=200, pose_iters=300, graph=True)
