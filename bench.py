@@ -364,12 +364,17 @@ def main():
                 st = RC.forward(means3D, opac, shs=shs, scales=scales, rotations=rots, viewmatrix=v, projmatrix=pj,
                                 campos=cp, bg=bg, W=W, H=H, tanfovx=cam["tanfovx"], tanfovy=cam["tanfovy"],
                                 sh_degree=wl["sh_degree"])
-                ctx.st = st
+                # as the reference's own wrapper: state through save_for_backward (outputs kept on ctx directly would form
+                # a reference cycle and leave the workspaces to the garbage collector)
+                ctx.save_for_backward(st["radii"], st["geom"], st["binning"], st["img"], st["alpha"])
+                ctx.meta = (st["num_rendered"], st["_args"])
                 return st["color"], st["depth"], st["alpha"]
 
             @staticmethod
             def backward(ctx, gcol, gdep, galp):
-                g = RC.backward(ctx.st, gcol.contiguous(), gdep.contiguous(), galp.contiguous())
+                radii, geom, binning, img, alpha = ctx.saved_tensors
+                st = dict(radii=radii, geom=geom, binning=binning, img=img, alpha=alpha, num_rendered=ctx.meta[0], _args=ctx.meta[1])
+                g = RC.backward(st, gcol.contiguous(), gdep.contiguous(), galp.contiguous())
                 return g["means3D"], g["opacities"], g["sh"], g["scales"], g["rotations"], None, None, None
 
         def render(leaves, m2d, settings=None):

@@ -207,12 +207,18 @@ def run_global(args, dev, rank=0, world=1):
         views_all = torch.stack([s.viewmatrix for s in settings]); projs_all = torch.stack([s.projmatrix for s in settings])
         campos_all = torch.stack([s.campos for s in settings]); targets_all = torch.stack(targets)
         idx_dev = torch.zeros(1, dtype=torch.int64, device=dev)
-        idx_host = torch.zeros(1, dtype=torch.int64).pin_memory()
+        # the schedule of views lives on the device and the graph advances its own position in it: a host-side "next view"
+        # word would be overwritten by the host, which runs ahead of the GPU, before the replay that should read it
+        order_dev = torch.as_tensor(order[:total_steps], dtype=torch.int64, device=dev)
+        pos_dev = torch.zeros(1, dtype=torch.int64, device=dev)
         cur = dict(view=torch.empty_like(settings[0].viewmatrix), proj=torch.empty_like(settings[0].projmatrix),
                    campos=torch.empty_like(settings[0].campos), target=torch.empty_like(targets[0]))
         rs_cur = settings[0]._replace(viewmatrix=cur["view"], projmatrix=cur["proj"], campos=cur["campos"])
 
-        def graph_body():
+        def graph_body(scheduled=False):
+            if scheduled:
+                idx_dev.copy_(order_dev.index_select(0, pos_dev))
+                pos_dev.add_(1)
             cur["view"].copy_(views_all.index_select(0, idx_dev)[0]); cur["proj"].copy_(projs_all.index_select(0, idx_dev)[0])
             cur["campos"].copy_(campos_all.index_select(0, idx_dev)[0]); cur["target"].copy_(targets_all.index_select(0, idx_dev)[0])
             return fused_iteration_frame(rs_cur, cur["target"])
@@ -234,16 +240,14 @@ def run_global(args, dev, rank=0, world=1):
             torch.cuda.current_stream().wait_stream(side)
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g):
-                loss = graph_body()
+                loss = graph_body(scheduled=True)
             torch.cuda.synchronize(dev)
             graph["g"], graph["loss"] = g, loss
             state["recaptures"] += 1
             state["recapture_s"] += time.time() - t0
 
         def graph_iteration(k):
-            idx_host[0] = view_of(k)
-            idx_dev.copy_(idx_host, non_blocking=True)
-            graph["g"].replay()
+            graph["g"].replay()            # renders view order[pos] and advances pos, all on the device
             return graph["loss"]
 
     def iteration(k):

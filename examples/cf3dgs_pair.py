@@ -270,13 +270,19 @@ def make_backend(impl, dev):
         @staticmethod
         def forward(ctx, means3D, opa, shs, scales, rots, rs):
             st = RC.forward(means3D, opa, shs=shs, scales=scales, rotations=rots, **rs)
-            ctx.st = st
+            # the state goes through save_for_backward, as the reference's own wrapper does: keeping the output tensors on
+            # ctx directly would tie node and outputs into a reference cycle that only the garbage collector breaks, and a
+            # GB of workspaces per iteration then piles up between collections
+            ctx.save_for_backward(st["radii"], st["geom"], st["binning"], st["img"], st["alpha"])
+            ctx.meta = (st["num_rendered"], st["_args"])
             return st["color"], st["depth"], st["alpha"]
 
         @staticmethod
         def backward(ctx, gc, gd, ga):
-            z = torch.zeros_like(ctx.st["depth"])
-            g = RC.backward(ctx.st, gc.contiguous(), z if gd is None else gd.contiguous(), z if ga is None else ga.contiguous())
+            radii, geom, binning, img, alpha = ctx.saved_tensors
+            st = dict(radii=radii, geom=geom, binning=binning, img=img, alpha=alpha, num_rendered=ctx.meta[0], _args=ctx.meta[1])
+            z = torch.zeros_like(alpha)
+            g = RC.backward(st, gc.contiguous(), z if gd is None else gd.contiguous(), z if ga is None else ga.contiguous())
             return g["means3D"], g["opacities"], g["sh"], g["scales"], g["rotations"], None
 
     def settings(cam, deg):
