@@ -9,7 +9,7 @@ import pytest
 import torch
 
 import gsr_synth as S
-from helpers import cuda_forward, rel_to_max
+from helpers import cuda_forward, diag, rel_elementwise, rel_to_max
 
 pytestmark = pytest.mark.gpu
 N_CASES = 24
@@ -41,6 +41,20 @@ def _case(i):
         sc["scales"] = (sc["scales"] * torch.tensor([1.0, 0.05, 8.0])).contiguous()
     bg = tuple(float(x) for x in rng.uniform(0, 1, 3)) if i % 2 else (0.0, 0.0, 0.0)
     return cam, sc, deg, bg, W, H, P
+
+
+def _float64_gradients(i, cam, sc, deg, bg, W, H, ct):
+    """Gradients of the same loss by float64 autograd through oracle/torch_oracle.py (CPU; a few seconds per case)."""
+    from oracle import torch_oracle as TO
+    lv = {k: sc[k].double().clone().requires_grad_(True) for k in ["means3D", "opacities", "shs", "scales", "rotations"]}
+    o = TO.forward(lv["means3D"], lv["opacities"], shs=lv["shs"], scales=lv["scales"], rotations=lv["rotations"],
+                   viewmatrix=cam["viewmatrix"].double(), projmatrix=cam["projmatrix"].double(), campos=cam["campos"].double(),
+                   bg=torch.tensor(bg).double(), W=W, H=H, tanfovx=cam["tanfovx"], tanfovy=cam["tanfovy"], sh_degree=deg)
+    loss = (o["color"] * ct["grad_color"].double()).sum()
+    if i % 3:
+        loss = loss + (o["depth"] * ct["grad_depth"].double()).sum() + (o["alpha"] * ct["grad_alpha"].double()).sum()
+    loss.backward()
+    return {k: v.grad.numpy() for k, v in lv.items()}
 
 
 @pytest.mark.parametrize("i", range(N_CASES))
@@ -75,16 +89,26 @@ def test_random_scene_vs_reference_cuda(i):
         loss = loss + (out["depth"] * gd).sum() + (out["alpha"] * ga).sum()
     loss.backward()
     gr = RC.backward(rst, ct["grad_color"].to(dev), gd, ga)
+    f64 = _float64_gradients(i, cam, sc, deg, bg, W, H, ct) if i % 5 == 0 else None
     for nm, key in [("means3D", "means3D"), ("opacities", "opacities"), ("shs", "sh"), ("scales", "scales"),
                     ("rotations", "rotations")]:
         if float(gr[key].abs().max()) == 0.0:
             assert float(leaves[nm].grad.abs().max()) == 0.0, nm
             continue
+        mine, ref = leaves[nm].grad.cpu().numpy(), gr[key].cpu().numpy()
+        if f64 is None:
+            assert rel_to_max(mine, ref) <= 1e-4, (nm, i)
+            # element by element too (entries below a thousandth of the largest are compared on that floor's scale)
+            assert rel_elementwise(mine, ref) <= 1e-2, (nm, i)
+            continue
         # Needle-shaped Gaussians (160:1) have nearly singular 2-D conics: the covariance chain amplifies float32 rounding
-        # about a thousandfold, and this build and the reference build then differ from a float64 evaluation by a few 1e-4
-        # each (measured with tools/diag_fuzz.py: case 0, Gaussian 1696 -- d/dz = -7.433 in float64, -7.493 here, -7.522
-        # in the reference; conic determinants of 0.002 against entries of 2 push the scale / rotation gradients of such a
-        # Gaussian 1-2 % apart).  Those cases are held to 1e-3 (5e-2 for scales and rotations); everything else to the 1e-4
-        # of the parity tests.
-        tol = (5e-2 if nm in ("scales", "rotations") else 1e-3) if i % 5 == 0 else 1e-4
-        assert rel_to_max(leaves[nm].grad.cpu().numpy(), gr[key].cpu().numpy()) <= tol, (nm, i)
+        # about a thousandfold, and this build and the reference build then each sit a few 1e-4 (means) to 1-2 % (scales,
+        # rotations) from a float64 evaluation, on either side of it (tools/diag_fuzz.py).  A comparison between the two
+        # float32 builds says nothing there; the float64 autograd of the PyTorch restatement is the judge: this build must be
+        # in the same place relative to it as the reference build is.  Both distances are float32 rounding noise of
+        # different operation orders (measured: 2.7e-3 here against 1.3e-3 there for the rotations of case 0, 8.5e-4 against
+        # 9.7e-4 for its scales), so "same place" is a factor of three, plus the 1e-4 of the parity tests.
+        truth = f64[nm]
+        d_mine, d_ref = rel_to_max(mine, truth), rel_to_max(ref, truth)
+        assert d_mine <= 3.0 * d_ref + 1e-4, (nm, i, d_mine, d_ref)
+        diag(f"fuzz case {i} {nm}: distance to float64 -- this build {d_mine:.2e}, reference build {d_ref:.2e}")
