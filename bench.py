@@ -603,8 +603,7 @@ def main():
         "depth_sort": ("hbm", P * 16 / 1e9),
         "offsets_scan": ("hbm", P * 8 / 1e9),
         "emit": ("hbm", (P * 20 + R * 12) / 1e9),
-        "tile_sort": ("hbm", R * 24 / 1e9),
-        "tile_ranges": ("hbm", (R * 8 + tiles * 8) / 1e9),
+        "tile_sort": ("hbm", R * 24 / 1e9),      # (the tile ranges are written by its last pass)
         "render_forward": ("fp32", (in_range * 24 + blended * 16) / 1e12),
         "render_backward": ("fp32", (blended * 75 + (in_range - blended) * 24) / 1e12),
         "preprocess_backward": ("hbm", P_vis * 627 / 1e9),
@@ -638,7 +637,8 @@ def main():
     line["work"] = {"num_rendered": R, "visible": P_vis, "pairs_in_range": in_range, "pairs_blended": blended,
                     "reference_pairs_no_early_exit": ref_pairs, "tile_rejected_entries": tile_rej}
     depth_passes, tile_passes = 4, (max(1, (tiles - 1).bit_length()) + 7) // 8
-    line["gpu_launches"] = args.steps * (1 + 3 * depth_passes + 2 + 1 + 3 * tile_passes + 1 + 1 + 1 + 1)
+    # preprocess, 3 kernels per radix pass, partial sums, emit, forward blend, backward blend, per-Gaussian backward
+    line["gpu_launches"] = args.steps * (1 + 3 * depth_passes + 1 + 1 + 3 * tile_passes + 1 + 1 + 1)
     if world == 1 and not args.no_cpu_baseline:
         try:
             line["cpu_baseline"] = cpu_oracle_baseline(S, wl, S.make_camera(W, H))

@@ -32,10 +32,10 @@ int fail(int code, const char* fmt, ...)
     } while (0)
 
 // ---- stage timing ------------------------------------------------------------------------------
-enum Stage { ST_PREPROCESS, ST_DEPTH_SORT, ST_OFFSETS, ST_EMIT, ST_TILE_SORT, ST_RANGES, ST_RENDER_FWD,
+enum Stage { ST_PREPROCESS, ST_DEPTH_SORT, ST_OFFSETS, ST_EMIT, ST_TILE_SORT, ST_RENDER_FWD,
              ST_GRAD_ZERO, ST_RENDER_BWD, ST_PREPROCESS_BWD, ST_COUNT };
 const char* const kStageNames[ST_COUNT] = {"preprocess", "depth_sort", "offsets_scan", "emit", "tile_sort",
-                                           "tile_ranges", "render_forward", "grad_zero", "render_backward",
+                                           "render_forward", "grad_zero", "render_backward",
                                            "preprocess_backward"};
 bool g_prof_on = false;
 cudaEvent_t g_ev[ST_COUNT][2];
@@ -176,7 +176,8 @@ static int bin_and_render(int P, int W, int H, int64_t n_layout, const unsigned 
         GSR_STAGE("emit");
         {
             StageTimer t(ST_TILE_SORT, s);
-            const int cur = radix_sort_pairs(b.keys, b.vals, n_layout, 0, tile_bits(tiles), b.hist, b.digit_total, s, n_dev);
+            const int cur = radix_sort_pairs(b.keys, b.vals, n_layout, 0, tile_bits(tiles), b.hist, b.digit_total, s, n_dev,
+                                             nullptr, iv.ranges);
             if (cur != 0) {  // invariant: keys[0]/vals[0] hold the sorted list
                 cudaMemcpyAsync(b.keys[0], b.keys[1], sizeof(uint32_t) * (size_t)n_layout, cudaMemcpyDeviceToDevice, s);
                 chain_break();
@@ -186,8 +187,7 @@ static int bin_and_render(int P, int W, int H, int64_t n_layout, const unsigned 
         }
         GSR_STAGE("tile sort");
     }
-    { StageTimer t(ST_RANGES, s); launch_tile_ranges(b.keys[0], n_layout, iv.ranges, tiles, s, n_dev); }
-    GSR_STAGE("tile ranges");
+    // (tile ranges: written by the last pass of the tile sort)
     {
         StageTimer t(ST_RENDER_FWD, s);
         launch_render_forward(W, H, iv.ranges, b.vals[0], g, background, out_color, out_depth, out_alpha, iv.n_contrib, s);
@@ -451,6 +451,12 @@ int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix, const
 
 // ---- parity accessor ----------------------------------------------------------------------------
 namespace {
+__global__ void decode_ranges_kernel(const uint2* __restrict__ enc, int tiles, uint2* __restrict__ out)
+{
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < tiles) out[t] = load_range(enc, t);
+}
+
 __global__ void unpack_geom_kernel(int P, GeomView g, float* depths, float* means2D, float* conic_opacity, float* rgb,
                                    uint32_t* tiles_touched, uint8_t* clamped)
 {
@@ -498,7 +504,7 @@ int gsr_debug_dump(int P, int W, int H, int64_t num_rendered, const void* geomet
     if (point_list && num_rendered > 0)
         cudaMemcpyAsync(point_list, b.vals[0], sizeof(uint32_t) * (size_t)num_rendered, cudaMemcpyDeviceToDevice, s);
         chain_break();
-    if (ranges) cudaMemcpyAsync(ranges, iv.ranges, sizeof(uint2) * (size_t)tiles, cudaMemcpyDeviceToDevice, s);
+    if (ranges) decode_ranges_kernel<<<div_up(tiles, 256), 256, 0, s>>>(iv.ranges, tiles, reinterpret_cast<uint2*>(ranges));
     if (n_contrib) cudaMemcpyAsync(n_contrib, iv.n_contrib, sizeof(uint32_t) * (size_t)W * H, cudaMemcpyDeviceToDevice, s);
     unpack_geom_kernel<<<div_up(P, 256), 256, 0, s>>>(P, g, depths, means2D, conic_opacity, rgb, tiles_touched, clamped);
     GSR_STAGE("debug dump");

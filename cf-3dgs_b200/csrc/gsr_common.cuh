@@ -37,7 +37,7 @@ struct GeomView {
     uint8_t* clamped;      // [P] bit ch set if SH colour channel ch was clamped at 0
     uint32_t* sort_keys[2];  // [P] ping-pong depth keys
     uint32_t* sort_vals[2];  // [P] ping-pong Gaussian ids; sort_vals[0] ends up holding the depth order
-    uint32_t* offsets;     // [P] exclusive scan of tiles[] in depth order
+    uint32_t* offsets;     // [P, first 8*nblk(P) used] sums of tiles[] per 256 depth ranks (the emit kernel scans the rest itself)
     uint32_t* hist;        // [RADIX * nblk(P)] per-block digit counts
     uint32_t* digit_total; // [SORT_AUX_WORDS] per-pass global digit histograms, block tickets
     uint32_t* block_sums;  // [nblk(P)+1]
@@ -114,6 +114,17 @@ inline size_t bin_layout(char* base, int64_t R, BinView& b)
 // ---- small device helpers ------------------------------------------------------------------
 #ifdef __CUDACC__
 __device__ __forceinline__ unsigned lane_id() { return threadIdx.x & 31; }
+
+// Tile ranges (reference: identifyTileRanges, rasterizer_impl.cu:116-138) are written by atomics inside the last
+// pass of the tile sort: every block knows where its own run of a tile id lands, the smallest start and the largest
+// end over the blocks are the tile's range.  So that zero-initialised memory works for both with atomicMax, .x holds
+// the COMPLEMENT of the start; a tile nobody touched decodes to the reference's (0, 0).
+__device__ __forceinline__ uint2 load_range(const uint2* __restrict__ ranges, int tile)
+{
+    uint2 r = ranges[tile];
+    r.x = r.y ? ~r.x : 0u;
+    return r;
+}
 
 // Block-wide exclusive scan of one value per thread (blockDim.x == 256). smem: 8 uint32.
 __device__ __forceinline__ uint32_t block_exclusive_scan_256(uint32_t v, uint32_t* warp_sums, uint32_t* total)

@@ -32,16 +32,15 @@ void launch_mark_visible(int P, const float* means3D, const float* view, uint8_t
 // holds the result.
 int radix_sort_pairs(uint32_t* keys[2], uint32_t* vals[2], int64_t n, int begin_bit, int end_bit,
                      uint32_t* hist, uint32_t* digit_total, cudaStream_t s,
-                     const unsigned long long* n_dev = nullptr, const uint32_t* first_keys = nullptr);
+                     const unsigned long long* n_dev = nullptr, const uint32_t* first_keys = nullptr,
+                     uint2* ranges = nullptr);   // ranges: the LAST pass also writes the tile ranges (load_range())
 
-// offsets[i] = exclusive prefix sum of tiles[order[i]]
-void launch_offsets_scan(const uint32_t* tiles, const uint32_t* order, uint32_t* offsets, uint32_t* block_sums,
+// partial sums of tiles[order[i]] per 2048 ranks (block_sums) and per 256 ranks (group_sums) for the emit kernel
+void launch_offsets_scan(const uint32_t* tiles, const uint32_t* order, uint32_t* group_sums, uint32_t* block_sums,
                          int P, cudaStream_t s);
 void launch_init_sort_input(const GeomView& g, int P, cudaStream_t s);
 void launch_emit(const GeomView& g, const uint32_t* order, int P, int grid_x, uint32_t* tile_keys,
                  uint32_t* tile_vals, int64_t cap, cudaStream_t s);
-void launch_tile_ranges(const uint32_t* sorted_tiles, int64_t R, uint2* ranges, int tiles, cudaStream_t s,
-                        const unsigned long long* n_dev = nullptr);
 void launch_publish_status(const unsigned long long* counters, int64_t cap, long long* status, cudaStream_t s);
 void launch_build_keys(const uint32_t* sorted_tiles, const uint32_t* point_list, const uint32_t* depth_key,
                        int64_t R, const unsigned long long* n_dev, uint64_t* keys_out, cudaStream_t s);

@@ -86,7 +86,7 @@ render_backward_packed_kernel(int W, int H, int grid_x, const uint2* __restrict_
 
     pdl_wait();
     pdl_trigger();
-    const uint2 range = ranges[tile];
+    const uint2 range = load_range(ranges, tile);
     const int total = (int)(range.y - range.x);
     if (total == 0) return;
 

@@ -50,7 +50,7 @@ render_forward_packed_kernel(int W, int H, int grid_x, const uint2* __restrict__
 
     pdl_wait();
     pdl_trigger();
-    const uint2 range = ranges[tile];
+    const uint2 range = load_range(ranges, tile);
     const int total = (int)(range.y - range.x);
     const bool inside_a = pix_x < W && pix_ya < H, inside_b = pix_x < W && pix_yb < H;
     // A finished pixel (outside the image, or T*(1-alpha) < 1e-4 reached) carries its transmittance with the sign
@@ -185,7 +185,7 @@ pair_counts_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges, c
     const int pix_x = tile_x * TILE + (warp & 1) * FOOT_W + (lane & 7), pix_y = tile_y * TILE + (warp >> 1) * FOOT_H + (lane >> 3);
     const bool inside = pix_x < W && pix_y < H;
     const float pxf = (float)pix_x, pyf = (float)pix_y;
-    const uint2 range = ranges[tile];
+    const uint2 range = load_range(ranges, tile);
     const int total = (int)(range.y - range.x);
     const int last = inside ? (int)n_contrib[(size_t)W * pix_y + pix_x] : 0;
     unsigned long long in_range = 0, blended = 0, tile_rej = 0;

@@ -126,7 +126,7 @@ radix_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __res
                      uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int64_t n_cap,
                      const unsigned long long* __restrict__ n_dev, int shift,
                      uint32_t mask, const uint32_t* __restrict__ hist, int nblk,
-                     const uint32_t* __restrict__ digit_total)
+                     const uint32_t* __restrict__ digit_total, uint2* __restrict__ ranges)
 {
     __shared__ uint32_t wcount[SORT_THREADS / 32][RADIX + 1];
     __shared__ uint32_t goff[RADIX];   // global base of digit d for this block minus its block-local start
@@ -230,13 +230,20 @@ radix_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __res
             const uint32_t pos = goff[(k >> shift) & mask] + (uint32_t)t;
             keys_out[pos] = k;
             vals_out[pos] = sval[t];
+            // last pass of the tile sort: the block's items with one tile id sit next to each other (equal last digit, and
+            // inside it the order the earlier passes left: ascending lower bits), so the two ends of each such run give the
+            // tile's range -- see load_range() in gsr_common.cuh
+            if (ranges) {
+                if (t == 0 || skey[t - 1] != k) atomicMax(&ranges[k].x, ~pos);
+                if (t == count - 1 || skey[t + 1] != k) atomicMax(&ranges[k].y, pos + 1u);
+            }
         }
     }
 }
 
 int radix_sort_pairs(uint32_t* keys[2], uint32_t* vals[2], int64_t n, int begin_bit, int end_bit,
                      uint32_t* hist, uint32_t* digit_total, cudaStream_t s, const unsigned long long* n_dev,
-                     const uint32_t* first_keys)
+                     const uint32_t* first_keys, uint2* ranges)
 {
     int cur = 0;
     if (n <= 0) return cur;
@@ -256,7 +263,8 @@ int radix_sort_pairs(uint32_t* keys[2], uint32_t* vals[2], int64_t n, int begin_
         const bool ballots = !(shift == 24 && end_bit == 32);
 #define GSR_SCATTER(B)                                                                                                \
     launch_pdl(radix_scatter_kernel<B>, nblk, SORT_THREADS, 0, s, kin, vin, keys[cur ^ 1], vals[cur ^ 1], n, n_dev, shift, \
-               mask, (const uint32_t*)hist, nblk, (const uint32_t*)digit_total)
+               mask, (const uint32_t*)hist, nblk, (const uint32_t*)digit_total,                                       \
+               (shift + RADIX_BITS >= end_bit) ? ranges : (uint2*)nullptr)
         if (!ballots) GSR_SCATTER(0);
         else if (bits <= 5) GSR_SCATTER(5);
         else GSR_SCATTER(8);
@@ -283,11 +291,17 @@ void launch_init_sort_input(const GeomView& g, int P, cudaStream_t s)
 }
 
 // ---------------------------------------------------------------------------------------------
-// offsets[i] = exclusive prefix sum over depth order of tiles[order[i]]  (reference: cub InclusiveSum over
-// Gaussian order, rasterizer_impl.cu:278; here over depth order because instances are emitted in depth order)
+// Instance offsets = exclusive prefix sum over depth order of tiles[order[i]]  (reference: cub InclusiveSum over
+// Gaussian order, rasterizer_impl.cu:278; here over depth order because instances are emitted in depth order).
+// Two levels of partial sums are all that is stored: per 2048 ranks (block_sums) and per 256 ranks (group_sums, one
+// per warp of this kernel = one per block of the emit kernel).  The emit kernel adds up the sums in front of its
+// 256 ranks itself and scans its own ranks in shared memory, so no per-rank offset array is written or read and the
+// second scan kernel is gone.
+static_assert(SORT_ITEMS * 32 == 256, "one warp of the sums kernel covers the 256 ranks of one emit block");
+
 __global__ void __launch_bounds__(SORT_THREADS)
 scan_block_sums_kernel(const uint32_t* __restrict__ tiles, const uint32_t* __restrict__ order, int P,
-                       uint32_t* __restrict__ block_sums)
+                       uint32_t* __restrict__ block_sums, uint32_t* __restrict__ group_sums)
 {
     __shared__ uint32_t warp_sums[8];
     const int base = blockIdx.x * SORT_CHUNK + threadIdx.x * SORT_ITEMS;
@@ -297,46 +311,27 @@ scan_block_sums_kernel(const uint32_t* __restrict__ tiles, const uint32_t* __res
 #pragma unroll
     for (int i = 0; i < SORT_ITEMS; i++)
         if (base + i < P) sum += tiles[order[base + i]];
-    uint32_t total;
-    block_exclusive_scan_256(sum, warp_sums, &total);
-    if (threadIdx.x == 0) block_sums[blockIdx.x] = total;
-}
-
-__global__ void __launch_bounds__(SORT_THREADS)
-scan_final_kernel(const uint32_t* __restrict__ tiles, const uint32_t* __restrict__ order, int P,
-                  const uint32_t* __restrict__ block_sums, uint32_t* __restrict__ offsets)
-{
-    __shared__ uint32_t warp_sums[8];
-    const int base = blockIdx.x * SORT_CHUNK + threadIdx.x * SORT_ITEMS;
-    uint32_t v[SORT_ITEMS];
-    uint32_t sum = 0;
-    pdl_wait();
-    pdl_trigger();
+    uint32_t wsum = sum;
 #pragma unroll
-    for (int i = 0; i < SORT_ITEMS; i++) {
-        v[i] = (base + i < P) ? tiles[order[base + i]] : 0u;
-        sum += v[i];
+    for (int o = 16; o > 0; o >>= 1) wsum += __shfl_xor_sync(0xffffffffu, wsum, o);
+    if ((threadIdx.x & 31) == 0) {
+        warp_sums[threadIdx.x >> 5] = wsum;
+        group_sums[blockIdx.x * 8 + (threadIdx.x >> 5)] = wsum;
     }
-    // the block's base = sum of the totals of the blocks before it: every block adds those up itself (a few hundred
-    // coalesced words) instead of waiting for a one-block scan kernel in between
-    uint32_t before = 0;
-    for (int i = threadIdx.x; i < (int)blockIdx.x; i += SORT_THREADS) before += block_sums[i];
-    uint32_t block_base;
-    block_exclusive_scan_256(before, warp_sums, &block_base);
-    uint32_t run = block_exclusive_scan_256(sum, warp_sums, nullptr) + block_base;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t total = 0;
 #pragma unroll
-    for (int i = 0; i < SORT_ITEMS; i++) {
-        if (base + i < P) offsets[base + i] = run;
-        run += v[i];
+        for (int w = 0; w < 8; w++) total += warp_sums[w];
+        block_sums[blockIdx.x] = total;
     }
 }
 
-void launch_offsets_scan(const uint32_t* tiles, const uint32_t* order, uint32_t* offsets, uint32_t* block_sums,
+void launch_offsets_scan(const uint32_t* tiles, const uint32_t* order, uint32_t* group_sums, uint32_t* block_sums,
                          int P, cudaStream_t s)
 {
     const int nblk = div_up(P, SORT_CHUNK);
-    launch_pdl(scan_block_sums_kernel, nblk, SORT_THREADS, 0, s, tiles, order, P, block_sums);
-    launch_pdl(scan_final_kernel, nblk, SORT_THREADS, 0, s, tiles, order, P, (const uint32_t*)block_sums, offsets);
+    launch_pdl(scan_block_sums_kernel, nblk, SORT_THREADS, 0, s, tiles, order, P, block_sums, group_sums);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -350,9 +345,11 @@ constexpr int EMIT_THREADS = 256;
 
 __global__ void __launch_bounds__(EMIT_THREADS)
 emit_kernel(const uint32_t* __restrict__ order, const uint32_t* __restrict__ tiles,
-            const uint32_t* __restrict__ offsets, const uint2* __restrict__ rect, int P, int grid_x,
+            const uint32_t* __restrict__ group_sums, const uint32_t* __restrict__ block_sums,
+            const uint2* __restrict__ rect, int P, int grid_x,
             uint32_t* __restrict__ tile_keys, uint32_t* __restrict__ tile_vals, uint32_t cap)
 {
+    __shared__ uint32_t warp_sums[8];
     __shared__ uint32_t s_off[EMIT_THREADS + 1];
     __shared__ uint32_t s_gid[EMIT_THREADS];
     __shared__ uint2 s_rect[EMIT_THREADS];
@@ -363,9 +360,19 @@ emit_kernel(const uint32_t* __restrict__ order, const uint32_t* __restrict__ til
     pdl_trigger();
     if (r < P) {
         gid = order[r];
-        off = offsets[r];
         n = tiles[gid];
         rc = rect[gid];
+    }
+    {
+        // instances in front of this block: whole 2048-rank chunks, then the 256-rank groups of its own chunk
+        const int chunk = blockIdx.x >> 3;
+        uint32_t before = 0;
+        for (int i = threadIdx.x; i < chunk; i += EMIT_THREADS) before += block_sums[i];
+        if ((int)threadIdx.x < (int)(blockIdx.x & 7)) before += group_sums[chunk * 8 + threadIdx.x];
+        uint32_t block_base;
+        block_exclusive_scan_256(before, warp_sums, &block_base);
+        const uint32_t mine = block_exclusive_scan_256(n, warp_sums, nullptr) + block_base;
+        if (r < P) off = mine;
     }
     s_off[threadIdx.x] = off;
     s_gid[threadIdx.x] = gid;
@@ -423,49 +430,8 @@ void launch_emit(const GeomView& g, const uint32_t* order, int P, int grid_x, ui
                  uint32_t* tile_vals, int64_t cap, cudaStream_t s)
 {
     launch_pdl(emit_kernel, div_up(P, EMIT_THREADS), EMIT_THREADS, 0, s, order, (const uint32_t*)g.tiles,
-               (const uint32_t*)g.offsets, (const uint2*)g.rect, P, grid_x, tile_keys, tile_vals, (uint32_t)cap);
-}
-
-// ---------------------------------------------------------------------------------------------
-// reference identifyTileRanges (rasterizer_impl.cu:116-138) on the sorted tile ids
-__global__ void __launch_bounds__(256)
-tile_ranges_kernel(const uint32_t* __restrict__ sorted_tiles, int64_t R_cap,
-                   const unsigned long long* __restrict__ n_dev, uint2* __restrict__ ranges)
-{
-    // four consecutive entries per thread (one 16-byte load) plus the entry before them
-    pdl_wait();
-    pdl_trigger();
-    const int64_t R = device_count(n_dev, R_cap);
-    const int64_t i0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
-    if (i0 >= R) return;
-    uint32_t t[5];
-    t[0] = i0 > 0 ? __ldg(sorted_tiles + i0 - 1) : 0xffffffffu;
-    if (i0 + 3 < R) {
-        const uint4 q = __ldg(reinterpret_cast<const uint4*>(sorted_tiles + i0));
-        t[1] = q.x; t[2] = q.y; t[3] = q.z; t[4] = q.w;
-    } else {
-#pragma unroll
-        for (int c = 0; c < 4; c++) t[c + 1] = i0 + c < R ? __ldg(sorted_tiles + i0 + c) : 0xffffffffu;
-    }
-#pragma unroll
-    for (int c = 0; c < 4; c++) {
-        const int64_t i = i0 + c;
-        if (i >= R) break;
-        const uint32_t cur = t[c + 1], prev = t[c];
-        if (i == 0) ranges[cur].x = 0;
-        else if (cur != prev) {
-            ranges[prev].y = (uint32_t)i;
-            ranges[cur].x = (uint32_t)i;
-        }
-        if (i == R - 1) ranges[cur].y = (uint32_t)R;
-    }
-}
-
-void launch_tile_ranges(const uint32_t* sorted_tiles, int64_t R, uint2* ranges, int tiles, cudaStream_t s,
-                        const unsigned long long* n_dev)
-{
-    (void)tiles;   // the caller has zeroed ranges (empty tiles read (0,0), rasterizer_impl.cu:311)
-    if (R > 0) launch_pdl(tile_ranges_kernel, div_up(div_up(R, 4), 256), 256, 0, s, sorted_tiles, R, n_dev, ranges);
+               (const uint32_t*)g.offsets, (const uint32_t*)g.block_sums, (const uint2*)g.rect, P, grid_x, tile_keys,
+               tile_vals, (uint32_t)cap);
 }
 
 // sync-free forward: publish (count, overflow) for the host to look at whenever it likes.  The status words only ever

@@ -84,7 +84,7 @@ for P in sizes:
     in_range, blended, _, _ = [int(x) for x in counts.tolist()]
     vis = int((holder["out"][1] > 0).sum())
     tiles = ((W + 15) // 16) * ((H + 15) // 16)
-    sort_ms = st["depth_sort"] + st["offsets_scan"] + st["emit"] + st["tile_sort"] + st["tile_ranges"]
+    sort_ms = st["depth_sort"] + st["offsets_scan"] + st["emit"] + st["tile_sort"] + st.get("tile_ranges", 0.0)
     sort_bytes = P * 16 + P * 8 + (P * 20 + R * 12) + R * 24 + R * 8 + tiles * 8          # SURVEY.md 8d floors
     line = {"P": P, "visible": vis, "num_rendered": R, "pairs_blended": blended, "ms_fwd_bwd": ms, "frames_per_s": 1000.0 / ms,
             "gaussians_per_s": P * 1000.0 / ms, "stages_ms": {k: round(v, 4) for k, v in st.items()},
