@@ -120,56 +120,43 @@ radix_rowscan_kernel(uint32_t* __restrict__ hist, int nblk, uint32_t* __restrict
 // Measured on B200 (tools/micro/match_bench.cu): MATCH.ANY costs ~7 cycles per DISTINCT value in the warp (226 cycles
 // for 32 distinct values), eight ballots a flat ~109 -- and the digits a warp sees here are mostly distinct (low tile
 // bits of consecutive instances, low mantissa bits of depths).
-template <int BALLOT_BITS>
-__global__ void __launch_bounds__(SORT_THREADS, GSR_SCATTER_MIN_BLOCKS)
-radix_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
-                     uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int64_t n_cap,
-                     const unsigned long long* __restrict__ n_dev, int shift,
-                     uint32_t mask, const uint32_t* __restrict__ hist, int nblk,
-                     const uint32_t* __restrict__ digit_total, uint2* __restrict__ ranges)
+template <int BALLOT_BITS, bool FULL>
+__device__ __forceinline__ void scatter_block(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+                                              uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int count,
+                                              int shift, uint32_t mask, uint32_t my_gbase, uint2* __restrict__ ranges,
+                                              uint32_t (*wcount)[RADIX + 1], uint32_t* goff, uint32_t* warp_sums,
+                                              uint32_t* skey, uint32_t* sval)
 {
-    __shared__ uint32_t wcount[SORT_THREADS / 32][RADIX + 1];
-    __shared__ uint32_t goff[RADIX];   // global base of digit d for this block minus its block-local start
-    __shared__ uint32_t warp_sums[8];
-    __shared__ uint32_t skey[SORT_CHUNK], sval[SORT_CHUNK];
+    // FULL: all SORT_CHUNK items of the block exist (every block but the last): no bounds logic anywhere below
     const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    for (int i = threadIdx.x; i < (SORT_THREADS / 32) * (RADIX + 1); i += SORT_THREADS) (&wcount[0][0])[i] = 0;
-    pdl_wait();
-    pdl_trigger();
-    const int64_t n = device_count(n_dev, n_cap);
-    // global base of each digit for this block = exclusive scan of digit totals + row prefix
-    uint32_t my_gbase;
-    {
-        const uint32_t tot = digit_total[threadIdx.x];
-        const uint32_t ex = block_exclusive_scan_256(tot, warp_sums, nullptr);  // contains __syncthreads
-        my_gbase = ex + hist[(size_t)threadIdx.x * nblk + blockIdx.x];
-    }
-    // each warp owns a contiguous run of SORT_ITEMS*32 items; order inside it is (step, lane)
-    const int64_t block_base = (int64_t)blockIdx.x * SORT_CHUNK;
-    const int64_t wbase = block_base + (int64_t)warp * (SORT_ITEMS * 32);
+    const uint32_t block_base = blockIdx.x * (uint32_t)SORT_CHUNK;       // item counts are below 2^31 (GSR_ERR_OVERFLOW)
+    const uint32_t wfirst = warp * (SORT_ITEMS * 32) + lane;              // block-local index of this lane's first item
     uint32_t key[SORT_ITEMS], rank[SORT_ITEMS];
 #pragma unroll
     for (int i = 0; i < SORT_ITEMS; i++) {
-        const int64_t idx = wbase + i * 32 + lane;
-        key[i] = idx < n ? keys_in[idx] : 0u;
+        const uint32_t li = wfirst + i * 32;
+        key[i] = (FULL || (int)li < count) ? keys_in[block_base + li] : 0u;
     }
-    // Ranking, written so that the eight items' latencies overlap instead of adding up: all MATCHes first, then one
+    // Ranking, written so that the eight items' latencies overlap instead of adding up: all group masks first, then one
     // shared-memory atomic per digit group (the group leader fetches-and-adds the warp-private counter; a warp's
     // shared-memory instructions execute in order, so item i's groups are counted before item i+1's), then the
     // broadcasts.  Nothing in one item's chain waits for another item's result.
     unsigned grp[SORT_ITEMS];
 #pragma unroll
     for (int i = 0; i < SORT_ITEMS; i++) {
-        const bool act = (wbase + i * 32 + lane) < n;
+        const bool act = FULL || (int)(wfirst + i * 32) < count;
         const uint32_t d = act ? ((key[i] >> shift) & mask) : (uint32_t)RADIX;
         if (BALLOT_BITS > 0) {
-            unsigned same = __ballot_sync(0xffffffffu, act);
-            if (!act) same = ~same;
+            unsigned same = 0xffffffffu;
+            if (!FULL) {
+                same = __ballot_sync(0xffffffffu, act);
+                if (!act) same = ~same;
+            }
 #pragma unroll
             for (int b = 0; b < BALLOT_BITS; b++) {
                 const bool bit = (d >> b) & 1u;
                 const unsigned bal = __ballot_sync(0xffffffffu, bit);
-                same &= bit ? bal : ~bal;
+                if (bit) same &= bal; else same &= ~bal;
             }
             grp[i] = same;
         } else {
@@ -178,7 +165,7 @@ radix_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __res
     }
 #pragma unroll
     for (int i = 0; i < SORT_ITEMS; i++) {
-        const bool act = (wbase + i * 32 + lane) < n;
+        const bool act = FULL || (int)(wfirst + i * 32) < count;
         const uint32_t d = act ? ((key[i] >> shift) & mask) : (uint32_t)RADIX;
         rank[i] = 0;
         if (lane == (unsigned)(__ffs(grp[i]) - 1)) rank[i] = atomicAdd(&wcount[warp][d], (uint32_t)__popc(grp[i]));
@@ -204,16 +191,16 @@ radix_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __res
     }
     __syncthreads();
     // the values are only needed now: loading them here instead of next to the keys keeps 8 registers free during the
-    // ranking loop (occupancy is what hides its shared-memory / MATCH latency)
+    // ranking loop (occupancy is what hides its shared-memory latency)
     uint32_t val[SORT_ITEMS];
 #pragma unroll
     for (int i = 0; i < SORT_ITEMS; i++) {
-        const int64_t idx = wbase + i * 32 + lane;
-        val[i] = vals_in ? (idx < n ? vals_in[idx] : 0u) : (uint32_t)idx;   // no value array: the item index
+        const uint32_t li = wfirst + i * 32;
+        val[i] = vals_in ? ((FULL || (int)li < count) ? vals_in[block_base + li] : 0u) : block_base + li;   // no value array: the item index
     }
 #pragma unroll
     for (int i = 0; i < SORT_ITEMS; i++) {
-        if ((wbase + i * 32 + lane) < n) {
+        if (FULL || (int)(wfirst + i * 32) < count) {
             const uint32_t d = (key[i] >> shift) & mask;
             const uint32_t lp = wcount[warp][d] + rank[i];
             skey[lp] = key[i];
@@ -221,11 +208,10 @@ radix_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __res
         }
     }
     __syncthreads();
-    const int count = (int)max((int64_t)0, min((int64_t)SORT_CHUNK, n - block_base));
 #pragma unroll
     for (int i = 0; i < SORT_ITEMS; i++) {
         const int t = i * SORT_THREADS + threadIdx.x;
-        if (t < count) {
+        if (FULL || t < count) {
             const uint32_t k = skey[t];
             const uint32_t pos = goff[(k >> shift) & mask] + (uint32_t)t;
             keys_out[pos] = k;
@@ -239,6 +225,38 @@ radix_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __res
             }
         }
     }
+}
+
+template <int BALLOT_BITS>
+__global__ void __launch_bounds__(SORT_THREADS, GSR_SCATTER_MIN_BLOCKS)
+radix_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+                     uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int64_t n_cap,
+                     const unsigned long long* __restrict__ n_dev, int shift,
+                     uint32_t mask, const uint32_t* __restrict__ hist, int nblk,
+                     const uint32_t* __restrict__ digit_total, uint2* __restrict__ ranges)
+{
+    __shared__ uint32_t wcount[SORT_THREADS / 32][RADIX + 1];
+    __shared__ uint32_t goff[RADIX];   // global base of digit d for this block minus its block-local start
+    __shared__ uint32_t warp_sums[8];
+    __shared__ uint32_t skey[SORT_CHUNK + 1], sval[SORT_CHUNK];
+    for (int i = threadIdx.x; i < (SORT_THREADS / 32) * (RADIX + 1); i += SORT_THREADS) (&wcount[0][0])[i] = 0;
+    pdl_wait();
+    pdl_trigger();
+    const int64_t n = device_count(n_dev, n_cap);
+    const int count = (int)max((int64_t)0, min((int64_t)SORT_CHUNK, n - (int64_t)blockIdx.x * SORT_CHUNK));
+    // global base of each digit for this block = exclusive scan of digit totals + row prefix
+    uint32_t my_gbase;
+    {
+        const uint32_t tot = digit_total[threadIdx.x];
+        const uint32_t ex = block_exclusive_scan_256(tot, warp_sums, nullptr);  // contains __syncthreads
+        my_gbase = ex + hist[(size_t)threadIdx.x * nblk + blockIdx.x];
+    }
+    if (count == SORT_CHUNK)
+        scatter_block<BALLOT_BITS, true>(keys_in, vals_in, keys_out, vals_out, count, shift, mask, my_gbase, ranges, wcount,
+                                         goff, warp_sums, skey, sval);
+    else if (count > 0)
+        scatter_block<BALLOT_BITS, false>(keys_in, vals_in, keys_out, vals_out, count, shift, mask, my_gbase, ranges, wcount,
+                                          goff, warp_sums, skey, sval);
 }
 
 int radix_sort_pairs(uint32_t* keys[2], uint32_t* vals[2], int64_t n, int begin_bit, int end_bit,
