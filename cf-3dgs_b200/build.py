@@ -9,7 +9,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libgsr_b200.so")
 SOURCES = ["gsr_api.cu", "gsr_preprocess.cu", "gsr_sort.cu", "gsr_render_fwd.cu", "gsr_render_bwd.cu",
-           "gsr_preprocess_bwd.cu", "gsr_pose_static.cu", "gsr_loss.cu", "gsr_model.cu", "gsr_knn.cu", "gsr_peaks.cu"]
+           "gsr_preprocess_bwd.cu", "gsr_pose_static.cu", "gsr_loss.cu", "gsr_model.cu", "gsr_knn.cu", "gsr_peaks.cu", "gsr_pose_opt.cu"]
 NVCC_FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden"]
 

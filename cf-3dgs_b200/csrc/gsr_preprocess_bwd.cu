@@ -22,19 +22,6 @@ constexpr int SLAB_ROW4 = 13;
 
 int pose_blocks(int P) { return div_up(P, PB_THREADS); }
 
-__device__ __forceinline__ float block_sum_256(float v, float* red)
-{
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
-    __syncthreads();
-    float t = 0.f;
-#pragma unroll
-    for (int w = 0; w < PB_THREADS / 32; w++) t += red[w];
-    __syncthreads();
-    return t;
-}
-
 template <bool SLAB>
 #ifndef GSR_PB_MIN_BLOCKS
 #define GSR_PB_MIN_BLOCKS 6
@@ -43,7 +30,6 @@ __global__ void __launch_bounds__(PB_THREADS, GSR_PB_MIN_BLOCKS)
 preprocess_backward_kernel(PreprocessBwdArgs a, GeomView g)
 {
     __shared__ float sV[16], sP[16], sCam[3];
-    __shared__ float red[PB_THREADS / 32];
     __shared__ float4 slab[SLAB ? PB_THREADS * SLAB_ROW4 : 1];
     pdl_wait();
     pdl_trigger();
@@ -238,7 +224,7 @@ preprocess_backward_kernel(PreprocessBwdArgs a, GeomView g)
                 gmz += (-ox * oz * ddx - oy * oz * ddy + (sum2 - oz * oz) * ddz) * inv32;
             }
             // ---- cov3D -> scale, rotation (backward.cu:278-341) ----
-            if (a.scales) {
+            if (a.scales && a.dL_dscales) {
                 const float r = rq.x, x = rq.y, y = rq.z, z = rq.w;
                 // glm columns of R
                 const float R[3][3] = {{1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y)},
@@ -320,37 +306,56 @@ preprocess_backward_kernel(PreprocessBwdArgs a, GeomView g)
         for (int q = threadIdx.x; q < rows * 12; q += PB_THREADS) dst[q] = slab[(q / 12) * SLAB_ROW4 + (q % 12)];
     }
     if (a.dL_dpose) {
-        // rigid pose gradient at xi = 0 for p' = Exp(xi) p:  d/dnu = g,  d/domega = p x g
-        const float v0 = block_sum_256(gmx, red), v1 = block_sum_256(gmy, red), v2 = block_sum_256(gmz, red);
-        const float w0 = block_sum_256(py * gmz - pz * gmy, red);
-        const float w1 = block_sum_256(pz * gmx - px * gmz, red);
-        const float w2 = block_sum_256(px * gmy - py * gmx, red);
-        if (threadIdx.x == 0) {
-            float* o = a.pose_scratch + (size_t)blockIdx.x * 6;
-            o[0] = v0; o[1] = v1; o[2] = v2; o[3] = w0; o[4] = w1; o[5] = w2;
+        // rigid pose gradient at xi = 0 for p' = Exp(xi) p:  d/dnu = g,  d/domega = p x g.  Six warp reductions, one
+        // barrier, then six threads add the warps' values (the earlier form took twelve barriers per block and cost more
+        // than the rest of the kernel in a pose-only fit).
+        __shared__ float pose_red[PB_THREADS / 32][6];
+        float v[6] = {gmx, gmy, gmz, py * gmz - pz * gmy, pz * gmx - px * gmz, px * gmy - py * gmx};
+#pragma unroll
+        for (int c = 0; c < 6; c++) {
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) v[c] += __shfl_xor_sync(0xffffffffu, v[c], o);
+        }
+        if ((threadIdx.x & 31) == 0) {
+#pragma unroll
+            for (int c = 0; c < 6; c++) pose_red[threadIdx.x >> 5][c] = v[c];
+        }
+        __syncthreads();
+        if (threadIdx.x < 6) {
+            float t = 0.f;
+#pragma unroll
+            for (int w = 0; w < PB_THREADS / 32; w++) t += pose_red[w][threadIdx.x];
+            a.pose_scratch[(size_t)blockIdx.x * 6 + threadIdx.x] = t;
         }
     }
 }
 
 // deterministic second stage: one block sums the per-block partials in double
-__global__ void __launch_bounds__(256) pose_reduce_kernel(const float* __restrict__ partial, int nblk, float* __restrict__ out)
+// (fixed summation order: thread t takes partials t, t + 1024, ..., then warps, then the 32 warp sums in order)
+__global__ void __launch_bounds__(1024) pose_reduce_kernel(const float* __restrict__ partial, int nblk, float* __restrict__ out)
 {
-    __shared__ double red[8];
+    __shared__ double red[32][6];
     pdl_wait();
     pdl_trigger();
-    for (int c = 0; c < 6; c++) {
-        double v = 0.0;
-        for (int i = threadIdx.x; i < nblk; i += 256) v += (double)partial[(size_t)i * 6 + c];
+    double v[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+    for (int i = threadIdx.x; i < nblk; i += 1024) {
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-        if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            double t = 0.0;
-            for (int w = 0; w < 8; w++) t += red[w];
-            out[c] = (float)t;
-        }
-        __syncthreads();
+        for (int c = 0; c < 6; c++) v[c] += (double)partial[(size_t)i * 6 + c];
+    }
+#pragma unroll
+    for (int c = 0; c < 6; c++) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v[c] += __shfl_xor_sync(0xffffffffu, v[c], o);
+    }
+    if ((threadIdx.x & 31) == 0) {
+#pragma unroll
+        for (int c = 0; c < 6; c++) red[threadIdx.x >> 5][c] = v[c];
+    }
+    __syncthreads();
+    if (threadIdx.x < 6) {
+        double t = 0.0;
+        for (int w = 0; w < 32; w++) t += red[w][threadIdx.x];
+        out[threadIdx.x] = (float)t;
     }
 }
 
@@ -361,7 +366,7 @@ void launch_preprocess_backward(const PreprocessBwdArgs& a, const GeomView& g, c
     const bool slab = a.shs && a.dL_dsh && a.M == 16 && a.dsh_M == 16 && (((uintptr_t)a.shs | (uintptr_t)a.dL_dsh) & 15) == 0;
     if (slab) launch_pdl(preprocess_backward_kernel<true>, nblk, PB_THREADS, 0, s, a, g);
     else launch_pdl(preprocess_backward_kernel<false>, nblk, PB_THREADS, 0, s, a, g);
-    if (a.dL_dpose) launch_pdl(pose_reduce_kernel, 1, 256, 0, s, (const float*)a.pose_scratch, nblk, a.dL_dpose);
+    if (a.dL_dpose) launch_pdl(pose_reduce_kernel, 1, 1024, 0, s, (const float*)a.pose_scratch, nblk, a.dL_dpose);
 }
 
 }  // namespace gsr

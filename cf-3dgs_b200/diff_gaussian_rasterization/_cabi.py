@@ -38,6 +38,7 @@ SIGNATURES = {
     "gsr_backward": (c_int, [c_int, c_int, c_int, c_int, c_int, c_int64, _P, _P, _P, _P, _P, _P, c_float, _P, _P,
                              _P, _P, c_float, c_float, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P,
                              _P, _P, _P, _P, _P, c_int]),
+    "gsr_pose_adam_step": (c_int, [_P, _P, _P, c_float, c_float, c_float, c_float, _P]),
     "gsr_pose_gradient_static": (c_int, [c_int, _P, _P, _P, _P]),
     "gsr_photo_loss_scratch_bytes": (c_size_t, [c_int, c_int, c_int]),
     "gsr_photo_loss_forward": (c_int, [c_int, c_int, c_int, _P, _P, c_float, c_int, _P, _P, _P]),

@@ -100,3 +100,69 @@ def rasterize_with_pose(raster_settings, xi, xyz, T, opacities, shs=None, colors
     return _PoseRasterize.apply(xi, xyz, T, e if shs is None else shs, e if colors_precomp is None else colors_precomp,
                                 opacities, e if scales is None else scales, e if rotations is None else rotations,
                                 e if cov3D_precomp is None else cov3D_precomp, raster_settings)
+
+
+class PoseOptimizer:
+    """Pose-only fit of a frozen set of Gaussians against target frames (the local pose fit of CF-3DGS,
+    trainer/cf3dgs_trainer.py:262-285) with nothing but library kernels in the loop: render through the rigid entry
+    points, fused L1 + SSIM loss and its gradient, backward that reduces the twist gradient only, and the Adam step +
+    SE(3) retraction on the device (gsr_pose_adam_step).  No autograd graph, no PyTorch element-wise kernel, no host
+    read-back: with the sync-free forward (diff_gaussian_rasterization.set_sync_free) a whole step can be captured in a
+    CUDA graph and replayed.  `T` (4x4, float32, on the device) is the current pose and is updated in place."""
+
+    def __init__(self, raster_settings, xyz, opacities, shs=None, colors_precomp=None, scales=None, rotations=None,
+                 cov3D_precomp=None, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8, lambda_dssim: float = 0.2,
+                 clamp: bool = True, T0=None):
+        from diff_gaussian_rasterization._cabi import lib
+        self._lib = lib
+        self.rs = raster_settings
+        dev = xyz.device
+        e = torch.Tensor([])
+        c = lambda t: e if t is None else t.detach().contiguous().float()
+        self.xyz, self.opacities = c(xyz), c(opacities)
+        self.shs, self.colors, self.scales, self.rotations, self.cov3D = c(shs), c(colors_precomp), c(scales), c(rotations), c(cov3D_precomp)
+        self.T = (torch.eye(4, device=dev) if T0 is None else T0.detach().to(dev).float()).contiguous().clone()
+        self.state = torch.zeros(13, device=dev)
+        self.lr, self.betas, self.eps, self.lam, self.clamp = float(lr), betas, float(eps), float(lambda_dssim), int(bool(clamp))
+        H, W = raster_settings.image_height, raster_settings.image_width
+        with torch.cuda.device(dev):
+            self._scratch = torch.empty(lib.gsr_photo_loss_scratch_bytes(3, H, W), dtype=torch.uint8, device=dev)
+        self._parts = torch.zeros(3, device=dev)       # loss, l1, ssim of the latest step
+        self._dimg = torch.empty(3, H, W, device=dev)
+        self._one = torch.ones(1, device=dev)
+        self._skip = ("means2D", "means3D", "opacity", "sh", "colors", "scales", "cov3D")
+        self.grad = None
+
+    def reset(self, T0=None) -> None:
+        self.state.zero_()
+        if T0 is None:
+            self.T.copy_(torch.eye(4, device=self.T.device))
+        else:
+            self.T.copy_(T0)
+
+    def step(self, target: torch.Tensor) -> torch.Tensor:
+        """One iteration against `target` (3,H,W).  Returns the loss as a 0-dim device tensor (a view that the next step
+        overwrites)."""
+        from diff_gaussian_rasterization._cabi import check
+        rs, lib = self.rs, self._lib
+        H, W = rs.image_height, rs.image_width
+        R, color, depth, alpha, radii, geom, binning, img = D._forward_impl(
+            rs.bg, self.xyz, self.colors, self.opacities, self.scales, self.rotations, rs.scale_modifier, self.cov3D,
+            rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, H, W, self.shs, rs.sh_degree, rs.campos, False, rs.debug,
+            rigid=self.T)
+        with torch.cuda.device(self.xyz.device):
+            s = torch.cuda.current_stream().cuda_stream
+            check(lib.gsr_photo_loss_forward(3, H, W, color.data_ptr(), target.data_ptr(), self.lam, self.clamp,
+                                             self._scratch.data_ptr(), self._parts.data_ptr(), s))
+            check(lib.gsr_photo_loss_backward(3, H, W, color.data_ptr(), target.data_ptr(), self.lam, self.clamp,
+                                              self._scratch.data_ptr(), self._one.data_ptr(), self._dimg.data_ptr(), s))
+        res = D._backward_impl(rs.bg, self.xyz, radii, self.colors, self.scales, self.rotations, rs.scale_modifier, self.cov3D,
+                               rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, self._dimg, None, None, self.shs,
+                               rs.sh_degree, rs.campos, geom, R, binning, img, alpha, rs.debug, want_pose_grad=True,
+                               rigid=self.T, skip=self._skip)
+        self.grad = res[8]
+        with torch.cuda.device(self.xyz.device):
+            check(lib.gsr_pose_adam_step(self.grad.data_ptr(), self.state.data_ptr(), self.T.data_ptr(), self.lr,
+                                         float(self.betas[0]), float(self.betas[1]), self.eps,
+                                         torch.cuda.current_stream().cuda_stream))
+        return self._parts[0]

@@ -194,7 +194,37 @@ def run_pair(p, args, dev, backend):
     T = torch.eye(4, device=dev)
     m = torch.zeros(6, device=dev); v = torch.zeros(6, device=dev)
     lr, b1, b2 = args.pose_lr, 0.9, 0.999
-    if args.graph:
+    fused_pose = args.impl == "ours" and args.loss == "fused" and getattr(args, "pose_loop", "fused") == "fused"
+    if fused_pose:
+        # the library's pose loop: rigid render, fused loss, twist-only backward, Adam + SE(3) retraction on the device --
+        # no PyTorch kernel in the iteration (gsr_pose.PoseOptimizer); as one replayed CUDA graph with --graph
+        popt = GP.PoseOptimizer(rs, xyz_f, opa, shs=fr["shs"], scales=fr["scales"], rotations=fr["rotations"], lr=lr,
+                                betas=(b1, b2), eps=1e-8)
+        if args.graph:
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                for _ in range(3):
+                    popt.step(frame1)
+            torch.cuda.current_stream().wait_stream(side)
+            popt.reset()
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                loss = popt.step(frame1)
+            popt.reset()
+            torch.cuda.synchronize(dev)
+            t0 = time.time()
+            for it in range(args.pose_iters):
+                graph.replay()
+        else:
+            torch.cuda.synchronize(dev)
+            t0 = time.time()
+            for it in range(args.pose_iters):
+                loss = popt.step(frame1)
+        torch.cuda.synchronize(dev)
+        pose_s = time.time() - t0
+        T = popt.T
+    elif args.graph:
         # whole pose iteration (render, loss, backward, Adam on the twist, pose retraction) as ONE CUDA graph:
         # needs the sync-free forward (no host read of num_rendered inside the loop)
         xi = torch.zeros(6, device=dev, requires_grad=True)
@@ -301,7 +331,7 @@ def make_backend(impl, dev):
 
 def default_args(**kw):
     d = dict(pairs=1, fit_iters=200, pose_iters=300, points=250_000, width=960, height=540, pose_lr=1e-3, impl="ours",
-             graph=False, sync_free=False, model=None, loss=None)
+             graph=False, sync_free=False, model=None, loss=None, pose_loop="fused")
     d.update(kw)
     if d["loss"] is None:
         d["loss"] = "fused" if d["impl"] == "ours" else "torch"
@@ -375,6 +405,9 @@ def main():
     ap.add_argument("--graph", action="store_true",
                     help="sync-free forward + the pose iteration captured as one CUDA graph (ours only)")
     ap.add_argument("--sync-free", action="store_true", help="sync-free forward without graph capture (ours only)")
+    ap.add_argument("--pose-loop", default="fused", choices=["fused", "torch"],
+                    help="pose fit: the library's loop (gsr_pose.PoseOptimizer, default for ours with the fused loss) or "
+                         "autograd + PyTorch Adam / retraction ops")
     ap.add_argument("--model", default=None, choices=["fused", "torch"],
                     help="Gaussian fit: the library's fused model step (default for ours) or PyTorch activations + Adam")
     ap.add_argument("--loss", default=None, choices=["fused", "torch"],
