@@ -44,12 +44,12 @@ import torch
 WORKLOAD = dict(name="gvol_1M_1080p_sh3", P=1_000_000, W=1920, H=1080, seed=5, sh_degree=3)
 PARAM_KEYS = ["means3D", "opacities", "shs", "scales", "rotations"]
 # DRAM bytes per launch of the kernels that can dominate, from the committed ncu capture of this workload
-NCU_TRAFFIC_BYTES = {"render_backward": 150.8e6 + 17.5e6, "render_forward": 66.8e6 + 29.3e6,
-                     "preprocess": 253.4e6 + 40.2e6, "preprocess_backward": 284.3e6 + 198.6e6}
+NCU_TRAFFIC_BYTES = {"render_backward": 150.4e6 + 17.9e6, "render_forward": 66.8e6 + 29.1e6,
+                     "preprocess": 253.4e6 + 40.1e6, "preprocess_backward": 284.8e6 + 201.8e6}
 # warp instructions per launch of the two blend kernels on this workload (smsp__inst_executed.sum, same ncu capture):
 # what their issue-slot utilisation is computed from
-NCU_WARP_INSTRUCTIONS = {"render_backward": 659.25e6, "render_forward": 392.0e6}
-NCU_SOURCE = "profiles/r01_ncu_packed_summary.txt"
+NCU_WARP_INSTRUCTIONS = {"render_backward": 659.5e6, "render_forward": 391.8e6}
+NCU_SOURCE = "profiles/r02_ncu_step_1M_summary.txt"
 
 
 def load_peaks():
@@ -629,7 +629,7 @@ def main():
                         "peak": hbm_peak if d["bound"] == "hbm" else fp32_peak, "unit": d["unit"], "frac": d["frac"],
                         "traffic": NCU_TRAFFIC_BYTES.get(dom), "ms": d["ms"],
                         "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full, "
-                                          "profiles/r01_ncu_packed_summary.txt (same workload)",
+                                          NCU_SOURCE + " (same workload)",
                         "peak_source": (f"{peak_kind} HBM copy" if d["bound"] == "hbm" else fp32_source)}
     if "issue" in d:
         line["roofline"]["issue_slot_frac"] = d["issue"]["frac"]
