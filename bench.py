@@ -628,7 +628,7 @@ def main():
     line["roofline"] = {"kernel": dom, "bound": d["bound"], "achieved": d["achieved"],
                         "peak": hbm_peak if d["bound"] == "hbm" else fp32_peak, "unit": d["unit"], "frac": d["frac"],
                         "traffic": NCU_TRAFFIC_BYTES.get(dom), "ms": d["ms"],
-                        "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full, "
+                        "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full, " +
                                           NCU_SOURCE + " (same workload)",
                         "peak_source": (f"{peak_kind} HBM copy" if d["bound"] == "hbm" else fp32_source)}
     if "issue" in d:
