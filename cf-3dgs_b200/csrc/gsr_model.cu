@@ -51,19 +51,22 @@ __global__ void gaussian_activate_kernel(int P, const float* __restrict__ opacit
     reinterpret_cast<float4*>(rot)[i] = make_float4(q.x / n, q.y / n, q.z / n, q.w / n);
 }
 
-// One thread per SH float of the rows [first, first + n / floats_per_gaussian).  The gradient may be packed to its
-// first grad_floats floats per Gaussian (the active bands): the rest of a row then has gradient zero, which still
-// decays its moments and moves the parameter by whatever the moments hold, exactly like torch.optim.Adam on a zero grad.
-__global__ void adam_features_kernel(size_t first, size_t n, int floats_per_gaussian, int grad_floats, float* __restrict__ p,
-                                     const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v, float lr_dc,
-                                     float lr_rest, AdamCfg c, const float* __restrict__ bias_dev)
+// One thread per SH float of the first upd_floats floats of the rows [row0, row0 + n / upd_floats).  The gradient may
+// be packed to its first grad_floats floats per Gaussian (the active bands): floats between grad_floats and upd_floats
+// have gradient zero, which still decays their moments and moves the parameter by whatever the moments hold, exactly
+// like torch.optim.Adam on a zero grad.  Floats from upd_floats on are not touched at all: the caller guarantees that
+// they never had a non-zero gradient, so their moments are zero and Adam's update of them is exactly zero.
+__global__ void adam_features_kernel(size_t row0, size_t n, int floats_per_gaussian, int grad_floats, int upd_floats,
+                                     float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
+                                     float* __restrict__ v, float lr_dc, float lr_rest, AdamCfg c,
+                                     const float* __restrict__ bias_dev)
 {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    i += first;
     if (bias_dev) { c.inv_bias1 = bias_dev[0]; c.inv_sqrt_bias2 = bias_dev[1]; }
-    const size_t row = i / (size_t)floats_per_gaussian;
-    const int k = (int)(i - row * (size_t)floats_per_gaussian);
+    const size_t row = row0 + i / (size_t)upd_floats;
+    const int k = (int)(i % (size_t)upd_floats);
+    i = row * (size_t)floats_per_gaussian + k;
     const float gi = k < grad_floats ? g[row * (size_t)grad_floats + k] : 0.f;
     float mm = m[i], vv = v[i];
     p[i] = adam_update(p[i], gi, mm, vv, k < 3 ? lr_dc : lr_rest, c);
@@ -177,7 +180,7 @@ __global__ void adam_tick_kernel(long long* step_state, float b1, float b2)
 
 // what: bit 0 = the per-Gaussian block (xyz, opacity, scale, rotation, statistics), bit 1 = SH rows [row0, row0 + rows).
 // tick: advance the device-side step counter first (once per optimiser step).
-static int adam_step_impl(int P, int M, int M_grad, int what, int row0, int rows, int tick, int step, long long* step_state,
+static int adam_step_impl(int P, int M, int M_grad, int M_upd, int what, int row0, int rows, int tick, int step, long long* step_state,
                           float beta1, float beta2, float eps,
                           const float* lrs_host, float* xyz, float* features, float* opacity_raw, float* log_scale,
                           float* rot_raw, const float* d_xyz, const float* d_features, const float* d_opacity,
@@ -186,8 +189,8 @@ static int adam_step_impl(int P, int M, int M_grad, int what, int row0, int rows
 {
     cudaStream_t s = (cudaStream_t)stream;
     if (P < 0 || M < 0 || (!step_state && step < 1) || !lrs_host) { set_last_error("gsr_gaussian_adam_step: bad argument"); return GSR_ERR_INVALID; }
-    if (M_grad < 0 || M_grad > M || row0 < 0 || rows < 0 || (long long)row0 + rows > P) {
-        set_last_error("gsr_gaussian_adam_step: M_grad / row range out of bounds");
+    if (M_grad < 0 || M_grad > M || M_upd < 0 || M_upd > M || row0 < 0 || rows < 0 || (long long)row0 + rows > P) {
+        set_last_error("gsr_gaussian_adam_step: M_grad <= M, M_upd <= M and the row range must lie inside P");
         return GSR_ERR_INVALID;
     }
     if (P == 0) return GSR_OK;
@@ -230,9 +233,9 @@ static int adam_step_impl(int P, int M, int M_grad, int what, int row0, int rows
     a.d_means2D = d_means2D; a.radii = radii; a.grad_accum = (d_means2D && radii && denom) ? grad_accum : nullptr;
     a.denom = denom; a.max_radii2D = max_radii2D;
     if (what & 1) adam_gaussians_kernel<<<div_up(P, 256), 256, 0, s>>>(a, c, bias_dev);
-    if ((what & 2) && M > 0 && rows > 0) {
-        const size_t nf = (size_t)3 * M * (size_t)rows;
-        adam_features_kernel<<<(unsigned)((nf + 255) / 256), 256, 0, s>>>((size_t)3 * M * (size_t)row0, nf, 3 * M, 3 * M_grad,
+    if ((what & 2) && M_upd > 0 && rows > 0) {
+        const size_t nf = (size_t)3 * M_upd * (size_t)rows;
+        adam_features_kernel<<<(unsigned)((nf + 255) / 256), 256, 0, s>>>((size_t)row0, nf, 3 * M, 3 * M_grad, 3 * M_upd,
                                                                       features, d_features, m_f, v_f, lrs_host[1],
                                                                       lrs_host[2], c, bias_dev);
     }
@@ -247,7 +250,7 @@ extern "C" int gsr_gaussian_adam_step(int P, int M, int step, float beta1, float
                                       const float* d_scale, const float* d_rot, float* state, const float* d_means2D,
                                       const int* radii, float* grad_accum, float* denom, float* max_radii2D, void* stream)
 {
-    return adam_step_impl(P, M, M, 3, 0, P, 1, step, nullptr, beta1, beta2, eps, lrs_host, xyz, features, opacity_raw, log_scale, rot_raw,
+    return adam_step_impl(P, M, M, M, 3, 0, P, 1, step, nullptr, beta1, beta2, eps, lrs_host, xyz, features, opacity_raw, log_scale, rot_raw,
                           d_xyz, d_features, d_opacity, d_scale, d_rot, state, d_means2D, radii, grad_accum, denom,
                           max_radii2D, stream);
 }
@@ -260,12 +263,12 @@ extern "C" int gsr_gaussian_adam_step_dev(int P, int M, int64_t* step_state, flo
                                           float* max_radii2D, void* stream)
 {
     if (!step_state) { set_last_error("gsr_gaussian_adam_step_dev: step_state is NULL"); return GSR_ERR_INVALID; }
-    return adam_step_impl(P, M, M, 3, 0, P, 1, 0, reinterpret_cast<long long*>(step_state), beta1, beta2, eps, lrs_host, xyz, features,
+    return adam_step_impl(P, M, M, M, 3, 0, P, 1, 0, reinterpret_cast<long long*>(step_state), beta1, beta2, eps, lrs_host, xyz, features,
                           opacity_raw, log_scale, rot_raw, d_xyz, d_features, d_opacity, d_scale, d_rot, state, d_means2D,
                           radii, grad_accum, denom, max_radii2D, stream);
 }
 
-extern "C" int gsr_gaussian_adam_step_part(int P, int M, int M_grad, int what, int row0, int rows, int tick,
+extern "C" int gsr_gaussian_adam_step_part(int P, int M, int M_grad, int M_upd, int what, int row0, int rows, int tick,
                                            int64_t* step_state, float beta1, float beta2, float eps, const float* lrs_host,
                                            float* xyz, float* features, float* opacity_raw, float* log_scale, float* rot_raw,
                                            const float* d_xyz, const float* d_features, const float* d_opacity,
@@ -274,7 +277,7 @@ extern "C" int gsr_gaussian_adam_step_part(int P, int M, int M_grad, int what, i
                                            void* stream)
 {
     if (!step_state) { set_last_error("gsr_gaussian_adam_step_part: step_state is NULL"); return GSR_ERR_INVALID; }
-    return adam_step_impl(P, M, M_grad, what, row0, rows, tick, 0, reinterpret_cast<long long*>(step_state), beta1, beta2, eps,
+    return adam_step_impl(P, M, M_grad, M_upd, what, row0, rows, tick, 0, reinterpret_cast<long long*>(step_state), beta1, beta2, eps,
                           lrs_host, xyz, features, opacity_raw, log_scale, rot_raw, d_xyz, d_features, d_opacity, d_scale,
                           d_rot, state, d_means2D, radii, grad_accum, denom, max_radii2D, stream);
 }

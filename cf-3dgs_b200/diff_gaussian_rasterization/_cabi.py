@@ -49,7 +49,7 @@ SIGNATURES = {
                                        _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "gsr_gaussian_adam_step_dev": (c_int, [c_int, c_int, _P, c_float, c_float, c_float, _P, _P, _P, _P, _P, _P, _P, _P, _P,
                                            _P, _P, _P, _P, _P, _P, _P, _P, _P]),
-    "gsr_gaussian_adam_step_part": (c_int, [c_int, c_int, c_int, c_int, c_int, c_int, c_int, _P, c_float, c_float, c_float,
+    "gsr_gaussian_adam_step_part": (c_int, [c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, _P, c_float, c_float, c_float,
                                             _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "gsr_mark_visible": (c_int, [c_int, _P, _P, _P, _P, _P]),
     "gsr_debug_dump": (c_int, [c_int, c_int, c_int, c_int64, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),

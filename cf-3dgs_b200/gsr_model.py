@@ -38,6 +38,9 @@ class FusedGaussianModel:
         # device_step: the step number lives in device memory (gsr_gaussian_adam_step_dev), so step() can be captured in
         # a CUDA graph and replayed; step_count on the host is then only a call counter
         self.step_state = torch.zeros(2, dtype=torch.int64, device=dev) if device_step else None
+        # SH bands that have ever received a gradient (as a coefficient count): the bands above it still have zero moments,
+        # so Adam's update of them is exactly zero and the step skips them (at degree 0: 3 of 48 floats per Gaussian)
+        self.sh_ever = 0
 
     def activated(self) -> Dict[str, torch.Tensor]:
         """opacities (P,1), scales (P,3), rotations (P,4) for the rasterizer (fresh tensors, no autograd history)."""
@@ -52,8 +55,17 @@ class FusedGaussianModel:
         return dict(opacities=opa, scales=sc, rotations=rot)
 
     def step(self, d_xyz, d_features, d_opacities, d_scales, d_rotations, d_means2D: Optional[torch.Tensor] = None,
-             radii: Optional[torch.Tensor] = None) -> None:
-        """One optimiser step from the gradients the rasterizer backward produced (w.r.t. the activated tensors)."""
+             radii: Optional[torch.Tensor] = None, sh_degree: Optional[int] = None) -> None:
+        """One optimiser step from the gradients the rasterizer backward produced (w.r.t. the activated tensors).
+        sh_degree (needs device_step=True): the active SH degree the gradient was produced at -- the coefficients of higher
+        bands have gradient zero; as long as they never had another, their moments are zero and they are skipped."""
+        if sh_degree is not None and self.step_state is not None and d_features is not None:
+            grads = dict(means3D=d_xyz.contiguous(), sh=d_features.contiguous(), opacity=d_opacities.contiguous(),
+                         scales=d_scales.contiguous(), rotations=d_rotations.contiguous())
+            self.step_part(3, grads, d_features.shape[1], tick=True, d_means2D=d_means2D, radii=radii,
+                           active=(int(sh_degree) + 1) ** 2)
+            return
+        self.sh_ever = self.M
         self.step_count += 1
         lr = (ctypes.c_float * 6)(*[float(self.lrs[k]) for k in LR_ORDER])
         stats = d_means2D is not None and radii is not None
@@ -72,20 +84,24 @@ class FusedGaussianModel:
                                                  float(self.betas[1]), float(self.eps), lr, *tail))
 
     def step_part(self, what: int, grads: Dict[str, torch.Tensor], M_grad: int, row0: int = 0, rows: Optional[int] = None,
-                  tick: bool = False, d_means2D: Optional[torch.Tensor] = None, radii: Optional[torch.Tensor] = None) -> None:
+                  tick: bool = False, d_means2D: Optional[torch.Tensor] = None, radii: Optional[torch.Tensor] = None,
+                  active: Optional[int] = None) -> None:
         """A part of one optimiser step (gsr_gaussian_adam_step_part): what & 1 = the per-Gaussian block, what & 2 = the
         SH rows [row0, row0 + rows).  grads: "means3D" (P,3), "sh" (P,M_grad,3), "opacity" (P,1), "scales" (P,3),
         "rotations" (P,4) -- typically views into one flat, all-reduced buffer.  Needs device_step=True."""
         if self.step_state is None:
             raise RuntimeError("step_part needs device_step=True (the step counter lives on the device)")
         rows = self.P if rows is None else rows
+        # active: coefficients that can hold a non-zero gradient in this step (default: all M_grad of them)
+        self.sh_ever = max(self.sh_ever, min(int(M_grad), self.M) if active is None else min(int(active), self.M))
         if tick:
             self.step_count += 1
         lr = (ctypes.c_float * 6)(*[float(self.lrs[k]) for k in LR_ORDER])
         stats = bool(what & 1) and d_means2D is not None and radii is not None
         with torch.cuda.device(self.xyz.device):
             check(lib.gsr_gaussian_adam_step_part(
-                self.P, self.M, int(M_grad), int(what), int(row0), int(rows), int(bool(tick)), self.step_state.data_ptr(),
+                self.P, self.M, int(M_grad), int(self.sh_ever), int(what), int(row0), int(rows), int(bool(tick)),
+                self.step_state.data_ptr(),
                 float(self.betas[0]), float(self.betas[1]), float(self.eps), lr,
                 self.xyz.data_ptr(), self.features.data_ptr(), self.opacity_raw.data_ptr(), self.log_scales.data_ptr(),
                 self.rot_raw.data_ptr(), grads["means3D"].data_ptr(), grads["sh"].data_ptr(), grads["opacity"].data_ptr(),

@@ -11,7 +11,7 @@ never split ("replicas only" inside a view); across the optimisation:
 """
 from __future__ import annotations
 
-from typing import Dict, List, Sequence
+from typing import Dict, List, Optional, Sequence
 
 import torch
 import torch.distributed as dist
@@ -83,30 +83,54 @@ def assert_replicas_identical(tensors: Sequence[torch.Tensor]) -> bool:
 class BatchedViewsStep:
     """One optimiser step of the batched-global-views form: every rank holds a replica of the
     global Gaussian model (gsr_model.FusedGaussianModel, device_step=True), renders ITS view, and the gradients of all
-    views are summed before the identical Adam step on every rank.
+    views are summed before the same Adam step reaches every replica.
 
     * the rasterizer backward writes its gradients straight into slices of one flat buffer (no packing copies);
     * only the active SH bands travel (the packed gradient, dsh_M = (degree+1)^2): 14 floats per Gaussian at degree 0
       instead of 59;
-    * the buffer is all-reduced in pieces -- geometry block, then SH row ranges -- on NCCL's own stream, and the model
-      step for a piece starts when that piece has arrived, so the optimiser overlaps the rest of the collective;
+    * collectives run on NCCL's own stream; the compute stream waits for each result where it needs it, the host never;
+    * small SH block (degrees 0 and 1): ONE all-reduce of the whole buffer, then the model step.  Measured on 8 B200s,
+      NCCL 2.28 with NVLS: all-reduces below ~100 MB run at ~400 GB/s bus bandwidth and cost 0.2 ms whatever their
+      size, above it ~650 GB/s -- cutting a buffer into pieces only multiplies the fixed part;
+    * large SH block (degrees 2 and 3: 4/5 of the bytes): all-reduce of the 11-float geometry block, and for the SH rows
+      reduce-scatter -> Adam on this rank's 1/N of the rows -> all-gather of the updated coefficients.  Same bytes on the
+      wire as an all-reduce, but the SH part of the optimiser (the larger part) runs on 1/N of the rows instead of being
+      repeated on every rank, and the geometry part of the step overlaps the reduce-scatter;
     * the densification statistics are per view and stay local (sum / sum / max over ranks when they are read:
       allreduce_densify_stats).
-    The sum over views is not divided by the number of ranks: Adam's update is invariant to the gradient's scale (up to
-    eps = 1e-15).  With world size 1 the same code runs without a collective."""
+    Every row is updated from the same reduced gradient on exactly one rank (SH) or identically on all (geometry), so the
+    replicas stay bit-identical (assert_replicas_identical).  The sum over views is not divided by the number of ranks:
+    Adam's update is invariant to the gradient's scale (up to eps = 1e-15).  With world size 1 the same code runs without
+    a collective."""
 
-    def __init__(self, model, sh_chunks: int = 4):
+    SHARD_FROM_M = 9       # SH coefficient count from which the SH rows are reduce-scattered / all-gathered
+
+    def __init__(self, model, shard_features: Optional[bool] = None):
         self.model = model
-        self.sh_chunks = sh_chunks
-        self._flat = None
+        self.world = dist.get_world_size() if dist.is_initialized() else 1
+        self.rank = dist.get_rank() if dist.is_initialized() else 0
+        self.shard_features = shard_features
         self._key = None
+        m = model
+        # rows padded to a multiple of the world size so that the SH rows split evenly; the model's coefficient tensor
+        # becomes a view of the padded storage (the all-gather writes straight into it)
+        self.rows_per = -(-m.P // self.world)
+        self.P_pad = self.rows_per * self.world
+        if self.world > 1 and m.features.untyped_storage().nbytes() < self.P_pad * m.M * 3 * 4:
+            store = torch.zeros((self.P_pad, m.M, 3), dtype=torch.float32, device=m.xyz.device)
+            store[:m.P].copy_(m.features)
+            m.features = store[:m.P]
+            self._feat_store = store
+        else:
+            self._feat_store = None
 
     def buffers(self, M_grad: int):
         m = self.model
         key = (m.P, M_grad)
         if self._key != key:
             lay = flat_layout(m.P, M_grad)
-            flat = torch.empty(lay["_total_floats"][0], dtype=torch.float32, device=m.xyz.device)
+            sh_off = lay["sh"][0]
+            flat = torch.zeros(sh_off + self.P_pad * M_grad * 3, dtype=torch.float32, device=m.xyz.device)
             views = {}
             for name in ("rotations", "means3D", "opacity", "scales", "sh"):
                 off, shape = lay[name]
@@ -115,8 +139,9 @@ class BatchedViewsStep:
                     n *= d
                 views[name] = flat[off:off + n].view(shape)
             self._flat, self._views, self._key = flat, views, key
+            self._sh_pad = flat[sh_off:]                                     # (P_pad * 3 M_grad) floats, pad rows stay zero
+            self._used = lay["_total_floats"][0]
             self._m2d = torch.empty((m.P, 3), dtype=torch.float32, device=m.xyz.device)
-            self._pieces = comm_pieces(m.P, M_grad, self.sh_chunks)
         return self._flat, self._views
 
     def __call__(self, settings, target, loss_fn, window=None):
@@ -140,18 +165,28 @@ class BatchedViewsStep:
                          binning, img, alpha, False,
                          out=dict(means3D=g["means3D"], means2D=self._m2d, opacity=g["opacity"], sh=g["sh"],
                                   scales=g["scales"], rotations=g["rotations"]), dsh_M=M_grad)
-        multi = dist.is_initialized() and dist.get_world_size() > 1
-        works = []
-        if multi:
-            for off, n, _, _, _ in self._pieces:
-                works.append(dist.all_reduce(flat[off:off + n], async_op=True))
-        first = True
-        for i, (off, n, what, row0, rows) in enumerate(self._pieces):
+        multi = self.world > 1
+        shard = multi and (self.shard_features if self.shard_features is not None else M_grad >= self.SHARD_FROM_M) \
+            and self._feat_store is not None
+        if not shard:
             if multi:
-                works[i].wait()        # the compute stream waits for this piece; the host does not
-            m.step_part(what, g, M_grad, row0=row0, rows=rows, tick=first,
-                        d_means2D=self._m2d if what & 1 else None, radii=radii if what & 1 else None)
-            first = False
+                dist.all_reduce(flat[:self._used])          # stream-ordered: the step below waits on the device, not the host
+            m.step_part(3, g, M_grad, tick=True, d_means2D=self._m2d, radii=radii)
+            return loss.detach()
+        n_own = self.rows_per * 3 * M_grad
+        own_grad = self._sh_pad[self.rank * n_own:(self.rank + 1) * n_own]
+        w_geo = dist.all_reduce(flat[:11 * m.P], async_op=True)
+        w_rs = dist.reduce_scatter_tensor(own_grad, self._sh_pad, async_op=True)       # in place: my rows of the summed SH gradient
+        w_geo.wait()
+        m.step_part(1, g, M_grad, tick=True, d_means2D=self._m2d, radii=radii)        # overlaps the reduce-scatter
+        w_rs.wait()
+        row0 = self.rank * self.rows_per
+        rows = max(0, min(self.rows_per, m.P - row0))
+        if rows:
+            m.step_part(2, g, M_grad, row0=row0, rows=rows)
+        store = self._feat_store.view(-1)
+        n_feat = self.rows_per * m.M * 3
+        dist.all_gather_into_tensor(store, store[self.rank * n_feat:(self.rank + 1) * n_feat])   # everyone's updated rows
         return loss.detach()
 
 

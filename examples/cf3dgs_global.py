@@ -14,8 +14,8 @@ Single GPU:
   python examples/cf3dgs_global.py [--frames 120] [--points-per-frame 8700] [--iters 600] [--impl ours|reference]
                                    [--graph] [--densify-every 100] [--psnr-every 100]
 Batched global views over N GPUs: every rank holds a replica of the model and renders a different
-training view per step; the gradients are written straight into one flat buffer, all-reduced over NCCL in pieces
-(only the active SH bands travel) and the model step for a piece runs while the next piece is on the wire:
+training view per step; the gradients are written straight into one flat buffer and summed over NCCL (only the active SH
+bands travel; at SH degree 2 and 3 the SH rows are reduce-scattered, stepped on 1/N of the rows per rank and all-gathered):
   python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 examples/cf3dgs_global.py --batched ...
 Prints one JSON line (rank 0).
 """
@@ -54,7 +54,7 @@ def frame_pose(i, n):
 
 def default_config(**kw):
     cfg = dict(frames=8, points_per_frame=130_000, iters=200, width=960, height=540, sh_degree=3, impl="ours", loss=None,
-               model=None, graph=False, batched=False, densify_every=0, psnr_every=0, sh_chunks=4, profile=False, warmup=10)
+               model=None, graph=False, batched=False, densify_every=0, psnr_every=0, profile=False, warmup=10)
     cfg.update(kw)
     if cfg["model"] is None:
         cfg["model"] = "fused" if cfg["impl"] == "ours" else "torch"
@@ -135,7 +135,7 @@ def run_global(args, dev, rank=0, world=1):
         if fused:
             import gsr_model
             m = gsr_model.FusedGaussianModel(r["xyz"], r["features"], r["opacity_raw"], r["log_scales"], r["rot_raw"], LRS,
-                                             device_step=bool(args.graph or args.batched))
+                                             device_step=True)
             return m
         p = {k: v.clone().requires_grad_(True) for k, v in r.items() if k != "features"}
         p["f_dc"] = r["features"][:, :1].clone().requires_grad_(True)
@@ -170,7 +170,7 @@ def run_global(args, dev, rank=0, world=1):
         img, radii, _, _ = D.GaussianRasterizer(rs)(x, m2d, o, shs=sh, scales=sc, rotations=r)
         loss = loss_fn(img, target, window)
         loss.backward()
-        m.step(x.grad, sh.grad, o.grad, sc.grad, r.grad, d_means2D=m2d.grad, radii=radii)
+        m.step(x.grad, sh.grad, o.grad, sc.grad, r.grad, d_means2D=m2d.grad, radii=radii, sh_degree=int(rs.sh_degree))
         return loss
 
     def torch_iteration_frame(rs, target):
@@ -189,7 +189,7 @@ def run_global(args, dev, rank=0, world=1):
         opt.step(); opt.zero_grad(set_to_none=True)
         return loss
 
-    batched = GPar.BatchedViewsStep(model, sh_chunks=args.sh_chunks) if args.batched else None
+    batched = GPar.BatchedViewsStep(model) if args.batched else None
 
     def view_of(k):
         return int(order[k * world + rank]) if args.batched else int(order[k])
@@ -266,7 +266,7 @@ def run_global(args, dev, rank=0, world=1):
         new = _densify_stand_in({k: v.detach() for k, v in r.items()}, accum, denom, round_index)
         model = build_model(new)
         if args.batched:
-            batched = GPar.BatchedViewsStep(model, sh_chunks=args.sh_chunks)
+            batched = GPar.BatchedViewsStep(model)
         state["P"] = new["xyz"].shape[0]
         state["P_history"].append(state["P"])
         state["densify_rounds"] += 1
@@ -325,8 +325,7 @@ def run_global(args, dev, rank=0, world=1):
     identical = None
     if args.batched:
         r = raw_of(model)
-        identical = GPar.assert_replicas_identical([r["xyz"], r["features"], r["opacity_raw"], r["log_scales"], r["rot_raw"],
-                                                    model.state])
+        identical = GPar.assert_replicas_identical([r["xyz"], r["features"], r["opacity_raw"], r["log_scales"], r["rot_raw"]])
         if world > 1:
             tmax = torch.tensor([dt], device=dev)
             dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
@@ -340,7 +339,7 @@ def run_global(args, dev, rank=0, world=1):
         line["views_per_s"] = world * args.iters / dt
         line["allreduce_floats_per_gaussian"] = 11 + 3 * (deg + 1) * (deg + 1)
         line["allreduce_bytes"] = 4 * (11 + 3 * (deg + 1) * (deg + 1)) * state["P"]
-        line["sh_chunks"] = args.sh_chunks
+        line["sh_rows_sharded"] = bool(world > 1 and (deg + 1) * (deg + 1) >= GPar.BatchedViewsStep.SHARD_FROM_M)
         line["replicas_bit_identical"] = identical
     if args.densify_every:
         line["densify_every"] = args.densify_every
@@ -373,7 +372,6 @@ def main():
     ap.add_argument("--model", default=None, choices=["fused", "torch"],
                     help="fused activation/Adam/statistics kernels (default for ours) or torch.optim.Adam + autograd")
     ap.add_argument("--batched", action="store_true", help="batched global views: one view per rank per step, NCCL all-reduce")
-    ap.add_argument("--sh-chunks", type=int, default=4, help="row ranges the SH gradient is all-reduced in (--batched)")
     ap.add_argument("--densify-every", type=int, default=0, help="change the Gaussian count every N iterations (0 = never)")
     ap.add_argument("--psnr-every", type=int, default=0, help="record the PSNR over 4 fixed views every N iterations")
     ap.add_argument("--c3", action="store_true", help="BASELINE configs[2] at its stated shape: 120 frames, ~1M Gaussians, "

@@ -118,7 +118,7 @@ def run_pair(p, args, dev, backend):
         fused_model = gsr_model.FusedGaussianModel(
             xyz, torch.cat([f_dc, f_rest], 1), opa_raw, log_s, rot,
             dict(xyz=0.0, f_dc=0.0025, f_rest=0.000125, opacity=0.05, scaling=0.005, rotation=0.001),
-            device_step=bool(args.graph))
+            device_step=True)
 
         def fit_iteration_fused():
             mdl = fused_model
@@ -130,7 +130,7 @@ def run_pair(p, args, dev, backend):
             img = D.GaussianRasterizer(rs)(x, m2d, o, shs=sh, scales=sc_, rotations=r)[0]
             loss = loss_fn(img, frame0, window)
             loss.backward()
-            mdl.step(x.grad, sh.grad, o.grad, sc_.grad, r.grad)
+            mdl.step(x.grad, sh.grad, o.grad, sc_.grad, r.grad, sh_degree=0)
             return loss
 
     if fused_model is not None and args.graph:

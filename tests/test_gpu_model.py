@@ -89,3 +89,27 @@ def test_device_side_step_counter_matches_the_host_one_and_replays_in_a_graph():
         a, b, c = getattr(host, name), getattr(dev_eager, name), getattr(dev_graph, name)
         assert torch.equal(a, b), name
         assert torch.equal(a, c), name
+
+
+def test_skipping_never_active_sh_bands_changes_nothing():
+    """step(..., sh_degree=d) leaves the coefficients of bands that never had a gradient alone; the result is bit-identical
+    to the full step on the same (zero above the active bands) gradient, also after the degree has grown."""
+    import gsr_model
+    P, M = 3001, 16
+    g = torch.Generator().manual_seed(6)
+    init = [torch.randn(P, 3, generator=g), torch.randn(P, M, 3, generator=g) * 0.2, torch.randn(P, 1, generator=g),
+            torch.randn(P, 3, generator=g) * 0.3 - 3, torch.randn(P, 4, generator=g)]
+    full = gsr_model.FusedGaussianModel(*[t.to(DEV) for t in init], LRS, device_step=True)
+    lean = gsr_model.FusedGaussianModel(*[t.to(DEV) for t in init], LRS, device_step=True)
+    for it, deg in enumerate([0, 0, 1, 1, 0, 3]):
+        n = (deg + 1) ** 2
+        d_f = torch.zeros(P, M, 3, device=DEV)
+        d_f[:, :n] = (torch.randn(P, n, 3, generator=g) * 0.1).to(DEV)
+        rest = [torch.randn(P, 3, generator=g).to(DEV), torch.randn(P, 1, generator=g).to(DEV),
+                torch.randn(P, 3, generator=g).to(DEV), torch.randn(P, 4, generator=g).to(DEV)]
+        full.step(rest[0], d_f, rest[1], rest[2], rest[3])
+        lean.step(rest[0], d_f, rest[1], rest[2], rest[3], sh_degree=deg)
+        assert lean.sh_ever == max((d + 1) ** 2 for d in [0, 0, 1, 1, 0, 3][:it + 1])
+    torch.cuda.synchronize()
+    for name in ["xyz", "features", "opacity_raw", "log_scales", "rot_raw", "state"]:
+        assert torch.equal(getattr(full, name), getattr(lean, name)), name

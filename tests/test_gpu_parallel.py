@@ -96,7 +96,7 @@ def test_batched_views_step_on_one_rank_matches_the_autograd_iteration():
         mk = lambda: gsr_model.FusedGaussianModel(t["means3D"], t["shs"], torch.logit(t["opacities"].clamp(1e-3, 1 - 1e-3)),
                                                   t["scales"].log(), t["rotations"], LRS, device_step=True)
         a, b = mk(), mk()
-        step = GP.BatchedViewsStep(a, sh_chunks=3)
+        step = GP.BatchedViewsStep(a)
         for it in range(3):
             la = step(rs, target, loss_fn)
             act = b.activated()
