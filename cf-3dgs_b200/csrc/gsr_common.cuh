@@ -17,6 +17,8 @@ constexpr int SORT_THREADS = 256;
 #endif
 constexpr int SORT_ITEMS = GSR_SORT_ITEMS;              // items per thread
 constexpr int SORT_CHUNK = SORT_THREADS * SORT_ITEMS;  // items per block
+constexpr int SCAN_ITEMS = 8;                           // depth ranks per thread of the instance-count sums kernel
+constexpr int SCAN_CHUNK = SORT_THREADS * SCAN_ITEMS;  // = 8 emit blocks of 256 ranks
 constexpr int RADIX_BITS = 8;
 constexpr int RADIX = 1 << RADIX_BITS;
 constexpr int SORT_MAX_PASSES = 4;
@@ -83,7 +85,7 @@ inline size_t geom_layout(char* base, int P, GeomView& g)
     carve(p, g.offsets, n);
     carve(p, g.hist, (size_t)RADIX * nblk);
     carve(p, g.digit_total, SORT_AUX_WORDS);
-    carve(p, g.block_sums, nblk + 1);
+    carve(p, g.block_sums, (size_t)div_up(P, SCAN_CHUNK) + 1);
     carve(p, g.counters, 4);
     return (size_t)(p - base) + 256;
 }

@@ -315,19 +315,19 @@ void launch_init_sort_input(const GeomView& g, int P, cudaStream_t s)
 // per warp of this kernel = one per block of the emit kernel).  The emit kernel adds up the sums in front of its
 // 256 ranks itself and scans its own ranks in shared memory, so no per-rank offset array is written or read and the
 // second scan kernel is gone.
-static_assert(SORT_ITEMS * 32 == 256, "one warp of the sums kernel covers the 256 ranks of one emit block");
+static_assert(SCAN_ITEMS * 32 == 256, "one warp of the sums kernel covers the 256 ranks of one emit block");
 
 __global__ void __launch_bounds__(SORT_THREADS)
 scan_block_sums_kernel(const uint32_t* __restrict__ tiles, const uint32_t* __restrict__ order, int P,
                        uint32_t* __restrict__ block_sums, uint32_t* __restrict__ group_sums)
 {
     __shared__ uint32_t warp_sums[8];
-    const int base = blockIdx.x * SORT_CHUNK + threadIdx.x * SORT_ITEMS;
+    const int base = blockIdx.x * SCAN_CHUNK + threadIdx.x * SCAN_ITEMS;
     uint32_t sum = 0;
     pdl_wait();
     pdl_trigger();
 #pragma unroll
-    for (int i = 0; i < SORT_ITEMS; i++)
+    for (int i = 0; i < SCAN_ITEMS; i++)
         if (base + i < P) sum += tiles[order[base + i]];
     uint32_t wsum = sum;
 #pragma unroll
@@ -348,7 +348,7 @@ scan_block_sums_kernel(const uint32_t* __restrict__ tiles, const uint32_t* __res
 void launch_offsets_scan(const uint32_t* tiles, const uint32_t* order, uint32_t* group_sums, uint32_t* block_sums,
                          int P, cudaStream_t s)
 {
-    const int nblk = div_up(P, SORT_CHUNK);
+    const int nblk = div_up(P, SCAN_CHUNK);
     launch_pdl(scan_block_sums_kernel, nblk, SORT_THREADS, 0, s, tiles, order, P, block_sums, group_sums);
 }
 
