@@ -56,7 +56,7 @@ def test_size_queries_need_no_gpu():
     assert 0 < g1 < g2
     assert lib.gsr_image_bytes(640, 360) >= 640 * 360 * 4 + 40 * 23 * 8
     assert lib.gsr_binning_bytes(1000, 640, 360) >= 16 * 1000
-    assert lib.gsr_profile_count() == 10
+    assert lib.gsr_profile_count() == 9      # stages with a timer (the tile ranges come out of the tile sort)
     assert lib.gsr_profile_name(0) == b"preprocess"
 
 
