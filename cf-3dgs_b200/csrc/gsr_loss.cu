@@ -7,21 +7,26 @@
 //
 // forward : per pixel  mu1, mu2, E[x^2], E[y^2], E[xy]  ->  SSIM value and the three maps the backward needs
 //             A = dS/dmu1 (total, through sigma1^2 and sigma12 as well),  B = dS/dsigma1^2,  C = dS/dsigma12
-//           block sums of |x - gt| and SSIM -> two double accumulators
+//           block sums of |x - gt| and SSIM -> one slot per block, added up in a fixed order by a small second kernel
 // backward: dL/dx(p) = gL * [ (1-lambda)/N * sign(x-gt)  -  lambda/N * ( G*A + 2 x G*B + gt G*C )(p) ] * clamp mask
 #include <cmath>
 
 #include "../../include/gsr.h"
+#include "gsr_f32x2.cuh"
 #include "gsr_kernels.h"
+#include "gsr_launch.cuh"
 
 namespace gsr {
 void set_last_error(const char* msg);
 
 namespace {
 
-constexpr int LT = 16;            // output tile
+constexpr int TW = 32, TH = 16;                   // output tile of one block (256 threads)
 constexpr int HALO = 5;
-constexpr int LW = LT + 2 * HALO; // 26
+constexpr int IW = TW + 2 * HALO, IH = TH + 2 * HALO;   // 42 x 26 input window
+constexpr int IWP = 44;                           // row pitch of the staged inputs: 16-byte aligned rows, 2 zero pad columns
+constexpr int HP = TW + 1;                        // row pitch of the horizontally filtered planes
+constexpr int LOSS_THREADS = 256;
 // The 11-tap window of utils/loss_utils.py:21-23 -- exp(-(x-5)^2 / (2*1.5^2)) in double, stored as float32, divided by
 // its float32 sum -- as the float32 values torch produces (tests/golden/make_golden_loss.py imports that code), fixed at
 // compile time: no first-call upload, nothing to synchronise, safe inside stream capture and from any host thread.
@@ -31,72 +36,135 @@ __constant__ float c_gw[11] = {1.028380124e-03f, 7.598758209e-03f, 3.600077331e-
 
 __device__ __forceinline__ float clamp01(float v, bool on) { return on ? fminf(fmaxf(v, 0.f), 1.f) : v; }
 
-__global__ void __launch_bounds__(LT * LT)
+// Both kernels are separable 11-tap convolutions over a 32 x 16 tile, written so that a value fetched from shared
+// memory is used for several outputs (round 1 fetched every tap of every output: 380 instructions per pixel, 22 M warp
+// instructions for a 960x540 image, 38 us -- instruction-bound, not bandwidth-bound):
+//   horizontal pass: one thread per (row, group of 4 output columns): 16 staged values -> 4 outputs x 11 taps
+//   vertical pass  : one thread per (column, pair of output rows):    12 filtered values -> 2 outputs x 11 taps
+// and the quantities ride in FP32 pairs (fma.rn.f32x2): (x, y), (x^2, y^2) and xy forward; (A, B) and C backward.
+__global__ void __launch_bounds__(LOSS_THREADS)
 photo_loss_forward_kernel(int H, int W, const float* __restrict__ img, const float* __restrict__ gt, int clamp_img,
-                          float* __restrict__ maps, double* __restrict__ sums)
+                          float* __restrict__ maps, double* __restrict__ block_sums)
 {
-    __shared__ float sx[LW][LW + 1], sy[LW][LW + 1];
-    __shared__ float hq[5][LW][LT];
-    __shared__ float red[2][LT * LT / 32];
+    __shared__ __align__(16) float sx[IH][IWP], sy[IH][IWP];
+    __shared__ float hq[5][IH][HP];
+    __shared__ float red[2][LOSS_THREADS / 32];
     const int ch = blockIdx.z;
     const size_t plane = (size_t)H * W;
+    pdl_wait();
+    pdl_trigger();
     const float* x = img + ch * plane;
     const float* y = gt + ch * plane;
-    const int x0 = blockIdx.x * LT - HALO, y0 = blockIdx.y * LT - HALO;
-    for (int i = threadIdx.x; i < LW * LW; i += LT * LT) {
-        const int r = i / LW, c = i % LW;
+    const int x0 = blockIdx.x * TW - HALO, y0 = blockIdx.y * TH - HALO;
+    for (int i = threadIdx.x; i < IH * IWP; i += LOSS_THREADS) {
+        const int r = i / IWP, c = i - r * IWP;
         const int gy = y0 + r, gx = x0 + c;
         float vx = 0.f, vy = 0.f;
-        if (gy >= 0 && gy < H && gx >= 0 && gx < W) {
+        if (c < IW && gy >= 0 && gy < H && gx >= 0 && gx < W) {
             vx = clamp01(x[(size_t)gy * W + gx], clamp_img);
             vy = y[(size_t)gy * W + gx];
         }
         sx[r][c] = vx; sy[r][c] = vy;
     }
     __syncthreads();
-    // horizontal pass: 26 rows x 16 columns, 5 quantities
-    for (int i = threadIdx.x; i < LW * LT; i += LT * LT) {
-        const int r = i / LT, c = i % LT;
-        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, a4 = 0.f;
+    // horizontal pass: 26 rows x 8 groups of 4 columns
+    if (threadIdx.x < IH * (TW / 4)) {
+        const int r = threadIdx.x / (TW / 4), c0 = (threadIdx.x % (TW / 4)) * 4;
+        // input-stationary: each staged value is turned into its products once and added into the (up to four) outputs
+        // whose window holds it; per output the taps still arrive in ascending order
+        f32x2 a1[4], a2[4];
+        float a3[4];
 #pragma unroll
-        for (int k = 0; k < 11; k++) {
-            const float w = c_gw[k], vx = sx[r][c + k], vy = sy[r][c + k];
-            a0 += w * vx; a1 += w * vy; a2 += w * vx * vx; a3 += w * vy * vy; a4 += w * vx * vy;
+        for (int o = 0; o < 4; o++) { a1[o] = bc(0.f); a2[o] = bc(0.f); a3[o] = 0.f; }
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            const float4 xa = *reinterpret_cast<const float4*>(&sx[r][c0 + 4 * q]);
+            const float4 ya = *reinterpret_cast<const float4*>(&sy[r][c0 + 4 * q]);
+            const float xs[4] = {xa.x, xa.y, xa.z, xa.w}, ys[4] = {ya.x, ya.y, ya.z, ya.w};
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+                const int k = 4 * q + e;
+                if (k < 14) {
+                    const f32x2 p1 = pk(xs[e], ys[e]);
+                    const f32x2 p2 = mul2(p1, p1);
+                    const float p3 = xs[e] * ys[e];
+#pragma unroll
+                    for (int o = 0; o < 4; o++) {
+                        const int t = k - o;
+                        if (t >= 0 && t <= 10) {
+                            a1[o] = fma2(bc(c_gw[t]), p1, a1[o]);
+                            a2[o] = fma2(bc(c_gw[t]), p2, a2[o]);
+                            a3[o] = fmaf(c_gw[t], p3, a3[o]);
+                        }
+                    }
+                }
+            }
         }
-        hq[0][r][c] = a0; hq[1][r][c] = a1; hq[2][r][c] = a2; hq[3][r][c] = a3; hq[4][r][c] = a4;
+#pragma unroll
+        for (int o = 0; o < 4; o++) {
+            float m1, m2, e11, e22;
+            unpk(a1[o], m1, m2);
+            unpk(a2[o], e11, e22);
+            hq[0][r][c0 + o] = m1; hq[1][r][c0 + o] = m2; hq[2][r][c0 + o] = e11; hq[3][r][c0 + o] = e22;
+            hq[4][r][c0 + o] = a3[o];
+        }
     }
     __syncthreads();
-    const int lx = threadIdx.x % LT, ly = threadIdx.x / LT;
-    const int px = blockIdx.x * LT + lx, py = blockIdx.y * LT + ly;
+    // vertical pass + SSIM: thread = (column, pair of rows)
+    const int lx = threadIdx.x % TW, ly0 = (threadIdx.x / TW) * 2;
+    const int px = blockIdx.x * TW + lx;
     float l1 = 0.f, ss = 0.f;
-    if (px < W && py < H) {
-        float mu1 = 0.f, mu2 = 0.f, e11 = 0.f, e22 = 0.f, e12 = 0.f;
+    {
+        f32x2 v1[2] = {bc(0.f), bc(0.f)}, v2[2] = {bc(0.f), bc(0.f)};
+        float v3[2] = {0.f, 0.f};
 #pragma unroll
-        for (int k = 0; k < 11; k++) {
-            const float w = c_gw[k];
-            mu1 += w * hq[0][ly + k][lx]; mu2 += w * hq[1][ly + k][lx]; e11 += w * hq[2][ly + k][lx];
-            e22 += w * hq[3][ly + k][lx]; e12 += w * hq[4][ly + k][lx];
+        for (int k = 0; k < 12; k++) {
+            const f32x2 p1 = pk(hq[0][ly0 + k][lx], hq[1][ly0 + k][lx]);
+            const f32x2 p2 = pk(hq[2][ly0 + k][lx], hq[3][ly0 + k][lx]);
+            const float p3 = hq[4][ly0 + k][lx];
+#pragma unroll
+            for (int o = 0; o < 2; o++) {
+                const int t = k - o;
+                if (t >= 0 && t <= 10) {
+                    v1[o] = fma2(bc(c_gw[t]), p1, v1[o]);
+                    v2[o] = fma2(bc(c_gw[t]), p2, v2[o]);
+                    v3[o] = fmaf(c_gw[t], p3, v3[o]);
+                }
+            }
         }
-        const float C1 = 0.01f * 0.01f, C2 = 0.03f * 0.03f;
-        const float mu1_sq = mu1 * mu1, mu2_sq = mu2 * mu2, mu12 = mu1 * mu2;
-        const float s1 = e11 - mu1_sq, s2 = e22 - mu2_sq, s12 = e12 - mu12;
-        const float n1 = 2.f * mu12 + C1, n2 = 2.f * s12 + C2;
-        const float d1 = mu1_sq + mu2_sq + C1, d2 = s1 + s2 + C2;
-        const float inv = 1.f / (d1 * d2);
-        const float S = n1 * n2 * inv;
-        // partials of S
-        const float dS_dmu1_direct = (2.f * mu2 * n2 * d1 - n1 * n2 * 2.f * mu1) / (d1 * d1 * d2);
-        const float dS_ds1 = -n1 * n2 / (d1 * d2 * d2);
-        const float dS_ds12 = 2.f * n1 * inv;
-        const float A = dS_dmu1_direct + dS_ds1 * (-2.f * mu1) + dS_ds12 * (-mu2);
-        const size_t o = (size_t)py * W + px;
-        maps[ch * plane + o] = A;
-        maps[((size_t)gridDim.z + ch) * plane + o] = dS_ds1;
-        maps[((size_t)2 * gridDim.z + ch) * plane + o] = dS_ds12;
-        ss = S;
-        l1 = fabsf(sx[ly + HALO][lx + HALO] - sy[ly + HALO][lx + HALO]);
+#pragma unroll
+        for (int o = 0; o < 2; o++) {
+            const int py = blockIdx.y * TH + ly0 + o;
+            const f32x2 a1 = v1[o], a2 = v2[o];
+            const float e12 = v3[o];
+            if (px < W && py < H) {
+                float mu1, mu2, e11, e22;
+                unpk(a1, mu1, mu2);
+                unpk(a2, e11, e22);
+                const float C1 = 0.01f * 0.01f, C2 = 0.03f * 0.03f;
+                const float mu1_sq = mu1 * mu1, mu2_sq = mu2 * mu2, mu12 = mu1 * mu2;
+                const float s1 = e11 - mu1_sq, s2 = e22 - mu2_sq, s12 = e12 - mu12;
+                const float n1 = 2.f * mu12 + C1, n2 = 2.f * s12 + C2;
+                const float d1 = mu1_sq + mu2_sq + C1, d2 = s1 + s2 + C2;
+                const float r1 = 1.f / d1, r2 = 1.f / d2;
+                const float inv = r1 * r2;
+                const float S = n1 * n2 * inv;
+                // partials of S:  dS/dmu1 (direct) = 2 mu2 n2 / (d1 d2) - 2 mu1 S / d1;  dS/ds1 = -S / d2;  dS/ds12 = 2 n1 / (d1 d2)
+                const float dS_dmu1_direct = 2.f * mu2 * n2 * inv - 2.f * mu1 * S * r1;
+                const float dS_ds1 = -S * r2;
+                const float dS_ds12 = 2.f * n1 * inv;
+                const float A = dS_dmu1_direct + dS_ds1 * (-2.f * mu1) + dS_ds12 * (-mu2);
+                const size_t o_ = (size_t)py * W + px;
+                maps[ch * plane + o_] = A;
+                maps[((size_t)gridDim.z + ch) * plane + o_] = dS_ds1;
+                maps[((size_t)2 * gridDim.z + ch) * plane + o_] = dS_ds12;
+                ss += S;
+                l1 += fabsf(sx[ly0 + o + HALO][lx + HALO] - sy[ly0 + o + HALO][lx + HALO]);
+            }
+        }
     }
-    // block sums -> two double atomics
+    // block sums -> this block's slot (summed in a fixed order by the finalize kernel: no atomics, no memset, the same
+    // loss bits on every run)
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
         l1 += __shfl_xor_sync(0xffffffffu, l1, o);
@@ -106,72 +174,135 @@ photo_loss_forward_kernel(int H, int W, const float* __restrict__ img, const flo
     __syncthreads();
     if (threadIdx.x == 0) {
         double a = 0.0, b = 0.0;
-        for (int w = 0; w < LT * LT / 32; w++) { a += red[0][w]; b += red[1][w]; }
-        atomicAdd(&sums[0], a);
-        atomicAdd(&sums[1], b);
+        for (int w = 0; w < LOSS_THREADS / 32; w++) { a += red[0][w]; b += red[1][w]; }
+        const size_t blk = ((size_t)blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+        block_sums[2 * blk] = a;
+        block_sums[2 * blk + 1] = b;
     }
 }
 
-__global__ void photo_loss_finalize_kernel(const double* __restrict__ sums, double n, float lambda, float* __restrict__ out)
+__global__ void __launch_bounds__(LOSS_THREADS)
+photo_loss_finalize_kernel(const double* __restrict__ block_sums, int nblk, double n, float lambda, float* __restrict__ out)
 {
-    const double l1 = sums[0] / n, ssim = sums[1] / n;
-    out[0] = (float)((1.0 - (double)lambda) * l1 + (double)lambda * (1.0 - ssim));
-    out[1] = (float)l1;
-    out[2] = (float)ssim;
+    __shared__ double red[2][LOSS_THREADS / 32];
+    pdl_wait();
+    pdl_trigger();
+    double a = 0.0, b = 0.0;
+    for (int i = threadIdx.x; i < nblk; i += LOSS_THREADS) { a += block_sums[2 * i]; b += block_sums[2 * i + 1]; }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        a += __shfl_xor_sync(0xffffffffu, a, o);
+        b += __shfl_xor_sync(0xffffffffu, b, o);
+    }
+    if ((threadIdx.x & 31) == 0) { red[0][threadIdx.x >> 5] = a; red[1][threadIdx.x >> 5] = b; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double sa = 0.0, sb = 0.0;
+        for (int w = 0; w < LOSS_THREADS / 32; w++) { sa += red[0][w]; sb += red[1][w]; }
+        const double l1 = sa / n, ssim = sb / n;
+        out[0] = (float)((1.0 - (double)lambda) * l1 + (double)lambda * (1.0 - ssim));
+        out[1] = (float)l1;
+        out[2] = (float)ssim;
+    }
 }
 
-__global__ void __launch_bounds__(LT * LT)
+__global__ void __launch_bounds__(LOSS_THREADS)
 photo_loss_backward_kernel(int H, int W, const float* __restrict__ img, const float* __restrict__ gt, int clamp_img,
                            const float* __restrict__ maps, float lambda, const float* __restrict__ grad_loss,
                            float* __restrict__ dL_dimg)
 {
-    __shared__ float sm[3][LW][LW + 1];
-    __shared__ float hq[3][LW][LT];
+    __shared__ __align__(16) float sa[IH][IWP], sb[IH][IWP], sc[IH][IWP];
+    __shared__ float hq[3][IH][HP];
     const int ch = blockIdx.z, C = gridDim.z;
     const size_t plane = (size_t)H * W;
-    const int x0 = blockIdx.x * LT - HALO, y0 = blockIdx.y * LT - HALO;
-    for (int i = threadIdx.x; i < LW * LW; i += LT * LT) {
-        const int r = i / LW, c = i % LW;
+    pdl_wait();
+    pdl_trigger();
+    const int x0 = blockIdx.x * TW - HALO, y0 = blockIdx.y * TH - HALO;
+    for (int i = threadIdx.x; i < IH * IWP; i += LOSS_THREADS) {
+        const int r = i / IWP, c = i - r * IWP;
         const int gy = y0 + r, gx = x0 + c;
         float a = 0.f, b = 0.f, cc = 0.f;
-        if (gy >= 0 && gy < H && gx >= 0 && gx < W) {
+        if (c < IW && gy >= 0 && gy < H && gx >= 0 && gx < W) {
             const size_t o = (size_t)gy * W + gx;
             a = maps[ch * plane + o];
             b = maps[((size_t)C + ch) * plane + o];
             cc = maps[((size_t)2 * C + ch) * plane + o];
         }
-        sm[0][r][c] = a; sm[1][r][c] = b; sm[2][r][c] = cc;
+        sa[r][c] = a; sb[r][c] = b; sc[r][c] = cc;
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < LW * LT; i += LT * LT) {
-        const int r = i / LT, c = i % LT;
-        float a0 = 0.f, a1 = 0.f, a2 = 0.f;
+    if (threadIdx.x < IH * (TW / 4)) {
+        const int r = threadIdx.x / (TW / 4), c0 = (threadIdx.x % (TW / 4)) * 4;
+        f32x2 a1[4];
+        float a3[4];
 #pragma unroll
-        for (int k = 0; k < 11; k++) {
-            const float w = c_gw[k];
-            a0 += w * sm[0][r][c + k]; a1 += w * sm[1][r][c + k]; a2 += w * sm[2][r][c + k];
+        for (int o = 0; o < 4; o++) { a1[o] = bc(0.f); a3[o] = 0.f; }
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            const float4 va = *reinterpret_cast<const float4*>(&sa[r][c0 + 4 * q]);
+            const float4 vb = *reinterpret_cast<const float4*>(&sb[r][c0 + 4 * q]);
+            const float4 vc = *reinterpret_cast<const float4*>(&sc[r][c0 + 4 * q]);
+            const float as[4] = {va.x, va.y, va.z, va.w}, bs[4] = {vb.x, vb.y, vb.z, vb.w}, cs[4] = {vc.x, vc.y, vc.z, vc.w};
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+                const int k = 4 * q + e;
+                if (k < 14) {
+                    const f32x2 p1 = pk(as[e], bs[e]);
+#pragma unroll
+                    for (int o = 0; o < 4; o++) {
+                        const int t = k - o;
+                        if (t >= 0 && t <= 10) {
+                            a1[o] = fma2(bc(c_gw[t]), p1, a1[o]);
+                            a3[o] = fmaf(c_gw[t], cs[e], a3[o]);
+                        }
+                    }
+                }
+            }
         }
-        hq[0][r][c] = a0; hq[1][r][c] = a1; hq[2][r][c] = a2;
+#pragma unroll
+        for (int o = 0; o < 4; o++) {
+            float ga, gb;
+            unpk(a1[o], ga, gb);
+            hq[0][r][c0 + o] = ga; hq[1][r][c0 + o] = gb; hq[2][r][c0 + o] = a3[o];
+        }
     }
     __syncthreads();
-    const int lx = threadIdx.x % LT, ly = threadIdx.x / LT;
-    const int px = blockIdx.x * LT + lx, py = blockIdx.y * LT + ly;
-    if (px < W && py < H) {
-        float ga = 0.f, gb = 0.f, gc = 0.f;
+    const int lx = threadIdx.x % TW, ly0 = (threadIdx.x / TW) * 2;
+    const int px = blockIdx.x * TW + lx;
+    f32x2 v1[2] = {bc(0.f), bc(0.f)};
+    float v3[2] = {0.f, 0.f};
 #pragma unroll
-        for (int k = 0; k < 11; k++) {
-            const float w = c_gw[k];
-            ga += w * hq[0][ly + k][lx]; gb += w * hq[1][ly + k][lx]; gc += w * hq[2][ly + k][lx];
+    for (int k = 0; k < 12; k++) {
+        const f32x2 p1 = pk(hq[0][ly0 + k][lx], hq[1][ly0 + k][lx]);
+        const float p3 = hq[2][ly0 + k][lx];
+#pragma unroll
+        for (int o = 0; o < 2; o++) {
+            const int t = k - o;
+            if (t >= 0 && t <= 10) {
+                v1[o] = fma2(bc(c_gw[t]), p1, v1[o]);
+                v3[o] = fmaf(c_gw[t], p3, v3[o]);
+            }
         }
-        const size_t o = ch * plane + (size_t)py * W + px;
-        const float raw = img[o];
-        const float xv = clamp01(raw, clamp_img), yv = gt[o];
-        const float n = (float)((double)C * (double)plane);
-        const float diff = xv - yv;
-        const float sgn = diff > 0.f ? 1.f : (diff < 0.f ? -1.f : 0.f);
-        float gval = (1.f - lambda) / n * sgn - lambda / n * (ga + 2.f * xv * gb + yv * gc);
-        if (clamp_img && (raw < 0.f || raw > 1.f)) gval = 0.f;
-        dL_dimg[o] = gval * grad_loss[0];
+    }
+    const float n = (float)((double)C * (double)plane);
+    const float gl = grad_loss[0];
+#pragma unroll
+    for (int o = 0; o < 2; o++) {
+        const int py = blockIdx.y * TH + ly0 + o;
+        const f32x2 a1 = v1[o];
+        const float gc = v3[o];
+        if (px < W && py < H) {
+            float ga, gb;
+            unpk(a1, ga, gb);
+            const size_t oo = ch * plane + (size_t)py * W + px;
+            const float raw = img[oo];
+            const float xv = clamp01(raw, clamp_img), yv = gt[oo];
+            const float diff = xv - yv;
+            const float sgn = diff > 0.f ? 1.f : (diff < 0.f ? -1.f : 0.f);
+            float gval = (1.f - lambda) / n * sgn - lambda / n * (ga + 2.f * xv * gb + yv * gc);
+            if (clamp_img && (raw < 0.f || raw > 1.f)) gval = 0.f;
+            dL_dimg[oo] = gval * gl;
+        }
     }
 }
 
@@ -180,9 +311,12 @@ photo_loss_backward_kernel(int H, int W, const float* __restrict__ img, const fl
 
 using namespace gsr;
 
+static size_t loss_blocks(int C, int H, int W) { return (size_t)((W + TW - 1) / TW) * ((H + TH - 1) / TH) * C; }
+
 extern "C" size_t gsr_photo_loss_scratch_bytes(int C, int H, int W)
 {
-    return (size_t)3 * C * H * W * sizeof(float) + 256;
+    // three derivative maps + two doubles per block of the forward kernel (its partial sums of |x - gt| and SSIM)
+    return (size_t)3 * C * H * W * sizeof(float) + 256 + loss_blocks(C, H, W) * 2 * sizeof(double);
 }
 
 extern "C" int gsr_photo_loss_forward(int C, int H, int W, const float* img, const float* gt, float lambda_dssim,
@@ -196,10 +330,11 @@ extern "C" int gsr_photo_loss_forward(int C, int H, int W, const float* img, con
     float* maps = (float*)scratch;
     double* sums = (double*)((char*)scratch + (size_t)3 * C * H * W * sizeof(float));
     sums = (double*)(((uintptr_t)sums + 15) & ~(uintptr_t)15);
-    cudaMemsetAsync(sums, 0, 2 * sizeof(double), s);
-    const dim3 grid((W + LT - 1) / LT, (H + LT - 1) / LT, C);
-    photo_loss_forward_kernel<<<grid, LT * LT, 0, s>>>(H, W, img, gt, clamp_img, maps, sums);
-    photo_loss_finalize_kernel<<<1, 1, 0, s>>>(sums, (double)C * H * W, lambda_dssim, loss_out);
+    const dim3 grid((W + TW - 1) / TW, (H + TH - 1) / TH, C);
+    chain_break();      // whatever ran before this call is not ours to overlap with
+    launch_pdl(photo_loss_forward_kernel, grid, LOSS_THREADS, 0, s, H, W, img, gt, clamp_img, maps, sums);
+    launch_pdl(photo_loss_finalize_kernel, 1, LOSS_THREADS, 0, s, (const double*)sums, (int)loss_blocks(C, H, W),
+               (double)C * H * W, lambda_dssim, loss_out);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) { set_last_error(cudaGetErrorString(e)); return GSR_ERR_CUDA; }
     return GSR_OK;
@@ -214,9 +349,10 @@ extern "C" int gsr_photo_loss_backward(int C, int H, int W, const float* img, co
         set_last_error("gsr_photo_loss_backward: bad argument");
         return GSR_ERR_INVALID;
     }
-    const dim3 grid((W + LT - 1) / LT, (H + LT - 1) / LT, C);
-    photo_loss_backward_kernel<<<grid, LT * LT, 0, s>>>(H, W, img, gt, clamp_img, (const float*)scratch, lambda_dssim,
-                                                        grad_loss, dL_dimg);
+    const dim3 grid((W + TW - 1) / TW, (H + TH - 1) / TH, C);
+    chain_break();
+    launch_pdl(photo_loss_backward_kernel, grid, LOSS_THREADS, 0, s, H, W, img, gt, clamp_img, (const float*)scratch,
+               lambda_dssim, grad_loss, dL_dimg);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) { set_last_error(cudaGetErrorString(e)); return GSR_ERR_CUDA; }
     return GSR_OK;
