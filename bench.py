@@ -338,6 +338,7 @@ def main():
     peaks = None
     if args.impl == "ours":
         import diff_gaussian_rasterization as D
+        import gsr_loss
         lib = D.lib
         if rank == 0:
             # measured ceilings for the blend kernels (FFMA, FFMA2, MUFU.EX2, LDS), before anything is timed
@@ -471,7 +472,10 @@ def main():
         else:
             st2, m2d = (view_d[slot], proj_d[slot], cam_d[slot]), None
         color = render(leaves, m2d, st2)[0]
-        loss = (color - tgt_dev[slot]).abs().mean()
+        if args.impl == "ours":       # the library's fused loss at lambda_dssim = 0: the plain L1 term, two small kernels
+            loss = gsr_loss.photometric_loss(color, tgt_dev[slot], 0.0, clamp=False)
+        else:
+            loss = (color - tgt_dev[slot]).abs().mean()
         loss.backward()
         loss_dev[slot].copy_(loss.detach())
         return leaves
@@ -536,7 +540,7 @@ def main():
             "gaussians_per_s": value * P, "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "what": "per step: camera + target image H2D from pinned memory (double-buffered on a copy stream), "
-                            "render + L1 loss + backward (" + ("one CUDA graph replay, sync-free forward" if use_graph else "eager") +
+                            "render + L1 loss (" + ("gsr_loss, lambda_dssim = 0" if args.impl == "ours" else "PyTorch ops") + ") + backward (" + ("one CUDA graph replay, sync-free forward" if use_graph else "eager") +
                             "), loss D2H + sync"}}
     line.update(loops)
     if peaks is not None:

@@ -181,6 +181,56 @@ photo_loss_forward_kernel(int H, int W, const float* __restrict__ img, const flo
     }
 }
 
+// lambda == 0: the loss is the plain L1 term (utils/loss_utils.py:14-15).  No window, no maps: a streaming pass each way.
+constexpr int L1_PER_THREAD = 8;
+
+__global__ void __launch_bounds__(LOSS_THREADS)
+l1_forward_kernel(size_t n, const float* __restrict__ img, const float* __restrict__ gt, int clamp_img,
+                  double* __restrict__ block_sums)
+{
+    __shared__ float red[LOSS_THREADS / 32];
+    pdl_wait();
+    pdl_trigger();
+    const size_t base = (size_t)blockIdx.x * (LOSS_THREADS * L1_PER_THREAD) + threadIdx.x;
+    float l1 = 0.f;
+#pragma unroll
+    for (int i = 0; i < L1_PER_THREAD; i++) {
+        const size_t k = base + (size_t)i * LOSS_THREADS;
+        if (k < n) l1 += fabsf(clamp01(img[k], clamp_img) - gt[k]);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) l1 += __shfl_xor_sync(0xffffffffu, l1, o);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = l1;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double a = 0.0;
+        for (int w = 0; w < LOSS_THREADS / 32; w++) a += red[w];
+        block_sums[2 * (size_t)blockIdx.x] = a;
+        block_sums[2 * (size_t)blockIdx.x + 1] = 0.0;
+    }
+}
+
+__global__ void __launch_bounds__(LOSS_THREADS)
+l1_backward_kernel(size_t n, const float* __restrict__ img, const float* __restrict__ gt, int clamp_img,
+                   const float* __restrict__ grad_loss, float* __restrict__ dL_dimg)
+{
+    pdl_wait();
+    pdl_trigger();
+    const float g = grad_loss[0] / (float)n;
+    const size_t base = (size_t)blockIdx.x * (LOSS_THREADS * L1_PER_THREAD) + threadIdx.x;
+#pragma unroll
+    for (int i = 0; i < L1_PER_THREAD; i++) {
+        const size_t k = base + (size_t)i * LOSS_THREADS;
+        if (k < n) {
+            const float raw = img[k];
+            const float diff = clamp01(raw, clamp_img) - gt[k];
+            float v = diff > 0.f ? g : (diff < 0.f ? -g : 0.f);
+            if (clamp_img && (raw < 0.f || raw > 1.f)) v = 0.f;
+            dL_dimg[k] = v;
+        }
+    }
+}
+
 __global__ void __launch_bounds__(LOSS_THREADS)
 photo_loss_finalize_kernel(const double* __restrict__ block_sums, int nblk, double n, float lambda, float* __restrict__ out)
 {
@@ -312,11 +362,16 @@ photo_loss_backward_kernel(int H, int W, const float* __restrict__ img, const fl
 using namespace gsr;
 
 static size_t loss_blocks(int C, int H, int W) { return (size_t)((W + TW - 1) / TW) * ((H + TH - 1) / TH) * C; }
+static size_t l1_blocks(int C, int H, int W)
+{
+    return ((size_t)C * H * W + LOSS_THREADS * L1_PER_THREAD - 1) / (LOSS_THREADS * L1_PER_THREAD);
+}
 
 extern "C" size_t gsr_photo_loss_scratch_bytes(int C, int H, int W)
 {
     // three derivative maps + two doubles per block of the forward kernel (its partial sums of |x - gt| and SSIM)
-    return (size_t)3 * C * H * W * sizeof(float) + 256 + loss_blocks(C, H, W) * 2 * sizeof(double);
+    const size_t blocks = loss_blocks(C, H, W) > l1_blocks(C, H, W) ? loss_blocks(C, H, W) : l1_blocks(C, H, W);
+    return (size_t)3 * C * H * W * sizeof(float) + 256 + blocks * 2 * sizeof(double);
 }
 
 extern "C" int gsr_photo_loss_forward(int C, int H, int W, const float* img, const float* gt, float lambda_dssim,
@@ -332,6 +387,15 @@ extern "C" int gsr_photo_loss_forward(int C, int H, int W, const float* img, con
     sums = (double*)(((uintptr_t)sums + 15) & ~(uintptr_t)15);
     const dim3 grid((W + TW - 1) / TW, (H + TH - 1) / TH, C);
     chain_break();      // whatever ran before this call is not ours to overlap with
+    if (lambda_dssim == 0.f) {      // plain L1: no SSIM term to evaluate (loss_out[2] is reported as 0)
+        const size_t n = (size_t)C * H * W;
+        launch_pdl(l1_forward_kernel, (unsigned)l1_blocks(C, H, W), LOSS_THREADS, 0, s, n, img, gt, clamp_img, sums);
+        launch_pdl(photo_loss_finalize_kernel, 1, LOSS_THREADS, 0, s, (const double*)sums, (int)l1_blocks(C, H, W), (double)n,
+                   0.f, loss_out);
+        cudaError_t e0 = cudaGetLastError();
+        if (e0 != cudaSuccess) { set_last_error(cudaGetErrorString(e0)); return GSR_ERR_CUDA; }
+        return GSR_OK;
+    }
     launch_pdl(photo_loss_forward_kernel, grid, LOSS_THREADS, 0, s, H, W, img, gt, clamp_img, maps, sums);
     launch_pdl(photo_loss_finalize_kernel, 1, LOSS_THREADS, 0, s, (const double*)sums, (int)loss_blocks(C, H, W),
                (double)C * H * W, lambda_dssim, loss_out);
@@ -351,6 +415,14 @@ extern "C" int gsr_photo_loss_backward(int C, int H, int W, const float* img, co
     }
     const dim3 grid((W + TW - 1) / TW, (H + TH - 1) / TH, C);
     chain_break();
+    if (lambda_dssim == 0.f) {
+        const size_t n = (size_t)C * H * W;
+        launch_pdl(l1_backward_kernel, (unsigned)l1_blocks(C, H, W), LOSS_THREADS, 0, s, n, img, gt, clamp_img, grad_loss,
+                   dL_dimg);
+        cudaError_t e0 = cudaGetLastError();
+        if (e0 != cudaSuccess) { set_last_error(cudaGetErrorString(e0)); return GSR_ERR_CUDA; }
+        return GSR_OK;
+    }
     launch_pdl(photo_loss_backward_kernel, grid, LOSS_THREADS, 0, s, H, W, img, gt, clamp_img, (const float*)scratch,
                lambda_dssim, grad_loss, dL_dimg);
     cudaError_t e = cudaGetLastError();

@@ -68,3 +68,20 @@ def test_fused_loss_reproduces_the_reference_code_output():
         assert abs(float(loss) - float(z["ref_loss"])) <= 1e-5, path
         ref_g = torch.from_numpy(z["ref_grad"]).to(DEV)
         assert float((img.grad.double() - ref_g).abs().max()) <= 1e-4 * float(ref_g.abs().max()), path
+
+
+@pytest.mark.parametrize("clamp", [False, True])
+def test_lambda_zero_is_the_plain_l1_loss(clamp):
+    """lambda_dssim = 0 takes the streaming L1 path (no SSIM evaluated): value and gradient against torch."""
+    import gsr_loss
+    g = torch.Generator().manual_seed(21)
+    img = (torch.rand(3, 67, 131, generator=g) * 1.4 - 0.2).to(DEV).requires_grad_(True)
+    gt = torch.rand(3, 67, 131, generator=g).to(DEV)
+    loss, parts = gsr_loss.photometric_loss(img, gt, 0.0, clamp=clamp, return_parts=True)
+    loss.backward()
+    ref_in = img.detach().clone().requires_grad_(True)
+    x = ref_in.clamp(0, 1) if clamp else ref_in
+    ref = (x - gt).abs().mean()
+    ref.backward()
+    assert abs(float(loss) - float(ref)) <= 1e-6 and float(parts[2]) == 0.0 and abs(float(parts[1]) - float(ref)) <= 1e-6
+    assert float((img.grad - ref_in.grad).abs().max()) <= 1e-9
