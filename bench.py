@@ -267,8 +267,9 @@ def run_loops(dev, rank, world):
                 "ms_per_iter": g["ms_per_iter"], "last_loss": g["last_loss"]}
     if rank == 0:
         out["global_views_loop"]["what"] = ("examples/cf3dgs_global.py --batched: full iteration (activations, render, fused "
-                                            "L1+SSIM, backward into the flat buffer, all-reduce in 1 + 4 pieces overlapped with the "
-                                            "fused Adam parts, densification statistics), 960x540, 8 training views")
+                                            "L1+SSIM, backward into the flat buffer, NCCL sum of the gradients -- one all-reduce at SH "
+                                            "degree 0; at degree 3 the SH rows are reduce-scattered, stepped on 1/N of the rows per "
+                                            "rank and all-gathered -- fused Adam, densification statistics), 960x540, 8 training views")
     return out
 
 
