@@ -2,17 +2,18 @@
 // n_contrib, T restarts at T_final = 1 - alpha_out and is unwound with T = T / (1 - alpha) -- the same
 // recurrence, not an algebraic equivalent, so nearly opaque pixels behave like the reference.
 //
-// The reference issues 10 global float atomics per blended (pixel, Gaussian) pair.  Here the 32 lanes of a
-// warp always look at the same Gaussian, so the partials are summed across the warp first: every lane drops
-// its 9 (10 with a depth cotangent) partials into a warp-private shared-memory slab ([value][lane], rows padded
-// to 36 floats so both the scalar stores and the 128-bit loads are bank-conflict free); once three entries are
-// parked, lane L sums slab row L (eight LDS.128) and adds it into the table -- ~25 issue slots per entry
-// instead of the ~100 a 5-step shuffle butterfly over 10 values costs (ncu: the butterfly was 70 % of this
-// kernel's instructions; same-address shared atomics from the contributing lanes measured slower still).
-// The 8 warps of the CTA accumulate into a
-// per-batch shared-memory table, and each CTA flushes one 48-byte record per touched Gaussian with three
-// 16-byte vector reductions (red.global.add.v4.f32).  Entries that cannot reach alpha >= 1/255 in the tile / in
-// the warp's 8x4 footprint are rejected exactly as in the forward.
+// The reference issues 10 global float atomics per blended (pixel, Gaussian) pair.  Here the 32 lanes of a warp always
+// look at the same Gaussian, so the partials are summed across the warp first: every lane adds its two pixels and
+// drops its 9 (10 with a depth cotangent) partials into a warp-private shared-memory slab ([value][lane], rows padded
+// to 36 floats so both the scalar stores and the 128-bit loads are bank-conflict free); once three entries are parked,
+// lane L sums slab row L (eight LDS.128) and adds it into a table shared by the CTA's 4 warps -- ~30 issue slots per
+// entry instead of the ~100 a 5-step shuffle butterfly over 10 values costs (ncu: the butterfly was 70 % of the first
+// kernel's instructions; same-address shared atomics from the contributing lanes measured slower still).  The CTA
+// flushes one 48-byte record per touched Gaussian with three 16-byte vector reductions (red.global.add.v4.f32; SASS
+// REDG.E.ADD.F32x4.FTZ: the vector form flushes denormal operands and results to zero -- partial sums below 1.2e-38 are
+// dropped, far under the 1e-4 relative bar; the reference's scalar atomicAdd, REDG.E.ADD.F32.FTZ.RN, flushes as well).
+// Entries that cannot reach alpha >= 1/255 in the tile / in the warp's 8x8 footprint are rejected exactly as in the
+// forward.
 //
 // Gradient record per Gaussian (grad_scratch, 12 floats):
 //   0 mean2D.x  1 mean2D.y  2 conic.x  3 conic.y | 4 conic.w  5 opacity  6 colour.r  7 colour.g |

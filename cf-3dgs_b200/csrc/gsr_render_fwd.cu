@@ -7,8 +7,8 @@
 //
 // What differs is how much work is skipped: entries are staged 256 at a time as packed records (one 16-B
 // gather each for geometry, conic and colour+depth), the staging thread rejects entries that cannot reach
-// alpha >= 1/255 anywhere in the tile, and each warp (8x4 pixels) rejects entries for its own footprint
-// with one lane per entry + a ballot, then walks only the surviving bits.  Rejected pairs are exactly
+// alpha >= 1/255 anywhere in the tile, and each warp (8x8 pixels, two per lane) rejects entries for its own
+// footprint with one lane per entry + a ballot, then walks only the surviving bits.  Rejected pairs are exactly
 // pairs the reference would have skipped at its alpha test.
 #include "gsr_blend.cuh"
 #include "gsr_f32x2.cuh"

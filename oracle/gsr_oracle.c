@@ -29,7 +29,8 @@
  *
  * Parity pinning: the reference ships no golden vectors;
  * this oracle is pinned against the reference's own CUDA build (oracle/_ref)
- * on the GPU box by tests/test_gpu_vs_reference.py.
+ * through golden vectors that build produced on a B200 (tests/golden/*.npz, tests/test_golden.py); the CUDA path is
+ * compared with the live reference build in tests/test_gpu_parity.py and tests/test_gpu_fuzz.py.
  */
 #include <math.h>
 #include <stdint.h>
