@@ -529,7 +529,12 @@ def main():
 
     loops = {}
     if args.impl == "ours" and not args.no_loops:
-        loops = run_loops(dev, rank, world)
+        try:
+            loops = run_loops(dev, rank, world)
+        except Exception as ex:      # the loop numbers must never take the headline line down with them
+            if world > 1:
+                raise                # (with several ranks a one-sided failure would leave the others in a collective)
+            loops = {"loops_error": f"{type(ex).__name__}: {ex}"}
     if rank != 0:
         return 0
     line = {"metric": "fwd+bwd rendered frames/s at 1080p", "value": value, "unit": "frames/s", "n_gpus": world,
