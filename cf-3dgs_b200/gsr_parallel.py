@@ -148,6 +148,8 @@ class BatchedViewsStep:
         """settings: GaussianRasterizationSettings of this rank's view; target: its image; returns this rank's loss."""
         import diff_gaussian_rasterization as D
         m = self.model
+        if m.P > self.P_pad or -(-m.P // self.world) != self.rows_per:
+            raise RuntimeError("the model's Gaussian count changed: build a new BatchedViewsStep for it")
         deg = int(settings.sh_degree)
         M_grad = (deg + 1) * (deg + 1)
         flat, g = self.buffers(M_grad)
