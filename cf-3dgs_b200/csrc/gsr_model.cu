@@ -148,6 +148,200 @@ __global__ void adam_gaussians_kernel(GaussianStepArgs a, AdamCfg c, const float
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------------
+// The step shared between the replicas of a multi-GPU run (batched global views).  Every replica owns
+// the rows [row0, row0 + rows) of the model.  For its rows it needs the SUM of all replicas' gradients and has to hand the
+// updated parameters to ALL replicas.  With the gradient and parameter arrays of the replicas mapped behind one NVSwitch
+// multicast address each, that is a load and a store: multimem.ld_reduce.add returns the sum over the replicas (added in
+// the switch), multimem.st writes every replica's copy.  So the reduce-scatter, the optimiser step and the all-gather of
+// the NCCL form are ONE pass over this replica's rows; gradients cross NVLink once (reduced), parameters once.
+// MC = false: the same kernels on ordinary addresses (one process, or a test): load and store are plain.
+template <bool MC>
+__device__ __forceinline__ float4 ld_sum4(const float* p)
+{
+    float4 r;
+    if (MC)
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                     : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p) : "memory");
+    else
+        r = *reinterpret_cast<const float4*>(p);
+    return r;
+}
+template <bool MC>
+__device__ __forceinline__ float ld_sum1(const float* p)
+{
+    float r;
+    if (MC)
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.f32 %0, [%1];" : "=f"(r) : "l"(p) : "memory");
+    else
+        r = *p;
+    return r;
+}
+template <bool MC>
+__device__ __forceinline__ void st_all4(float* p, const float4 v)
+{
+    if (MC)
+        asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
+                     :: "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+    else
+        *reinterpret_cast<float4*>(p) = v;
+}
+template <bool MC>
+__device__ __forceinline__ void st_all1(float* p, const float v)
+{
+    if (MC)
+        asm volatile("multimem.st.relaxed.sys.global.f32 [%0], %1;" :: "l"(p), "f"(v) : "memory");
+    else
+        *p = v;
+}
+
+struct SharedStepArgs {
+    int row0, rows;                                                   // this replica's rows (multiples of 4)
+    const float *xyz, *opacity_raw, *log_scale, *rot_raw;             // this replica's copy (read)
+    float *xyz_all, *opacity_raw_all, *log_scale_all, *rot_raw_all;   // every replica's copy (written)
+    const float *d_xyz, *d_opacity, *d_scale, *d_rot;                 // sum over the replicas' gradients (read)
+    float *m_xyz, *v_xyz, *m_op, *v_op, *m_sc, *v_sc, *m_rot, *v_rot; // this replica's moments
+    float lr_xyz, lr_op, lr_sc, lr_rot;
+};
+
+__device__ __forceinline__ float4 adam_update4(const float4 p, const float4 g, float4& m, float4& v, float lr, const AdamCfg& c)
+{
+    float4 o;
+    o.x = adam_update(p.x, g.x, m.x, v.x, lr, c);
+    o.y = adam_update(p.y, g.y, m.y, v.y, lr, c);
+    o.z = adam_update(p.z, g.z, m.z, v.z, lr, c);
+    o.w = adam_update(p.w, g.w, m.w, v.w, lr, c);
+    return o;
+}
+
+// The per-Gaussian block of the rows this replica owns, as four streams of float4: rotations (one quaternion each),
+// then xyz, opacity and scale as flat element-wise ranges (their chain rules are per element).  One thread per float4.
+template <bool MC>
+__global__ void adam_shared_gaussians_kernel(SharedStepArgs a, AdamCfg c, const float* __restrict__ bias_dev)
+{
+    const int rows = a.rows;
+    const int n_rot = rows, n_xyz = 3 * (rows / 4), n_op = rows / 4, n_sc = 3 * (rows / 4);
+    int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_rot + n_xyz + n_op + n_sc) return;
+    if (bias_dev) { c.inv_bias1 = bias_dev[0]; c.inv_sqrt_bias2 = bias_dev[1]; }
+    if (t < n_rot) {   // rotation = q / max(|q|, eps): d q = (g - y (y . g)) / n
+        const size_t f = (size_t)4 * (a.row0 + t);
+        const float4 q = *reinterpret_cast<const float4*>(a.rot_raw + f);
+        const float4 gy = ld_sum4<MC>(a.d_rot + f);
+        const float n = sqrtf(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w);
+        float4 g;
+        if (n > 1e-12f) {
+            const float inv = 1.f / n;
+            const float4 y = make_float4(q.x * inv, q.y * inv, q.z * inv, q.w * inv);
+            const float d = y.x * gy.x + y.y * gy.y + y.z * gy.z + y.w * gy.w;
+            g = make_float4((gy.x - y.x * d) * inv, (gy.y - y.y * d) * inv, (gy.z - y.z * d) * inv, (gy.w - y.w * d) * inv);
+        } else {
+            g = make_float4(gy.x * 1e12f, gy.y * 1e12f, gy.z * 1e12f, gy.w * 1e12f);
+        }
+        float4 mm = *reinterpret_cast<float4*>(a.m_rot + f), vv = *reinterpret_cast<float4*>(a.v_rot + f);
+        st_all4<MC>(a.rot_raw_all + f, adam_update4(q, g, mm, vv, a.lr_rot, c));
+        *reinterpret_cast<float4*>(a.m_rot + f) = mm;
+        *reinterpret_cast<float4*>(a.v_rot + f) = vv;
+        return;
+    }
+    t -= n_rot;
+    if (t < n_xyz) {
+        const size_t f = (size_t)3 * a.row0 + (size_t)4 * t;
+        const float4 p = *reinterpret_cast<const float4*>(a.xyz + f);
+        const float4 g = ld_sum4<MC>(a.d_xyz + f);
+        float4 mm = *reinterpret_cast<float4*>(a.m_xyz + f), vv = *reinterpret_cast<float4*>(a.v_xyz + f);
+        st_all4<MC>(a.xyz_all + f, adam_update4(p, g, mm, vv, a.lr_xyz, c));
+        *reinterpret_cast<float4*>(a.m_xyz + f) = mm;
+        *reinterpret_cast<float4*>(a.v_xyz + f) = vv;
+        return;
+    }
+    t -= n_xyz;
+    if (t < n_op) {    // opacity = sigmoid(raw): d raw = d o * o (1 - o)
+        const size_t f = (size_t)a.row0 + (size_t)4 * t;
+        const float4 p = *reinterpret_cast<const float4*>(a.opacity_raw + f);
+        float4 g = ld_sum4<MC>(a.d_opacity + f);
+        const float ox = 1.f / (1.f + expf(-p.x)), oy = 1.f / (1.f + expf(-p.y));
+        const float oz = 1.f / (1.f + expf(-p.z)), ow = 1.f / (1.f + expf(-p.w));
+        g = make_float4(g.x * ox * (1.f - ox), g.y * oy * (1.f - oy), g.z * oz * (1.f - oz), g.w * ow * (1.f - ow));
+        float4 mm = *reinterpret_cast<float4*>(a.m_op + f), vv = *reinterpret_cast<float4*>(a.v_op + f);
+        st_all4<MC>(a.opacity_raw_all + f, adam_update4(p, g, mm, vv, a.lr_op, c));
+        *reinterpret_cast<float4*>(a.m_op + f) = mm;
+        *reinterpret_cast<float4*>(a.v_op + f) = vv;
+        return;
+    }
+    t -= n_op;
+    {                  // scale = exp(raw): d raw = d s * s
+        const size_t f = (size_t)3 * a.row0 + (size_t)4 * t;
+        const float4 p = *reinterpret_cast<const float4*>(a.log_scale + f);
+        float4 g = ld_sum4<MC>(a.d_scale + f);
+        g = make_float4(g.x * expf(p.x), g.y * expf(p.y), g.z * expf(p.z), g.w * expf(p.w));
+        float4 mm = *reinterpret_cast<float4*>(a.m_sc + f), vv = *reinterpret_cast<float4*>(a.v_sc + f);
+        st_all4<MC>(a.log_scale_all + f, adam_update4(p, g, mm, vv, a.lr_sc, c));
+        *reinterpret_cast<float4*>(a.m_sc + f) = mm;
+        *reinterpret_cast<float4*>(a.v_sc + f) = vv;
+    }
+}
+
+// SH rows [row0, row0 + rows): one thread per float4 (VEC) or per float of the first upd_floats floats of a row; see
+// adam_features_kernel for grad_floats / upd_floats.  VEC needs floats_per_gaussian, grad_floats, upd_floats % 4 == 0.
+template <bool MC, bool VEC>
+__global__ void adam_shared_features_kernel(size_t row0, size_t n, int floats_per_gaussian, int grad_floats, int upd_floats,
+                                            const float* __restrict__ p, float* p_all, const float* g,
+                                            float* __restrict__ m, float* __restrict__ v, float lr_dc, float lr_rest,
+                                            AdamCfg c, const float* __restrict__ bias_dev)
+{
+    constexpr int W = VEC ? 4 : 1;
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    if (bias_dev) { c.inv_bias1 = bias_dev[0]; c.inv_sqrt_bias2 = bias_dev[1]; }
+    const size_t per_row = (size_t)(upd_floats / W);
+    const size_t row = row0 + i / per_row;
+    const int k = (int)(i % per_row) * W;
+    i = row * (size_t)floats_per_gaussian + k;
+    if (VEC) {
+        const float4 gi = k < grad_floats ? ld_sum4<MC>(g + row * (size_t)grad_floats + k) : make_float4(0.f, 0.f, 0.f, 0.f);
+        const float4 pp = *reinterpret_cast<const float4*>(p + i);
+        float4 mm = *reinterpret_cast<float4*>(m + i), vv = *reinterpret_cast<float4*>(v + i);
+        float4 o;
+        o.x = adam_update(pp.x, gi.x, mm.x, vv.x, k < 3 ? lr_dc : lr_rest, c);        // coefficient 0 = floats 0..2 of the row
+        o.y = adam_update(pp.y, gi.y, mm.y, vv.y, k + 1 < 3 ? lr_dc : lr_rest, c);
+        o.z = adam_update(pp.z, gi.z, mm.z, vv.z, k + 2 < 3 ? lr_dc : lr_rest, c);
+        o.w = adam_update(pp.w, gi.w, mm.w, vv.w, lr_rest, c);
+        st_all4<MC>(p_all + i, o);
+        *reinterpret_cast<float4*>(m + i) = mm;
+        *reinterpret_cast<float4*>(v + i) = vv;
+    } else {
+        const float gi = k < grad_floats ? ld_sum1<MC>(g + row * (size_t)grad_floats + k) : 0.f;
+        float mm = m[i], vv = v[i];
+        st_all1<MC>(p_all + i, adam_update(p[i], gi, mm, vv, k < 3 ? lr_dc : lr_rest, c));
+        m[i] = mm; v[i] = vv;
+    }
+}
+
+// dst[i] = sum over the replicas of src[i], read through a multicast address (set-up check of the shared step)
+__global__ void multicast_probe_kernel(const float* mc_src, float* __restrict__ dst, int n4)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n4) reinterpret_cast<float4*>(dst)[i] = ld_sum4<true>(mc_src + 4 * (size_t)i);
+}
+
+// add_densification_stats + max_radii2D alone (gaussian_model_cf.py:716-719): in the shared step they stay per replica
+// (each replica saw its own view) and cover all P Gaussians.
+__global__ void densify_stats_kernel(int P, const float* __restrict__ d_means2D, const int* __restrict__ radii,
+                                     float* __restrict__ grad_accum, float* __restrict__ denom, float* __restrict__ max_radii2D)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    const int r = radii[i];
+    if (r > 0) {
+        const float gx = d_means2D[3 * i], gy = d_means2D[3 * i + 1];
+        grad_accum[i] += sqrtf(gx * gx + gy * gy);
+        denom[i] += 1.f;
+        if (max_radii2D) max_radii2D[i] = fmaxf(max_radii2D[i], (float)r);
+    }
+}
+
 }  // namespace
 }  // namespace gsr
 
@@ -285,4 +479,109 @@ extern "C" int gsr_gaussian_adam_step_part(int P, int M, int M_grad, int M_upd, 
 extern "C" size_t gsr_gaussian_adam_state_floats(int P, int M)
 {
     return (size_t)2 * ((size_t)3 + 1 + 3 + 4 + (size_t)3 * M) * (size_t)(P > 0 ? P : 0);
+}
+
+extern "C" int gsr_gaussian_adam_step_shared(int P_pad, int M, int M_grad, int M_upd, int row0, int rows, int multicast,
+                                             int tick, int64_t* step_state, float beta1, float beta2, float eps,
+                                             const float* lrs_host, const float* xyz, const float* features,
+                                             const float* opacity_raw, const float* log_scale, const float* rot_raw,
+                                             float* xyz_all, float* features_all, float* opacity_raw_all,
+                                             float* log_scale_all, float* rot_raw_all, const float* d_xyz_sum,
+                                             const float* d_features_sum, const float* d_opacity_sum,
+                                             const float* d_scale_sum, const float* d_rot_sum, float* state, void* stream)
+{
+    cudaStream_t s = (cudaStream_t)stream;
+    if (P_pad < 0 || M < 0 || !step_state || !lrs_host || M_grad < 0 || M_grad > M || M_upd < 0 || M_upd > M || row0 < 0 ||
+        rows < 0 || (long long)row0 + rows > P_pad) {
+        set_last_error("gsr_gaussian_adam_step_shared: bad size, or the row range lies outside P_pad");
+        return GSR_ERR_INVALID;
+    }
+    if ((P_pad | row0 | rows) & 3) {
+        set_last_error("gsr_gaussian_adam_step_shared: P_pad, row0 and rows must be multiples of 4 (the rows are moved as float4)");
+        return GSR_ERR_INVALID;
+    }
+    if (P_pad == 0) return GSR_OK;
+    if (!xyz || !opacity_raw || !log_scale || !rot_raw || !xyz_all || !opacity_raw_all || !log_scale_all || !rot_raw_all ||
+        !d_xyz_sum || !d_opacity_sum || !d_scale_sum || !d_rot_sum || !state ||
+        (M > 0 && (!features || !features_all || !d_features_sum))) {
+        set_last_error("gsr_gaussian_adam_step_shared: required pointer is NULL");
+        return GSR_ERR_INVALID;
+    }
+    const uintptr_t all_ptrs = (uintptr_t)xyz | (uintptr_t)features | (uintptr_t)opacity_raw | (uintptr_t)log_scale |
+                               (uintptr_t)rot_raw | (uintptr_t)xyz_all | (uintptr_t)features_all | (uintptr_t)opacity_raw_all |
+                               (uintptr_t)log_scale_all | (uintptr_t)rot_raw_all | (uintptr_t)d_xyz_sum |
+                               (uintptr_t)d_features_sum | (uintptr_t)d_opacity_sum | (uintptr_t)d_scale_sum |
+                               (uintptr_t)d_rot_sum | (uintptr_t)state;
+    if (all_ptrs & 15) {
+        set_last_error("gsr_gaussian_adam_step_shared: every array must be 16-byte aligned");
+        return GSR_ERR_INVALID;
+    }
+    AdamCfg c;
+    c.b1 = beta1; c.b2 = beta2; c.eps = eps;
+    c.inv_bias1 = c.inv_sqrt_bias2 = 1.f;
+    if (tick) adam_tick_kernel<<<1, 1, 0, s>>>(reinterpret_cast<long long*>(step_state), beta1, beta2);
+    const float* bias_dev = reinterpret_cast<const float*>(reinterpret_cast<long long*>(step_state) + 1);
+    // moments: the layout of gsr_gaussian_adam_step for P_pad Gaussians (every sub-array then starts 16-byte aligned)
+    const size_t n = (size_t)P_pad;
+    float* st = state;
+    SharedStepArgs a;
+    a.row0 = row0; a.rows = rows;
+    a.xyz = xyz; a.opacity_raw = opacity_raw; a.log_scale = log_scale; a.rot_raw = rot_raw;
+    a.xyz_all = xyz_all; a.opacity_raw_all = opacity_raw_all; a.log_scale_all = log_scale_all; a.rot_raw_all = rot_raw_all;
+    a.d_xyz = d_xyz_sum; a.d_opacity = d_opacity_sum; a.d_scale = d_scale_sum; a.d_rot = d_rot_sum;
+    a.m_rot = st; st += 4 * n; a.v_rot = st; st += 4 * n;
+    a.m_xyz = st; st += 3 * n; a.v_xyz = st; st += 3 * n;
+    a.m_op = st; st += n; a.v_op = st; st += n;
+    a.m_sc = st; st += 3 * n; a.v_sc = st; st += 3 * n;
+    float* m_f = st; st += 3 * (size_t)M * n;
+    float* v_f = st;
+    a.lr_xyz = lrs_host[0]; a.lr_op = lrs_host[3]; a.lr_sc = lrs_host[4]; a.lr_rot = lrs_host[5];
+    if (rows > 0) {
+        const int threads = rows + 3 * (rows / 4) + rows / 4 + 3 * (rows / 4);
+        if (multicast) adam_shared_gaussians_kernel<true><<<div_up(threads, 256), 256, 0, s>>>(a, c, bias_dev);
+        else adam_shared_gaussians_kernel<false><<<div_up(threads, 256), 256, 0, s>>>(a, c, bias_dev);
+    }
+    if (M_upd > 0 && rows > 0) {
+        const int fpg = 3 * M, gf = 3 * M_grad, uf = 3 * M_upd;
+        const bool vec = !((fpg | gf | uf) & 3);
+        const size_t nf = (size_t)(uf / (vec ? 4 : 1)) * (size_t)rows;
+        const unsigned blocks = (unsigned)((nf + 255) / 256);
+#define GSR_FEAT(MC, VEC)                                                                                           \
+        adam_shared_features_kernel<MC, VEC><<<blocks, 256, 0, s>>>((size_t)row0, nf, fpg, gf, uf, features, features_all, \
+                                                                    d_features_sum, m_f, v_f, lrs_host[1], lrs_host[2], c, \
+                                                                    bias_dev)
+        if (multicast) { if (vec) GSR_FEAT(true, true); else GSR_FEAT(true, false); }
+        else           { if (vec) GSR_FEAT(false, true); else GSR_FEAT(false, false); }
+#undef GSR_FEAT
+    }
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { set_last_error(cudaGetErrorString(e)); return GSR_ERR_CUDA; }
+    return GSR_OK;
+}
+
+extern "C" int gsr_densify_stats(int P, const float* d_means2D, const int* radii, float* grad_accum, float* denom,
+                                 float* max_radii2D, void* stream)
+{
+    if (P < 0 || (P > 0 && (!d_means2D || !radii || !grad_accum || !denom))) {
+        set_last_error("gsr_densify_stats: bad argument");
+        return GSR_ERR_INVALID;
+    }
+    if (P == 0) return GSR_OK;
+    densify_stats_kernel<<<div_up(P, 256), 256, 0, (cudaStream_t)stream>>>(P, d_means2D, radii, grad_accum, denom, max_radii2D);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { set_last_error(cudaGetErrorString(e)); return GSR_ERR_CUDA; }
+    return GSR_OK;
+}
+
+extern "C" int gsr_multicast_probe(const float* mc_src, float* dst, int n, void* stream)
+{
+    if (!mc_src || !dst || n < 0 || (n & 3) || (((uintptr_t)mc_src | (uintptr_t)dst) & 15)) {
+        set_last_error("gsr_multicast_probe: n must be a multiple of 4 and both pointers 16-byte aligned");
+        return GSR_ERR_INVALID;
+    }
+    if (n == 0) return GSR_OK;
+    multicast_probe_kernel<<<div_up(n / 4, 256), 256, 0, (cudaStream_t)stream>>>(mc_src, dst, n / 4);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { set_last_error(cudaGetErrorString(e)); return GSR_ERR_CUDA; }
+    return GSR_OK;
 }

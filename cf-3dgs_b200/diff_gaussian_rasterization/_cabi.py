@@ -51,6 +51,9 @@ SIGNATURES = {
                                            _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "gsr_gaussian_adam_step_part": (c_int, [c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, _P, c_float, c_float, c_float,
                                             _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "gsr_gaussian_adam_step_shared": (c_int, [c_int] * 8 + [_P, c_float, c_float, c_float] + [_P] * 18),
+    "gsr_densify_stats": (c_int, [c_int, _P, _P, _P, _P, _P, _P]),
+    "gsr_multicast_probe": (c_int, [_P, _P, c_int, _P]),
     "gsr_mark_visible": (c_int, [c_int, _P, _P, _P, _P, _P]),
     "gsr_debug_dump": (c_int, [c_int, c_int, c_int, c_int64, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "gsr_profile_enable": (c_int, [c_int]),

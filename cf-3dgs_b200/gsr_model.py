@@ -41,6 +41,9 @@ class FusedGaussianModel:
         # SH bands that have ever received a gradient (as a coefficient count): the bands above it still have zero moments,
         # so Adam's update of them is exactly zero and the step skips them (at degree 0: 3 of 48 floats per Gaussian)
         self.sh_ever = 0
+        # set by gsr_parallel.BatchedViewsStep when the parameters live in symmetric memory and the step is shared between
+        # the replicas: the moments then have the padded layout and only that object may step the model
+        self.shared_step_owner = None
 
     def activated(self) -> Dict[str, torch.Tensor]:
         """opacities (P,1), scales (P,3), rotations (P,4) for the rasterizer (fresh tensors, no autograd history)."""
@@ -59,6 +62,8 @@ class FusedGaussianModel:
         """One optimiser step from the gradients the rasterizer backward produced (w.r.t. the activated tensors).
         sh_degree (needs device_step=True): the active SH degree the gradient was produced at -- the coefficients of higher
         bands have gradient zero; as long as they never had another, their moments are zero and they are skipped."""
+        if self.shared_step_owner is not None:
+            raise RuntimeError("this model is stepped by a BatchedViewsStep (shared step): call that object")
         if sh_degree is not None and self.step_state is not None and d_features is not None:
             grads = dict(means3D=d_xyz.contiguous(), sh=d_features.contiguous(), opacity=d_opacities.contiguous(),
                          scales=d_scales.contiguous(), rotations=d_rotations.contiguous())
@@ -91,6 +96,8 @@ class FusedGaussianModel:
         "rotations" (P,4) -- typically views into one flat, all-reduced buffer.  Needs device_step=True."""
         if self.step_state is None:
             raise RuntimeError("step_part needs device_step=True (the step counter lives on the device)")
+        if self.shared_step_owner is not None:
+            raise RuntimeError("this model is stepped by a BatchedViewsStep (shared step): call that object")
         rows = self.P if rows is None else rows
         # active: coefficients that can hold a non-zero gradient in this step (default: all M_grad of them)
         self.sh_ever = max(self.sh_ever, min(int(M_grad), self.M) if active is None else min(int(active), self.M))

@@ -105,13 +105,36 @@ class BatchedViewsStep:
 
     SHARD_FROM_M = 9       # SH coefficient count from which the SH rows are reduce-scattered / all-gathered
 
-    def __init__(self, model, shard_features: Optional[bool] = None):
+    def __init__(self, model, shard_features: Optional[bool] = None, multicast: Optional[bool] = False):
+        """multicast: True = the shared step over NVSwitch multicast (see _setup_multicast; raises if the box cannot),
+        None = use it when it can be set up on every rank and fall back to NCCL otherwise (`multicast_reason` says why),
+        False = the NCCL form."""
         self.model = model
         self.world = dist.get_world_size() if dist.is_initialized() else 1
         self.rank = dist.get_rank() if dist.is_initialized() else 0
         self.shard_features = shard_features
         self._key = None
+        self._mc = None
+        self.multicast_reason = "not requested"
         m = model
+        if multicast is not False and self.world > 1:
+            ok, why = True, ""
+            try:
+                self._setup_multicast()
+            except Exception as ex:      # noqa: BLE001 -- whatever the reason, every rank has to take the same path
+                ok, why = False, f"{type(ex).__name__}: {ex}"
+            flag = torch.tensor([1 if ok else 0], device=m.xyz.device)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+            if int(flag) == 1:
+                self.multicast_reason = "in use"
+                self.rows_per, self.P_pad, self._feat_store = self._mc["rows_per"], self._mc["Pp"], None
+                return
+            if ok:
+                self._release_multicast()
+                why = "another rank could not set it up"
+            self.multicast_reason = why
+            if multicast is True:
+                raise RuntimeError("NVSwitch multicast is not available for the shared step: " + why)
         # rows padded to a multiple of the world size so that the SH rows split evenly; the model's coefficient tensor
         # becomes a view of the padded storage (the all-gather writes straight into it)
         self.rows_per = -(-m.P // self.world)
@@ -123,6 +146,133 @@ class BatchedViewsStep:
             self._feat_store = store
         else:
             self._feat_store = None
+
+    # ---- the shared step over NVSwitch multicast -----------------------------------------------------------------------
+    # Parameters and gradients of every replica live in ONE symmetric allocation per rank (torch.distributed.
+    # _symmetric_memory: same size and layout everywhere, the allocations of all ranks bound to one multicast object).
+    # The rasterizer reads and writes its own copy through ordinary pointers; gsr_gaussian_adam_step_shared reads the
+    # gradients of its rows through the multicast address with multimem.ld_reduce (the switch adds the replicas) and
+    # writes the new parameters through it with multimem.st (the switch delivers them to every replica).  No NCCL call,
+    # no reduced gradient buffer, and Adam runs on 1/N of the rows for every parameter group.
+    _WIDTHS = (("rot_raw", 4), ("xyz", 3), ("opacity_raw", 1), ("log_scales", 3))
+
+    def _setup_multicast(self):
+        import torch.distributed._symmetric_memory as symm
+        from diff_gaussian_rasterization._cabi import check, lib
+        m, W = self.model, self.world
+        dev = m.xyz.device
+        rows_per = -(-(-(-m.P // W)) // 4) * 4            # rows per rank, a multiple of 4: every range moves as float4
+        Pp = rows_per * W
+        per = 11 + 3 * m.M                                 # floats per Gaussian: parameters, and again gradients
+        buf = symm.empty(2 * per * Pp, dtype=torch.float32, device=dev)
+        hdl = symm.rendezvous(buf, dist.group.WORLD)
+        mc0 = int(hdl.multicast_ptr)
+        if mc0 == 0:
+            raise RuntimeError("the symmetric allocation has no multicast address on this system")
+        mc0 += buf.data_ptr() - int(hdl.buffer_ptrs[hdl.rank])
+        buf.zero_()
+        # self-check of the address arithmetic and of the switch: every rank writes rank + 1, the multicast read must
+        # return 1 + 2 + ... + W on every rank
+        probe_n = 4 * 64
+        buf[:probe_n].fill_(float(self.rank + 1))
+        got = torch.empty(probe_n, dtype=torch.float32, device=dev)
+        hdl.barrier(channel=0)
+        check(lib.gsr_multicast_probe(mc0, got.data_ptr(), probe_n, torch.cuda.current_stream().cuda_stream))
+        hdl.barrier(channel=0)
+        want = float(W * (W + 1) // 2)
+        if not bool((got == want).all()):
+            raise RuntimeError(f"multicast probe read {float(got[0])}, expected {want}")
+        buf[:probe_n].zero_()
+        off, par, grd = 0, {}, {}
+        for name, w in self._WIDTHS + (("features", 3 * m.M),):
+            par[name] = (off, w)
+            off += w * Pp
+        # re-home the parameters: the model's tensors become views of the first P rows of the symmetric arrays
+        old_state = m.state
+        for name, (o, w) in par.items():
+            src = getattr(m, name)
+            dst = buf[o:o + w * Pp].view((Pp,) + tuple(src.shape[1:]))
+            dst[:m.P].copy_(src)
+            setattr(m, name, dst[:m.P])
+        state = torch.zeros(lib.gsr_gaussian_adam_state_floats(Pp, m.M), dtype=torch.float32, device=dev)
+        so, sn = 0, 0
+        for w in (4, 4, 3, 3, 1, 1, 3, 3, 3 * m.M, 3 * m.M):       # the moment arrays, from P rows each to P_pad rows each
+            state[sn:sn + w * m.P].copy_(old_state[so:so + w * m.P])
+            so += w * m.P
+            sn += w * Pp
+        m.state = state
+        m.shared_step_owner = self                                 # FusedGaussianModel.step()/step_part() refuse from now on
+        self._mc = dict(hdl=hdl, buf=buf, mc0=mc0, par=par, per=per, Pp=Pp, rows_per=rows_per, M_grad=None,
+                        m2d=torch.empty((m.P, 3), dtype=torch.float32, device=dev))
+        dist.barrier()
+
+    def _release_multicast(self):
+        """Back to ordinary tensors (used when another rank could not set the shared step up)."""
+        m, mc = self.model, self._mc
+        if mc is None:
+            return
+        Pp, P = mc["Pp"], m.P
+        for name in mc["par"]:
+            setattr(m, name, getattr(m, name).clone())
+        state = torch.zeros(_state_floats(P, m.M), dtype=torch.float32, device=m.xyz.device)
+        so, sn = 0, 0
+        for w in (4, 4, 3, 3, 1, 1, 3, 3, 3 * m.M, 3 * m.M):
+            state[sn:sn + w * P].copy_(m.state[so:so + w * P])
+            so += w * Pp
+            sn += w * P
+        m.state = state
+        m.shared_step_owner = None
+        self._mc = None
+
+    def _multicast_step(self, settings, target, loss_fn, window):
+        import ctypes
+        import diff_gaussian_rasterization as D
+        from diff_gaussian_rasterization._cabi import check, lib
+        from gsr_model import LR_ORDER
+        m, mc = self.model, self._mc
+        Pp, per, buf, P = mc["Pp"], mc["per"], mc["buf"], m.P
+        deg = int(settings.sh_degree)
+        M_grad = (deg + 1) * (deg + 1)
+        g0 = per * Pp                                              # gradients: same order and offsets as the parameters
+        if mc["M_grad"] != M_grad:                                 # the packing of the SH gradient changes with the degree
+            buf[g0 + 11 * Pp:].zero_()
+            mc["M_grad"] = M_grad
+        gv = {}
+        for name, (o, w) in mc["par"].items():
+            w = 3 * M_grad if name == "features" else w
+            gv[name] = buf[g0 + o:g0 + o + w * P].view((P, M_grad, 3) if name == "features" else (P, w))
+        act = m.activated()
+        e = torch.Tensor([])
+        rs = settings
+        R, color, depth, alpha, radii, geom, binning, img = D._forward_impl(
+            rs.bg, m.xyz, e, act["opacities"], act["scales"], act["rotations"], rs.scale_modifier, e, rs.viewmatrix,
+            rs.projmatrix, rs.tanfovx, rs.tanfovy, rs.image_height, rs.image_width, m.features, deg, rs.campos, False, False)
+        leaf = color.requires_grad_(True)
+        loss = loss_fn(leaf, target, window)
+        loss.backward()
+        D._backward_impl(rs.bg, m.xyz, radii, e, act["scales"], act["rotations"], rs.scale_modifier, e, rs.viewmatrix,
+                         rs.projmatrix, rs.tanfovx, rs.tanfovy, leaf.grad, None, None, m.features, deg, rs.campos, geom, R,
+                         binning, img, alpha, False,
+                         out=dict(means3D=gv["xyz"], means2D=mc["m2d"], opacity=gv["opacity_raw"], sh=gv["features"],
+                                  scales=gv["log_scales"], rotations=gv["rot_raw"]), dsh_M=M_grad)
+        m.sh_ever = max(m.sh_ever, min(M_grad, m.M))
+        m.step_count += 1
+        lr = (ctypes.c_float * 6)(*[float(m.lrs[k]) for k in LR_ORDER])
+        local, mcast = buf.data_ptr(), mc["mc0"]
+        order = ("xyz", "features", "opacity_raw", "log_scales", "rot_raw")
+        loc = [local + 4 * mc["par"][k][0] for k in order]
+        allp = [mcast + 4 * mc["par"][k][0] for k in order]
+        gsum = [mcast + 4 * (g0 + mc["par"][k][0]) for k in order]
+        stream = torch.cuda.current_stream().cuda_stream
+        mc["hdl"].barrier(channel=0)        # every replica's gradients are written, and nobody still reads the parameters
+        with torch.cuda.device(m.xyz.device):
+            check(lib.gsr_gaussian_adam_step_shared(
+                Pp, m.M, M_grad, int(m.sh_ever), self.rank * mc["rows_per"], mc["rows_per"], 1, 1, m.step_state.data_ptr(),
+                float(m.betas[0]), float(m.betas[1]), float(m.eps), lr, *loc, *allp, *gsum, m.state.data_ptr(), stream))
+            check(lib.gsr_densify_stats(P, mc["m2d"].data_ptr(), radii.data_ptr(), m.xyz_gradient_accum.data_ptr(),
+                                        m.denom.data_ptr(), m.max_radii2D.data_ptr(), stream))
+        mc["hdl"].barrier(channel=0)        # every replica's rows have arrived here, and mine everywhere
+        return loss.detach()
 
     def buffers(self, M_grad: int):
         m = self.model
@@ -147,6 +297,8 @@ class BatchedViewsStep:
     def __call__(self, settings, target, loss_fn, window=None):
         """settings: GaussianRasterizationSettings of this rank's view; target: its image; returns this rank's loss."""
         import diff_gaussian_rasterization as D
+        if self._mc is not None:
+            return self._multicast_step(settings, target, loss_fn, window)
         m = self.model
         if m.P > self.P_pad or -(-m.P // self.world) != self.rows_per:
             raise RuntimeError("the model's Gaussian count changed: build a new BatchedViewsStep for it")
@@ -190,6 +342,10 @@ class BatchedViewsStep:
         n_feat = self.rows_per * m.M * 3
         dist.all_gather_into_tensor(store, store[self.rank * n_feat:(self.rank + 1) * n_feat])   # everyone's updated rows
         return loss.detach()
+
+
+def _state_floats(P: int, M: int) -> int:
+    return 2 * (11 + 3 * M) * max(P, 0)
 
 
 def shard_pairs(n_pairs: int, rank: int, world: int) -> List[int]:

@@ -54,7 +54,7 @@ def frame_pose(i, n):
 
 def default_config(**kw):
     cfg = dict(frames=8, points_per_frame=130_000, iters=200, width=960, height=540, sh_degree=3, impl="ours", loss=None,
-               model=None, graph=False, batched=False, densify_every=0, psnr_every=0, profile=False, warmup=10)
+               model=None, graph=False, batched=False, densify_every=0, psnr_every=0, profile=False, warmup=10, multicast="off")
     cfg.update(kw)
     if cfg["model"] is None:
         cfg["model"] = "fused" if cfg["impl"] == "ours" else "torch"
@@ -189,7 +189,8 @@ def run_global(args, dev, rank=0, world=1):
         opt.step(); opt.zero_grad(set_to_none=True)
         return loss
 
-    batched = GPar.BatchedViewsStep(model) if args.batched else None
+    mcast = {"on": True, "auto": None, "off": False}[args.multicast]
+    batched = GPar.BatchedViewsStep(model, multicast=mcast) if args.batched else None
 
     def view_of(k):
         return int(order[k * world + rank]) if args.batched else int(order[k])
@@ -266,7 +267,7 @@ def run_global(args, dev, rank=0, world=1):
         new = _densify_stand_in({k: v.detach() for k, v in r.items()}, accum, denom, round_index)
         model = build_model(new)
         if args.batched:
-            batched = GPar.BatchedViewsStep(model)
+            batched = GPar.BatchedViewsStep(model, multicast=mcast)
         state["P"] = new["xyz"].shape[0]
         state["P_history"].append(state["P"])
         state["densify_rounds"] += 1
@@ -341,6 +342,7 @@ def run_global(args, dev, rank=0, world=1):
         line["allreduce_bytes"] = 4 * (11 + 3 * (deg + 1) * (deg + 1)) * state["P"]
         line["sh_rows_sharded"] = bool(world > 1 and (deg + 1) * (deg + 1) >= GPar.BatchedViewsStep.SHARD_FROM_M)
         line["replicas_bit_identical"] = identical
+        line["shared_step_multicast"] = batched.multicast_reason      # "in use", or why the NCCL form ran
     if args.densify_every:
         line["densify_every"] = args.densify_every
         line["densify_rounds"] = state["densify_rounds"]
@@ -372,6 +374,9 @@ def main():
     ap.add_argument("--model", default=None, choices=["fused", "torch"],
                     help="fused activation/Adam/statistics kernels (default for ours) or torch.optim.Adam + autograd")
     ap.add_argument("--batched", action="store_true", help="batched global views: one view per rank per step, NCCL all-reduce")
+    ap.add_argument("--multicast", default="off", choices=["on", "auto", "off"],
+                    help="--batched: the optimiser step shared between the replicas over NVSwitch multicast (multimem loads / "
+                         "stores) instead of NCCL collectives; auto = when the box supports it")
     ap.add_argument("--densify-every", type=int, default=0, help="change the Gaussian count every N iterations (0 = never)")
     ap.add_argument("--psnr-every", type=int, default=0, help="record the PSNR over 4 fixed views every N iterations")
     ap.add_argument("--c3", action="store_true", help="BASELINE configs[2] at its stated shape: 120 frames, ~1M Gaussians, "

@@ -113,3 +113,62 @@ def test_skipping_never_active_sh_bands_changes_nothing():
     torch.cuda.synchronize()
     for name in ["xyz", "features", "opacity_raw", "log_scales", "rot_raw", "state"]:
         assert torch.equal(getattr(full, name), getattr(lean, name)), name
+
+
+@pytest.mark.parametrize("M,M_grad,M_upd", [(16, 16, 16), (16, 1, 1), (16, 4, 9), (4, 4, 4), (16, 9, 16)])
+def test_shared_step_on_plain_addresses_equals_the_step_in_parts(M, M_grad, M_upd):
+    """gsr_gaussian_adam_step_shared with multicast = 0 (plain loads and stores) over two row ranges of a padded model
+    gives what gsr_gaussian_adam_step_part gives on the same arrays: the multi-GPU form differs from it only in how the
+    summed gradient is read and where the new parameters are written.  Float4 and scalar SH packings."""
+    import ctypes
+    from diff_gaussian_rasterization._cabi import check, lib
+    Pp = 4 * 613
+    g = torch.Generator().manual_seed(3)
+    mk = lambda *s, sc=1.0: (sc * torch.randn(*s, generator=g)).to(DEV)
+    par = dict(xyz=mk(Pp, 3), feat=mk(Pp, M, 3, sc=0.3), opa=mk(Pp, 1), ls=mk(Pp, 3, sc=0.3) - 3, rot=mk(Pp, 4))
+    par["rot"][7] = 0                                       # a degenerate quaternion takes the eps branch
+    lr = (ctypes.c_float * 6)(1.6e-4, 2.5e-3, 1.25e-4, 0.05, 5e-3, 1e-3)
+    n_state = lib.gsr_gaussian_adam_state_floats(Pp, M)
+    a = {k: v.clone() for k, v in par.items()}
+    b = {k: v.clone() for k, v in par.items()}
+    st_a = torch.zeros(n_state, device=DEV); st_b = torch.zeros(n_state, device=DEV)
+    ss_a = torch.zeros(2, dtype=torch.int64, device=DEV); ss_b = torch.zeros(2, dtype=torch.int64, device=DEV)
+    s = torch.cuda.current_stream().cuda_stream
+    for it in range(3):
+        gr = dict(xyz=mk(Pp, 3), feat=mk(Pp, M_grad, 3), opa=mk(Pp, 1), ls=mk(Pp, 3), rot=mk(Pp, 4))
+        check(lib.gsr_gaussian_adam_step_part(
+            Pp, M, M_grad, M_upd, 3, 0, Pp, 1, ss_a.data_ptr(), 0.9, 0.999, 1e-15, lr, a["xyz"].data_ptr(), a["feat"].data_ptr(),
+            a["opa"].data_ptr(), a["ls"].data_ptr(), a["rot"].data_ptr(), gr["xyz"].data_ptr(), gr["feat"].data_ptr(),
+            gr["opa"].data_ptr(), gr["ls"].data_ptr(), gr["rot"].data_ptr(), st_a.data_ptr(), None, None, None, None, None, s))
+        split = 4 * 200
+        for i, (row0, rows) in enumerate([(0, split), (split, Pp - split)]):
+            ptrs = [b[k].data_ptr() for k in ("xyz", "feat", "opa", "ls", "rot")]
+            check(lib.gsr_gaussian_adam_step_shared(
+                Pp, M, M_grad, M_upd, row0, rows, 0, int(i == 0), ss_b.data_ptr(), 0.9, 0.999, 1e-15, lr, *ptrs, *ptrs,
+                *[gr[k].data_ptr() for k in ("xyz", "feat", "opa", "ls", "rot")], st_b.data_ptr(), s))
+    torch.cuda.synchronize()
+    assert torch.equal(ss_a, ss_b)
+    for k in par:
+        assert torch.allclose(a[k], b[k], rtol=1e-6, atol=1e-7), (k, float((a[k] - b[k]).abs().max()))
+    # (moments: b1 m + (1 - b1) g cancels for some elements, so the bar is absolute; the two kernels may contract differently)
+    assert torch.allclose(st_a, st_b, rtol=1e-6, atol=1e-6), float((st_a - st_b).abs().max())
+    # arguments that cannot be moved as float4 are refused
+    ptrs = [b[k].data_ptr() for k in ("xyz", "feat", "opa", "ls", "rot")]
+    rc = lib.gsr_gaussian_adam_step_shared(Pp, M, M_grad, M_upd, 2, 8, 0, 0, ss_b.data_ptr(), 0.9, 0.999, 1e-15, lr, *ptrs, *ptrs,
+                                           *ptrs, st_b.data_ptr(), s)
+    assert rc != 0
+
+
+def test_densify_stats_alone_match_the_reference_update():
+    from diff_gaussian_rasterization._cabi import check, lib
+    P = 4321
+    g = torch.Generator().manual_seed(5)
+    m2 = torch.randn(P, 3, generator=g).to(DEV)
+    radii = (torch.rand(P, generator=g) * 20 - 5).clamp(min=0).int().to(DEV)
+    accum = torch.rand(P, generator=g).to(DEV); denom = torch.ones(P, device=DEV); maxr = torch.full((P,), 3.0, device=DEV)
+    want_a, want_d, want_m = accum.clone(), denom.clone(), maxr.clone()
+    vis = radii > 0
+    want_a[vis] += torch.norm(m2[vis, :2], dim=-1); want_d[vis] += 1; want_m[vis] = torch.max(want_m[vis], radii[vis].float())
+    check(lib.gsr_densify_stats(P, m2.data_ptr(), radii.data_ptr(), accum.data_ptr(), denom.data_ptr(), maxr.data_ptr(),
+                                torch.cuda.current_stream().cuda_stream))
+    assert float((accum - want_a).abs().max()) <= 1e-6 and torch.equal(denom, want_d) and torch.equal(maxr, want_m)
