@@ -253,23 +253,39 @@ def run_loops(dev, rank, world):
                             "max_pose_err_r_deg": line["max_pose_err_r_deg"], "binning_overflow": bool(overflow),
                             "what": "examples/cf3dgs_pair.py --graph: 518 k-Gaussian local models at 960x540, 2 pairs per GPU, "
                                     "pairs sharded over the ranks, one gather of the relative poses at the end"}
-    # (ii) batched global views: replicated 1.04 M-Gaussian model, one view per rank per optimiser step, NCCL all-reduce of
-    # the flat gradient (only the active SH bands), fused Adam on every rank; at SH degree 0 and 3
+    # (ii) batched global views: replicated 1.04 M-Gaussian model, one view per rank per optimiser step, at SH degree 0 and
+    # 3.  With several ranks the optimiser step is SHARED over NVSwitch multicast when the box can (every rank sums the
+    # replicas' gradients of its 1/N of the rows with multimem.ld_reduce, steps them, and writes the new parameters to every
+    # replica with multimem.st); the NCCL form (all-reduce / reduce-scatter + all-gather) is timed beside it.
     for deg in (0, 3):
-        gargs = CG.default_config(frames=8, points_per_frame=130_000, iters=100, sh_degree=deg, batched=True, warmup=10)
+        gargs = CG.default_config(frames=8, points_per_frame=130_000, iters=100, sh_degree=deg, batched=True, warmup=10,
+                                  multicast="auto" if world > 1 else "off")
         g = CG.run_global(gargs, dev, rank, world)
+        shared = g.get("shared_step_multicast") == "in use"      # the same answer on every rank (gsr_parallel agrees on it)
         if rank == 0:
             out[f"global_views_iters_per_s_sh{deg}"] = g["iters_per_s"]
             out[f"global_views_per_s_sh{deg}"] = g["views_per_s"]
             out.setdefault("global_views_loop", {})[f"sh{deg}"] = {
-                "P": g["P"], "allreduce_bytes": g["allreduce_bytes"] if world > 1 else 0,
+                "P": g["P"], "gradient_bytes_per_replica": g["allreduce_bytes"] if world > 1 else 0,
                 "floats_per_gaussian": g["allreduce_floats_per_gaussian"], "replicas_bit_identical": g["replicas_bit_identical"],
-                "ms_per_iter": g["ms_per_iter"], "last_loss": g["last_loss"]}
+                "ms_per_iter": g["ms_per_iter"], "last_loss": g["last_loss"],
+                "step": ("shared over NVSwitch multicast" if shared else
+                         "NCCL" + (f" ({g.get('shared_step_multicast')})" if world > 1 else " not needed: one rank"))}
+        done_nccl = not shared
+        if world > 1 and not done_nccl:
+            gargs = CG.default_config(frames=8, points_per_frame=130_000, iters=100, sh_degree=deg, batched=True, warmup=10,
+                                      multicast="off")
+            g = CG.run_global(gargs, dev, rank, world)
+            if rank == 0:
+                out[f"global_views_nccl_iters_per_s_sh{deg}"] = g["iters_per_s"]
+                out["global_views_loop"][f"sh{deg}"]["nccl_form_ms_per_iter"] = g["ms_per_iter"]
+                out["global_views_loop"][f"sh{deg}"]["nccl_form_replicas_bit_identical"] = g["replicas_bit_identical"]
     if rank == 0:
         out["global_views_loop"]["what"] = ("examples/cf3dgs_global.py --batched: full iteration (activations, render, fused "
-                                            "L1+SSIM, backward into the flat buffer, NCCL sum of the gradients -- one all-reduce at SH "
-                                            "degree 0; at degree 3 the SH rows are reduce-scattered, stepped on 1/N of the rows per "
-                                            "rank and all-gathered -- fused Adam, densification statistics), 960x540, 8 training views")
+                                            "L1+SSIM, backward into the flat buffer, the optimiser step over the sum of the "
+                                            "replicas' gradients, densification statistics), 960x540, 8 training views; the "
+                                            "NCCL form is one all-reduce at SH degree 0 and, at degree 3, all-reduce of the "
+                                            "geometry block + reduce-scatter / Adam on 1/N of the SH rows / all-gather")
     return out
 
 

@@ -283,9 +283,13 @@ __global__ void adam_shared_gaussians_kernel(SharedStepArgs a, AdamCfg c, const 
     }
 }
 
-// SH rows [row0, row0 + rows): one thread per float4 (VEC) or per float of the first upd_floats floats of a row; see
-// adam_features_kernel for grad_floats / upd_floats.  VEC needs floats_per_gaussian, grad_floats, upd_floats % 4 == 0.
-template <bool MC, bool VEC>
+// SH rows [row0, row0 + rows); see adam_features_kernel for grad_floats / upd_floats.
+//  VEC: one thread per float4 of a row's first ceil4(upd_floats) floats (floats_per_gaussian % 4 == 0, so parameters and
+//       moments move as aligned float4).  Rounding upd_floats up touches floats that never had a gradient: their moments
+//       are zero, Adam's update of them is exactly zero, they are rewritten with their own value.  The gradient comes as
+//       one 16-byte sum when the packed row allows it (GVEC: grad_floats % 4 == 0), else float by float.
+//  !VEC: one thread per float.
+template <bool MC, bool VEC, bool GVEC>
 __global__ void adam_shared_features_kernel(size_t row0, size_t n, int floats_per_gaussian, int grad_floats, int upd_floats,
                                             const float* __restrict__ p, float* p_all, const float* g,
                                             float* __restrict__ m, float* __restrict__ v, float lr_dc, float lr_rest,
@@ -295,12 +299,21 @@ __global__ void adam_shared_features_kernel(size_t row0, size_t n, int floats_pe
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     if (bias_dev) { c.inv_bias1 = bias_dev[0]; c.inv_sqrt_bias2 = bias_dev[1]; }
-    const size_t per_row = (size_t)(upd_floats / W);
+    const size_t per_row = (size_t)((upd_floats + W - 1) / W);
     const size_t row = row0 + i / per_row;
     const int k = (int)(i % per_row) * W;
     i = row * (size_t)floats_per_gaussian + k;
+    const float* grow = g + row * (size_t)grad_floats;
     if (VEC) {
-        const float4 gi = k < grad_floats ? ld_sum4<MC>(g + row * (size_t)grad_floats + k) : make_float4(0.f, 0.f, 0.f, 0.f);
+        float4 gi = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (GVEC) {
+            if (k < grad_floats) gi = ld_sum4<MC>(grow + k);
+        } else {
+            if (k < grad_floats) gi.x = ld_sum1<MC>(grow + k);
+            if (k + 1 < grad_floats) gi.y = ld_sum1<MC>(grow + k + 1);
+            if (k + 2 < grad_floats) gi.z = ld_sum1<MC>(grow + k + 2);
+            if (k + 3 < grad_floats) gi.w = ld_sum1<MC>(grow + k + 3);
+        }
         const float4 pp = *reinterpret_cast<const float4*>(p + i);
         float4 mm = *reinterpret_cast<float4*>(m + i), vv = *reinterpret_cast<float4*>(v + i);
         float4 o;
@@ -312,11 +325,42 @@ __global__ void adam_shared_features_kernel(size_t row0, size_t n, int floats_pe
         *reinterpret_cast<float4*>(m + i) = mm;
         *reinterpret_cast<float4*>(v + i) = vv;
     } else {
-        const float gi = k < grad_floats ? ld_sum1<MC>(g + row * (size_t)grad_floats + k) : 0.f;
+        const float gi = k < grad_floats ? ld_sum1<MC>(grow + k) : 0.f;
         float mm = m[i], vv = v[i];
         st_all1<MC>(p_all + i, adam_update(p[i], gi, mm, vv, k < 3 ? lr_dc : lr_rest, c));
         m[i] = mm; v[i] = vv;
     }
+}
+
+// SH degree 0 (grad_floats == upd_floats == 3: every local CF-3DGS model, and the global one's first thousand
+// iterations): a block takes 256 rows, whose packed gradients are 192 consecutive float4 -- fetched as such (one
+// 16-byte sum per thread instead of three 4-byte ones per row) and handed to the row's thread through shared memory.
+template <bool MC>
+__global__ void __launch_bounds__(256)
+adam_shared_features_dc_kernel(int row0, int rows, int floats_per_gaussian, const float* __restrict__ p, float* p_all,
+                               const float* g, float* __restrict__ m, float* __restrict__ v, float lr_dc, float lr_rest,
+                               AdamCfg c, const float* __restrict__ bias_dev)
+{
+    __shared__ __align__(16) float sg[768];
+    const int first = blockIdx.x * 256;
+    const int nr = min(256, rows - first);                  // a multiple of 4
+    const float* gblock = g + (size_t)3 * (row0 + first);   // 16-byte aligned: row0 and first are multiples of 4
+    if ((int)threadIdx.x < 3 * nr / 4)
+        reinterpret_cast<float4*>(sg)[threadIdx.x] = ld_sum4<MC>(gblock + 4 * threadIdx.x);
+    __syncthreads();
+    if ((int)threadIdx.x >= nr) return;
+    if (bias_dev) { c.inv_bias1 = bias_dev[0]; c.inv_sqrt_bias2 = bias_dev[1]; }
+    const size_t i = (size_t)(row0 + first + threadIdx.x) * (size_t)floats_per_gaussian;
+    const float4 pp = *reinterpret_cast<const float4*>(p + i);
+    float4 mm = *reinterpret_cast<float4*>(m + i), vv = *reinterpret_cast<float4*>(v + i);
+    float4 o;
+    o.x = adam_update(pp.x, sg[3 * threadIdx.x], mm.x, vv.x, lr_dc, c);
+    o.y = adam_update(pp.y, sg[3 * threadIdx.x + 1], mm.y, vv.y, lr_dc, c);
+    o.z = adam_update(pp.z, sg[3 * threadIdx.x + 2], mm.z, vv.z, lr_dc, c);
+    o.w = adam_update(pp.w, 0.f, mm.w, vv.w, lr_rest, c);   // never had a gradient: stays what it is (see above)
+    st_all4<MC>(p_all + i, o);
+    *reinterpret_cast<float4*>(m + i) = mm;
+    *reinterpret_cast<float4*>(v + i) = vv;
 }
 
 // dst[i] = sum over the replicas of src[i], read through a multicast address (set-up check of the shared step)
@@ -543,15 +587,23 @@ extern "C" int gsr_gaussian_adam_step_shared(int P_pad, int M, int M_grad, int M
     }
     if (M_upd > 0 && rows > 0) {
         const int fpg = 3 * M, gf = 3 * M_grad, uf = 3 * M_upd;
-        const bool vec = !((fpg | gf | uf) & 3);
-        const size_t nf = (size_t)(uf / (vec ? 4 : 1)) * (size_t)rows;
+        const bool vec = !(fpg & 3), gvec = vec && !(gf & 3);
+        const size_t nf = (size_t)(vec ? (uf + 3) / 4 : uf) * (size_t)rows;
         const unsigned blocks = (unsigned)((nf + 255) / 256);
-#define GSR_FEAT(MC, VEC)                                                                                           \
-        adam_shared_features_kernel<MC, VEC><<<blocks, 256, 0, s>>>((size_t)row0, nf, fpg, gf, uf, features, features_all, \
-                                                                    d_features_sum, m_f, v_f, lrs_host[1], lrs_host[2], c, \
-                                                                    bias_dev)
-        if (multicast) { if (vec) GSR_FEAT(true, true); else GSR_FEAT(true, false); }
-        else           { if (vec) GSR_FEAT(false, true); else GSR_FEAT(false, false); }
+#define GSR_FEAT(MC, VEC, GVEC)                                                                                     \
+        adam_shared_features_kernel<MC, VEC, GVEC><<<blocks, 256, 0, s>>>((size_t)row0, nf, fpg, gf, uf, features,   \
+                                                                          features_all, d_features_sum, m_f, v_f,  \
+                                                                          lrs_host[1], lrs_host[2], c, bias_dev)
+        if (vec && gf == 3 && uf == 3 && fpg >= 4) {
+            if (multicast)
+                adam_shared_features_dc_kernel<true><<<div_up(rows, 256), 256, 0, s>>>(row0, rows, fpg, features, features_all,
+                    d_features_sum, m_f, v_f, lrs_host[1], lrs_host[2], c, bias_dev);
+            else
+                adam_shared_features_dc_kernel<false><<<div_up(rows, 256), 256, 0, s>>>(row0, rows, fpg, features, features_all,
+                    d_features_sum, m_f, v_f, lrs_host[1], lrs_host[2], c, bias_dev);
+        } else
+        if (multicast) { if (gvec) GSR_FEAT(true, true, true); else if (vec) GSR_FEAT(true, true, false); else GSR_FEAT(true, false, false); }
+        else           { if (gvec) GSR_FEAT(false, true, true); else if (vec) GSR_FEAT(false, true, false); else GSR_FEAT(false, false, false); }
 #undef GSR_FEAT
     }
     cudaError_t e = cudaGetLastError();

@@ -201,7 +201,7 @@ class BatchedViewsStep:
             so += w * m.P
             sn += w * Pp
         m.state = state
-        m.shared_step_owner = self                                 # FusedGaussianModel.step()/step_part() refuse from now on
+        m.shared_step_owner = "BatchedViewsStep"                   # FusedGaussianModel.step()/step_part() refuse from now on (a name, not the object: no reference cycle keeps the symmetric allocation alive)
         self._mc = dict(hdl=hdl, buf=buf, mc0=mc0, par=par, per=per, Pp=Pp, rows_per=rows_per, M_grad=None,
                         m2d=torch.empty((m.P, 3), dtype=torch.float32, device=dev))
         dist.barrier()
@@ -225,10 +225,7 @@ class BatchedViewsStep:
         self._mc = None
 
     def _multicast_step(self, settings, target, loss_fn, window):
-        import ctypes
         import diff_gaussian_rasterization as D
-        from diff_gaussian_rasterization._cabi import check, lib
-        from gsr_model import LR_ORDER
         m, mc = self.model, self._mc
         Pp, per, buf, P = mc["Pp"], mc["per"], mc["buf"], m.P
         deg = int(settings.sh_degree)
@@ -255,6 +252,17 @@ class BatchedViewsStep:
                          binning, img, alpha, False,
                          out=dict(means3D=gv["xyz"], means2D=mc["m2d"], opacity=gv["opacity_raw"], sh=gv["features"],
                                   scales=gv["log_scales"], rotations=gv["rot_raw"]), dsh_M=M_grad)
+        self._shared_update(M_grad, radii)
+        return loss.detach()
+
+    def _shared_update(self, M_grad: int, radii):
+        """barrier, gsr_gaussian_adam_step_shared on this rank's rows (+ the local statistics), barrier."""
+        import ctypes
+        from diff_gaussian_rasterization._cabi import check, lib
+        from gsr_model import LR_ORDER
+        m, mc = self.model, self._mc
+        Pp, per, buf, P = mc["Pp"], mc["per"], mc["buf"], m.P
+        g0 = per * Pp
         m.sh_ever = max(m.sh_ever, min(M_grad, m.M))
         m.step_count += 1
         lr = (ctypes.c_float * 6)(*[float(m.lrs[k]) for k in LR_ORDER])
@@ -272,7 +280,6 @@ class BatchedViewsStep:
             check(lib.gsr_densify_stats(P, mc["m2d"].data_ptr(), radii.data_ptr(), m.xyz_gradient_accum.data_ptr(),
                                         m.denom.data_ptr(), m.max_radii2D.data_ptr(), stream))
         mc["hdl"].barrier(channel=0)        # every replica's rows have arrived here, and mine everywhere
-        return loss.detach()
 
     def buffers(self, M_grad: int):
         m = self.model

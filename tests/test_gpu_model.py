@@ -115,7 +115,7 @@ def test_skipping_never_active_sh_bands_changes_nothing():
         assert torch.equal(getattr(full, name), getattr(lean, name)), name
 
 
-@pytest.mark.parametrize("M,M_grad,M_upd", [(16, 16, 16), (16, 1, 1), (16, 4, 9), (4, 4, 4), (16, 9, 16)])
+@pytest.mark.parametrize("M,M_grad,M_upd", [(16, 16, 16), (16, 1, 1), (16, 4, 9), (4, 4, 4), (16, 9, 16), (9, 4, 9), (1, 1, 1)])
 def test_shared_step_on_plain_addresses_equals_the_step_in_parts(M, M_grad, M_upd):
     """gsr_gaussian_adam_step_shared with multicast = 0 (plain loads and stores) over two row ranges of a padded model
     gives what gsr_gaussian_adam_step_part gives on the same arrays: the multi-GPU form differs from it only in how the
