@@ -16,6 +16,7 @@
 
 #include "../../include/gsr.h"
 #include "gsr_kernels.h"
+#include "gsr_launch.cuh"
 
 namespace gsr {
 void set_last_error(const char* msg);
@@ -56,10 +57,14 @@ __global__ void gaussian_activate_kernel(int P, const float* __restrict__ opacit
 // have gradient zero, which still decays their moments and moves the parameter by whatever the moments hold, exactly
 // like torch.optim.Adam on a zero grad.  Floats from upd_floats on are not touched at all: the caller guarantees that
 // they never had a non-zero gradient, so their moments are zero and Adam's update of them is exactly zero.
+// The moments of coefficient 0 (the three "dc" floats of a row) live in dense (P, 3) arrays of their own, m_dc / v_dc: at SH
+// degree 0 -- every local model, the global one's first thousand iterations -- they are all the step touches, and as
+// 12 bytes out of every 192-byte row of m / v they cost three partial sectors per Gaussian.  Slots 0..2 of a row of m / v
+// are unused.
 __global__ void adam_features_kernel(size_t row0, size_t n, int floats_per_gaussian, int grad_floats, int upd_floats,
                                      float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
-                                     float* __restrict__ v, float lr_dc, float lr_rest, AdamCfg c,
-                                     const float* __restrict__ bias_dev)
+                                     float* __restrict__ v, float* __restrict__ m_dc, float* __restrict__ v_dc,
+                                     float lr_dc, float lr_rest, AdamCfg c, const float* __restrict__ bias_dev)
 {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
@@ -68,9 +73,11 @@ __global__ void adam_features_kernel(size_t row0, size_t n, int floats_per_gauss
     const int k = (int)(i % (size_t)upd_floats);
     i = row * (size_t)floats_per_gaussian + k;
     const float gi = k < grad_floats ? g[row * (size_t)grad_floats + k] : 0.f;
-    float mm = m[i], vv = v[i];
+    float* const mp = k < 3 ? m_dc + 3 * row + k : m + i;
+    float* const vp = k < 3 ? v_dc + 3 * row + k : v + i;
+    float mm = *mp, vv = *vp;
     p[i] = adam_update(p[i], gi, mm, vv, k < 3 ? lr_dc : lr_rest, c);
-    m[i] = mm; v[i] = vv;
+    *mp = mm; *vp = vv;
 }
 
 struct GaussianStepArgs {
@@ -220,6 +227,9 @@ __device__ __forceinline__ float4 adam_update4(const float4 p, const float4 g, f
 template <bool MC>
 __global__ void adam_shared_gaussians_kernel(SharedStepArgs a, AdamCfg c, const float* __restrict__ bias_dev)
 {
+    // The SH kernel behind this one touches other arrays: it is launched as a programmatic dependent and may start while
+    // this grid is still running (it waits for this grid only at its very end, so that its completion implies ours).
+    pdl_trigger();
     const int rows = a.rows;
     const int n_rot = rows, n_xyz = 3 * (rows / 4), n_op = rows / 4, n_sc = 3 * (rows / 4);
     int t = blockIdx.x * blockDim.x + threadIdx.x;
@@ -292,7 +302,8 @@ __global__ void adam_shared_gaussians_kernel(SharedStepArgs a, AdamCfg c, const 
 template <bool MC, bool VEC, bool GVEC>
 __global__ void adam_shared_features_kernel(size_t row0, size_t n, int floats_per_gaussian, int grad_floats, int upd_floats,
                                             const float* __restrict__ p, float* p_all, const float* g,
-                                            float* __restrict__ m, float* __restrict__ v, float lr_dc, float lr_rest,
+                                            float* __restrict__ m, float* __restrict__ v, float* __restrict__ m_dc,
+                                            float* __restrict__ v_dc, float lr_dc, float lr_rest,
                                             AdamCfg c, const float* __restrict__ bias_dev)
 {
     constexpr int W = VEC ? 4 : 1;
@@ -315,21 +326,35 @@ __global__ void adam_shared_features_kernel(size_t row0, size_t n, int floats_pe
             if (k + 3 < grad_floats) gi.w = ld_sum1<MC>(grow + k + 3);
         }
         const float4 pp = *reinterpret_cast<const float4*>(p + i);
-        float4 mm = *reinterpret_cast<float4*>(m + i), vv = *reinterpret_cast<float4*>(v + i);
-        float4 o;
-        o.x = adam_update(pp.x, gi.x, mm.x, vv.x, k < 3 ? lr_dc : lr_rest, c);        // coefficient 0 = floats 0..2 of the row
-        o.y = adam_update(pp.y, gi.y, mm.y, vv.y, k + 1 < 3 ? lr_dc : lr_rest, c);
-        o.z = adam_update(pp.z, gi.z, mm.z, vv.z, k + 2 < 3 ? lr_dc : lr_rest, c);
-        o.w = adam_update(pp.w, gi.w, mm.w, vv.w, lr_rest, c);
+        float4 mm, vv, o;
+        if (k == 0) {   // coefficient 0 (floats 0..2 of the row) keeps its moments in the dense arrays
+            float* const md = m_dc + 3 * row;
+            float* const vd = v_dc + 3 * row;
+            mm = make_float4(md[0], md[1], md[2], m[i + 3]);
+            vv = make_float4(vd[0], vd[1], vd[2], v[i + 3]);
+            o.x = adam_update(pp.x, gi.x, mm.x, vv.x, lr_dc, c);
+            o.y = adam_update(pp.y, gi.y, mm.y, vv.y, lr_dc, c);
+            o.z = adam_update(pp.z, gi.z, mm.z, vv.z, lr_dc, c);
+            o.w = adam_update(pp.w, gi.w, mm.w, vv.w, lr_rest, c);
+            md[0] = mm.x; md[1] = mm.y; md[2] = mm.z; m[i + 3] = mm.w;
+            vd[0] = vv.x; vd[1] = vv.y; vd[2] = vv.z; v[i + 3] = vv.w;
+        } else {
+            mm = *reinterpret_cast<float4*>(m + i);
+            vv = *reinterpret_cast<float4*>(v + i);
+            o = adam_update4(pp, gi, mm, vv, lr_rest, c);
+            *reinterpret_cast<float4*>(m + i) = mm;
+            *reinterpret_cast<float4*>(v + i) = vv;
+        }
         st_all4<MC>(p_all + i, o);
-        *reinterpret_cast<float4*>(m + i) = mm;
-        *reinterpret_cast<float4*>(v + i) = vv;
     } else {
         const float gi = k < grad_floats ? ld_sum1<MC>(grow + k) : 0.f;
-        float mm = m[i], vv = v[i];
+        float* const mp = k < 3 ? m_dc + 3 * row + k : m + i;
+        float* const vp = k < 3 ? v_dc + 3 * row + k : v + i;
+        float mm = *mp, vv = *vp;
         st_all1<MC>(p_all + i, adam_update(p[i], gi, mm, vv, k < 3 ? lr_dc : lr_rest, c));
-        m[i] = mm; v[i] = vv;
+        *mp = mm; *vp = vv;
     }
+    pdl_wait();     // see adam_shared_gaussians_kernel
 }
 
 // SH degree 0 (grad_floats == upd_floats == 3: every local CF-3DGS model, and the global one's first thousand
@@ -338,7 +363,7 @@ __global__ void adam_shared_features_kernel(size_t row0, size_t n, int floats_pe
 template <bool MC>
 __global__ void __launch_bounds__(256)
 adam_shared_features_dc_kernel(int row0, int rows, int floats_per_gaussian, const float* __restrict__ p, float* p_all,
-                               const float* g, float* __restrict__ m, float* __restrict__ v, float lr_dc, float lr_rest,
+                               const float* g, float* __restrict__ m_dc, float* __restrict__ v_dc, float lr_dc,
                                AdamCfg c, const float* __restrict__ bias_dev)
 {
     __shared__ __align__(16) float sg[768];
@@ -350,17 +375,21 @@ adam_shared_features_dc_kernel(int row0, int rows, int floats_per_gaussian, cons
     __syncthreads();
     if ((int)threadIdx.x >= nr) return;
     if (bias_dev) { c.inv_bias1 = bias_dev[0]; c.inv_sqrt_bias2 = bias_dev[1]; }
-    const size_t i = (size_t)(row0 + first + threadIdx.x) * (size_t)floats_per_gaussian;
+    const size_t row = (size_t)(row0 + first + threadIdx.x);
+    const size_t i = row * (size_t)floats_per_gaussian;
     const float4 pp = *reinterpret_cast<const float4*>(p + i);
-    float4 mm = *reinterpret_cast<float4*>(m + i), vv = *reinterpret_cast<float4*>(v + i);
+    float* const md = m_dc + 3 * row;      // dense: a warp's 32 rows are 384 consecutive bytes
+    float* const vd = v_dc + 3 * row;
+    float m0 = md[0], m1 = md[1], m2 = md[2], v0 = vd[0], v1 = vd[1], v2 = vd[2];
     float4 o;
-    o.x = adam_update(pp.x, sg[3 * threadIdx.x], mm.x, vv.x, lr_dc, c);
-    o.y = adam_update(pp.y, sg[3 * threadIdx.x + 1], mm.y, vv.y, lr_dc, c);
-    o.z = adam_update(pp.z, sg[3 * threadIdx.x + 2], mm.z, vv.z, lr_dc, c);
-    o.w = adam_update(pp.w, 0.f, mm.w, vv.w, lr_rest, c);   // never had a gradient: stays what it is (see above)
+    o.x = adam_update(pp.x, sg[3 * threadIdx.x], m0, v0, lr_dc, c);
+    o.y = adam_update(pp.y, sg[3 * threadIdx.x + 1], m1, v1, lr_dc, c);
+    o.z = adam_update(pp.z, sg[3 * threadIdx.x + 2], m2, v2, lr_dc, c);
+    o.w = pp.w;                            // first float of coefficient 1: never had a gradient, rewritten as it is
     st_all4<MC>(p_all + i, o);
-    *reinterpret_cast<float4*>(m + i) = mm;
-    *reinterpret_cast<float4*>(v + i) = vv;
+    md[0] = m0; md[1] = m1; md[2] = m2;
+    vd[0] = v0; vd[1] = v1; vd[2] = v2;
+    pdl_wait();     // see adam_shared_gaussians_kernel
 }
 
 // dst[i] = sum over the replicas of src[i], read through a multicast address (set-up check of the shared step)
@@ -452,7 +481,7 @@ static int adam_step_impl(int P, int M, int M_grad, int M_upd, int what, int row
         c.inv_bias1 = (float)(1.0 / (1.0 - std::pow((double)beta1, (double)step)));
         c.inv_sqrt_bias2 = (float)(1.0 / std::sqrt(1.0 - std::pow((double)beta2, (double)step)));
     }
-    // state layout: [m | v] for rot(4P) xyz(3P) opacity(P) scale(3P) features(3MP), in that order.  The rotation moments
+    // state layout: [m | v] for rot(4P) xyz(3P) opacity(P) scale(3P) features-dc(3P) features(3MP), in that order.  The rotation moments
     // come first because the kernel moves them as float4: at 32*P bytes past a 16-byte aligned base everything behind
     // them may start at any 4-byte boundary (odd P), they may not.
     const size_t n = (size_t)P;
@@ -465,6 +494,8 @@ static int adam_step_impl(int P, int M, int M_grad, int M_upd, int what, int row
     a.m_xyz = st; st += 3 * n; a.v_xyz = st; st += 3 * n;
     a.m_op = st; st += n; a.v_op = st; st += n;
     a.m_sc = st; st += 3 * n; a.v_sc = st; st += 3 * n;
+    float* m_dc = st; st += 3 * n;
+    float* v_dc = st; st += 3 * n;
     float* m_f = st; st += 3 * (size_t)M * n;
     float* v_f = st;
     a.lr_xyz = lrs_host[0]; a.lr_op = lrs_host[3]; a.lr_sc = lrs_host[4]; a.lr_rot = lrs_host[5];
@@ -474,8 +505,8 @@ static int adam_step_impl(int P, int M, int M_grad, int M_upd, int what, int row
     if ((what & 2) && M_upd > 0 && rows > 0) {
         const size_t nf = (size_t)3 * M_upd * (size_t)rows;
         adam_features_kernel<<<(unsigned)((nf + 255) / 256), 256, 0, s>>>((size_t)row0, nf, 3 * M, 3 * M_grad, 3 * M_upd,
-                                                                      features, d_features, m_f, v_f, lrs_host[1],
-                                                                      lrs_host[2], c, bias_dev);
+                                                                      features, d_features, m_f, v_f, m_dc, v_dc,
+                                                                      lrs_host[1], lrs_host[2], c, bias_dev);
     }
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) { set_last_error(cudaGetErrorString(e)); return GSR_ERR_CUDA; }
@@ -522,7 +553,7 @@ extern "C" int gsr_gaussian_adam_step_part(int P, int M, int M_grad, int M_upd, 
 
 extern "C" size_t gsr_gaussian_adam_state_floats(int P, int M)
 {
-    return (size_t)2 * ((size_t)3 + 1 + 3 + 4 + (size_t)3 * M) * (size_t)(P > 0 ? P : 0);
+    return (size_t)2 * ((size_t)3 + 1 + 3 + 4 + 3 + (size_t)3 * M) * (size_t)(P > 0 ? P : 0);   // + 3: the dense dc moments
 }
 
 extern "C" int gsr_gaussian_adam_step_shared(int P_pad, int M, int M_grad, int M_upd, int row0, int rows, int multicast,
@@ -577,13 +608,16 @@ extern "C" int gsr_gaussian_adam_step_shared(int P_pad, int M, int M_grad, int M
     a.m_xyz = st; st += 3 * n; a.v_xyz = st; st += 3 * n;
     a.m_op = st; st += n; a.v_op = st; st += n;
     a.m_sc = st; st += 3 * n; a.v_sc = st; st += 3 * n;
+    float* m_dc = st; st += 3 * n;
+    float* v_dc = st; st += 3 * n;
     float* m_f = st; st += 3 * (size_t)M * n;
     float* v_f = st;
     a.lr_xyz = lrs_host[0]; a.lr_op = lrs_host[3]; a.lr_sc = lrs_host[4]; a.lr_rot = lrs_host[5];
     if (rows > 0) {
         const int threads = rows + 3 * (rows / 4) + rows / 4 + 3 * (rows / 4);
-        if (multicast) adam_shared_gaussians_kernel<true><<<div_up(threads, 256), 256, 0, s>>>(a, c, bias_dev);
-        else adam_shared_gaussians_kernel<false><<<div_up(threads, 256), 256, 0, s>>>(a, c, bias_dev);
+        chain_break();      // ordinary launch: waits for everything before it in the stream
+        if (multicast) launch_pdl(adam_shared_gaussians_kernel<true>, div_up(threads, 256), 256, 0, s, a, c, bias_dev);
+        else launch_pdl(adam_shared_gaussians_kernel<false>, div_up(threads, 256), 256, 0, s, a, c, bias_dev);
     }
     if (M_upd > 0 && rows > 0) {
         const int fpg = 3 * M, gf = 3 * M_grad, uf = 3 * M_upd;
@@ -591,21 +625,21 @@ extern "C" int gsr_gaussian_adam_step_shared(int P_pad, int M, int M_grad, int M
         const size_t nf = (size_t)(vec ? (uf + 3) / 4 : uf) * (size_t)rows;
         const unsigned blocks = (unsigned)((nf + 255) / 256);
 #define GSR_FEAT(MC, VEC, GVEC)                                                                                     \
-        adam_shared_features_kernel<MC, VEC, GVEC><<<blocks, 256, 0, s>>>((size_t)row0, nf, fpg, gf, uf, features,   \
-                                                                          features_all, d_features_sum, m_f, v_f,  \
-                                                                          lrs_host[1], lrs_host[2], c, bias_dev)
+        launch_pdl(adam_shared_features_kernel<MC, VEC, GVEC>, blocks, 256, 0, s, (size_t)row0, nf, fpg, gf, uf,      \
+                   features, features_all, d_features_sum, m_f, v_f, m_dc, v_dc, lrs_host[1], lrs_host[2], c, bias_dev)
         if (vec && gf == 3 && uf == 3 && fpg >= 4) {
             if (multicast)
-                adam_shared_features_dc_kernel<true><<<div_up(rows, 256), 256, 0, s>>>(row0, rows, fpg, features, features_all,
-                    d_features_sum, m_f, v_f, lrs_host[1], lrs_host[2], c, bias_dev);
+                launch_pdl(adam_shared_features_dc_kernel<true>, div_up(rows, 256), 256, 0, s, row0, rows, fpg, features,
+                           features_all, d_features_sum, m_dc, v_dc, lrs_host[1], c, bias_dev);
             else
-                adam_shared_features_dc_kernel<false><<<div_up(rows, 256), 256, 0, s>>>(row0, rows, fpg, features, features_all,
-                    d_features_sum, m_f, v_f, lrs_host[1], lrs_host[2], c, bias_dev);
+                launch_pdl(adam_shared_features_dc_kernel<false>, div_up(rows, 256), 256, 0, s, row0, rows, fpg, features,
+                           features_all, d_features_sum, m_dc, v_dc, lrs_host[1], c, bias_dev);
         } else
         if (multicast) { if (gvec) GSR_FEAT(true, true, true); else if (vec) GSR_FEAT(true, true, false); else GSR_FEAT(true, false, false); }
         else           { if (gvec) GSR_FEAT(false, true, true); else if (vec) GSR_FEAT(false, true, false); else GSR_FEAT(false, false, false); }
 #undef GSR_FEAT
     }
+    chain_break();
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) { set_last_error(cudaGetErrorString(e)); return GSR_ERR_CUDA; }
     return GSR_OK;

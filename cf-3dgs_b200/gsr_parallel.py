@@ -196,7 +196,7 @@ class BatchedViewsStep:
             setattr(m, name, dst[:m.P])
         state = torch.zeros(lib.gsr_gaussian_adam_state_floats(Pp, m.M), dtype=torch.float32, device=dev)
         so, sn = 0, 0
-        for w in (4, 4, 3, 3, 1, 1, 3, 3, 3 * m.M, 3 * m.M):       # the moment arrays, from P rows each to P_pad rows each
+        for w in (4, 4, 3, 3, 1, 1, 3, 3, 3, 3, 3 * m.M, 3 * m.M):       # the moment arrays, from P rows each to P_pad rows each
             state[sn:sn + w * m.P].copy_(old_state[so:so + w * m.P])
             so += w * m.P
             sn += w * Pp
@@ -216,7 +216,7 @@ class BatchedViewsStep:
             setattr(m, name, getattr(m, name).clone())
         state = torch.zeros(_state_floats(P, m.M), dtype=torch.float32, device=m.xyz.device)
         so, sn = 0, 0
-        for w in (4, 4, 3, 3, 1, 1, 3, 3, 3 * m.M, 3 * m.M):
+        for w in (4, 4, 3, 3, 1, 1, 3, 3, 3, 3, 3 * m.M, 3 * m.M):
             state[sn:sn + w * P].copy_(m.state[so:so + w * P])
             so += w * Pp
             sn += w * P
@@ -352,7 +352,7 @@ class BatchedViewsStep:
 
 
 def _state_floats(P: int, M: int) -> int:
-    return 2 * (11 + 3 * M) * max(P, 0)
+    return 2 * (14 + 3 * M) * max(P, 0)
 
 
 def shard_pairs(n_pairs: int, rank: int, world: int) -> List[int]:

@@ -43,6 +43,31 @@ def main():
         Mg = (deg + 1) ** 2
         model.sh_ever = Mg
         out[f"shared_update_sh{deg}_ms"] = timed(lambda: bvs._shared_update(Mg, radii))
+    # the pieces: the per-Gaussian block alone (no SH rows), and the same kernels on plain addresses (no NVLink at all)
+    import ctypes
+    from diff_gaussian_rasterization._cabi import check, lib
+    lr = (ctypes.c_float * 6)(1.6e-4, 2.5e-3, 1.25e-4, 0.05, 5e-3, 1e-3)
+    Pp, per, buf = mc["Pp"], mc["per"], mc["buf"]
+    order = ("xyz", "features", "opacity_raw", "log_scales", "rot_raw")
+    local = [buf.data_ptr() + 4 * mc["par"][k][0] for k in order]
+    mcp = [mc["mc0"] + 4 * mc["par"][k][0] for k in order]
+    lgrad = [buf.data_ptr() + 4 * (per * Pp + mc["par"][k][0]) for k in order]
+    mgrad = [mc["mc0"] + 4 * (per * Pp + mc["par"][k][0]) for k in order]
+
+    def raw(multicast, M_grad, M_upd):
+        s = torch.cuda.current_stream().cuda_stream
+        mc["hdl"].barrier(channel=0)
+        check(lib.gsr_gaussian_adam_step_shared(Pp, M, M_grad, M_upd, rank * mc["rows_per"], mc["rows_per"], int(multicast), 1,
+                                                model.step_state.data_ptr(), 0.9, 0.999, 1e-15, lr, *local,
+                                                *(mcp if multicast else local), *(mgrad if multicast else lgrad),
+                                                model.state.data_ptr(), s))
+        mc["hdl"].barrier(channel=0)
+    out["geometry_only_multicast_ms"] = timed(lambda: raw(True, 1, 0))
+    out["geometry_only_plain_ms"] = timed(lambda: raw(False, 1, 0))
+    out["sh0_multicast_ms"] = timed(lambda: raw(True, 1, 1))
+    out["sh0_plain_ms"] = timed(lambda: raw(False, 1, 1))
+    out["sh3_multicast_ms"] = timed(lambda: raw(True, 16, 16))
+    out["sh3_plain_ms"] = timed(lambda: raw(False, 16, 16))
     ok = gsr_parallel.assert_replicas_identical([model.xyz, model.features, model.opacity_raw, model.log_scales, model.rot_raw])
     out["replicas_bit_identical"] = ok
     if rank == 0:
