@@ -164,25 +164,39 @@ class BatchedViewsStep:
         rows_per = -(-(-(-m.P // W)) // 4) * 4            # rows per rank, a multiple of 4: every range moves as float4
         Pp = rows_per * W
         per = 11 + 3 * m.M                                 # floats per Gaussian: parameters, and again gradients
-        buf = symm.empty(2 * per * Pp, dtype=torch.float32, device=dev)
-        hdl = symm.rendezvous(buf, dist.group.WORLD)
-        mc0 = int(hdl.multicast_ptr)
-        if mc0 == 0:
-            raise RuntimeError("the symmetric allocation has no multicast address on this system")
-        mc0 += buf.data_ptr() - int(hdl.buffer_ptrs[hdl.rank])
+        need = 2 * per * Pp
+        # The symmetric allocation is kept and reused when the Gaussian count changes (densification rebuilds the model
+        # every 100 iterations; allocating and binding a new multicast object costs ~0.1 s): it is made with 30 % headroom
+        # and replaced only when a model outgrows it.  Every rank takes the same decision (same P, same history).
+        key = (dev.index, W)
+        cached = _SYMM_CACHE.get(key)
+        if cached is not None and cached["floats"] >= need:
+            whole, hdl, mc_base = cached["buf"], cached["hdl"], cached["mc0"]
+        else:
+            _SYMM_CACHE.pop(key, None)
+            cached = None
+            whole = symm.empty(int(need * 1.3) // 4 * 4, dtype=torch.float32, device=dev)
+            hdl = symm.rendezvous(whole, dist.group.WORLD)
+            mc_base = int(hdl.multicast_ptr)
+            if mc_base == 0:
+                raise RuntimeError("the symmetric allocation has no multicast address on this system")
+            mc_base += whole.data_ptr() - int(hdl.buffer_ptrs[hdl.rank])
+        buf, mc0 = whole[:need], mc_base
         buf.zero_()
-        # self-check of the address arithmetic and of the switch: every rank writes rank + 1, the multicast read must
-        # return 1 + 2 + ... + W on every rank
-        probe_n = 4 * 64
-        buf[:probe_n].fill_(float(self.rank + 1))
-        got = torch.empty(probe_n, dtype=torch.float32, device=dev)
-        hdl.barrier(channel=0)
-        check(lib.gsr_multicast_probe(mc0, got.data_ptr(), probe_n, torch.cuda.current_stream().cuda_stream))
-        hdl.barrier(channel=0)
-        want = float(W * (W + 1) // 2)
-        if not bool((got == want).all()):
-            raise RuntimeError(f"multicast probe read {float(got[0])}, expected {want}")
-        buf[:probe_n].zero_()
+        if cached is None:
+            # self-check of the address arithmetic and of the switch: every rank writes rank + 1, the multicast read must
+            # return 1 + 2 + ... + W on every rank
+            probe_n = 4 * 64
+            buf[:probe_n].fill_(float(self.rank + 1))
+            got = torch.empty(probe_n, dtype=torch.float32, device=dev)
+            hdl.barrier(channel=0)
+            check(lib.gsr_multicast_probe(mc0, got.data_ptr(), probe_n, torch.cuda.current_stream().cuda_stream))
+            hdl.barrier(channel=0)
+            want = float(W * (W + 1) // 2)
+            if not bool((got == want).all()):
+                raise RuntimeError(f"multicast probe read {float(got[0])}, expected {want}")
+            buf[:probe_n].zero_()
+            _SYMM_CACHE[key] = dict(buf=whole, hdl=hdl, mc0=mc_base, floats=whole.numel())
         off, par, grd = 0, {}, {}
         for name, w in self._WIDTHS + (("features", 3 * m.M),):
             par[name] = (off, w)
@@ -204,7 +218,7 @@ class BatchedViewsStep:
         m.shared_step_owner = "BatchedViewsStep"                   # FusedGaussianModel.step()/step_part() refuse from now on (a name, not the object: no reference cycle keeps the symmetric allocation alive)
         self._mc = dict(hdl=hdl, buf=buf, mc0=mc0, par=par, per=per, Pp=Pp, rows_per=rows_per, M_grad=None,
                         m2d=torch.empty((m.P, 3), dtype=torch.float32, device=dev))
-        dist.barrier()
+        hdl.barrier(channel=0)     # nobody's first shared step writes into a buffer that is still being filled
 
     def _release_multicast(self):
         """Back to ordinary tensors (used when another rank could not set the shared step up)."""
@@ -349,6 +363,14 @@ class BatchedViewsStep:
         n_feat = self.rows_per * m.M * 3
         dist.all_gather_into_tensor(store, store[self.rank * n_feat:(self.rank + 1) * n_feat])   # everyone's updated rows
         return loss.detach()
+
+
+_SYMM_CACHE: Dict[tuple, dict] = {}     # (device index, world size) -> the symmetric allocation of the shared step
+
+
+def release_symmetric_memory() -> None:
+    """Drop the cached symmetric allocation (call on every rank, with no BatchedViewsStep in use)."""
+    _SYMM_CACHE.clear()
 
 
 def _state_floats(P: int, M: int) -> int:
