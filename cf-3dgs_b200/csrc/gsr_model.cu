@@ -392,6 +392,28 @@ adam_shared_features_dc_kernel(int row0, int rows, int floats_per_gaussian, cons
     pdl_wait();     // see adam_shared_gaussians_kernel
 }
 
+// A one-coefficient SH tensor (M = 1: the dense coefficient-0 plane a model keeps while it is trained at SH degree 0,
+// gsr_model.py shs()): parameters, gradients and the dense dc moments are all (P, 3), so the rows of a replica are one
+// flat range of float4 -- the same stream as xyz.
+template <bool MC>
+__global__ void adam_shared_dc_plane_kernel(size_t f0, int n4, const float* __restrict__ p, float* p_all, const float* g,
+                                            float* __restrict__ m_dc, float* __restrict__ v_dc, float lr_dc, AdamCfg c,
+                                            const float* __restrict__ bias_dev)
+{
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < n4) {
+        if (bias_dev) { c.inv_bias1 = bias_dev[0]; c.inv_sqrt_bias2 = bias_dev[1]; }
+        const size_t f = f0 + (size_t)4 * t;
+        const float4 pp = *reinterpret_cast<const float4*>(p + f);
+        const float4 gi = ld_sum4<MC>(g + f);
+        float4 mm = *reinterpret_cast<float4*>(m_dc + f), vv = *reinterpret_cast<float4*>(v_dc + f);
+        st_all4<MC>(p_all + f, adam_update4(pp, gi, mm, vv, lr_dc, c));
+        *reinterpret_cast<float4*>(m_dc + f) = mm;
+        *reinterpret_cast<float4*>(v_dc + f) = vv;
+    }
+    pdl_wait();     // see adam_shared_gaussians_kernel
+}
+
 // dst[i] = sum over the replicas of src[i], read through a multicast address (set-up check of the shared step)
 __global__ void multicast_probe_kernel(const float* mc_src, float* __restrict__ dst, int n4)
 {
@@ -627,7 +649,15 @@ extern "C" int gsr_gaussian_adam_step_shared(int P_pad, int M, int M_grad, int M
 #define GSR_FEAT(MC, VEC, GVEC)                                                                                     \
         launch_pdl(adam_shared_features_kernel<MC, VEC, GVEC>, blocks, 256, 0, s, (size_t)row0, nf, fpg, gf, uf,      \
                    features, features_all, d_features_sum, m_f, v_f, m_dc, v_dc, lrs_host[1], lrs_host[2], c, bias_dev)
-        if (vec && gf == 3 && uf == 3 && fpg >= 4) {
+        if (fpg == 3 && gf == 3 && uf == 3) {
+            const int n4 = 3 * (rows / 4);
+            if (multicast)
+                launch_pdl(adam_shared_dc_plane_kernel<true>, div_up(n4, 256), 256, 0, s, (size_t)3 * row0, n4, features,
+                           features_all, d_features_sum, m_dc, v_dc, lrs_host[1], c, bias_dev);
+            else
+                launch_pdl(adam_shared_dc_plane_kernel<false>, div_up(n4, 256), 256, 0, s, (size_t)3 * row0, n4, features,
+                           features_all, d_features_sum, m_dc, v_dc, lrs_host[1], c, bias_dev);
+        } else if (vec && gf == 3 && uf == 3 && fpg >= 4) {
             if (multicast)
                 launch_pdl(adam_shared_features_dc_kernel<true>, div_up(rows, 256), 256, 0, s, row0, rows, fpg, features,
                            features_all, d_features_sum, m_dc, v_dc, lrs_host[1], c, bias_dev);

@@ -22,7 +22,10 @@ class FusedGaussianModel:
     def __init__(self, xyz, features, opacity_raw, log_scales, rot_raw, lrs: Dict[str, float], betas=(0.9, 0.999),
                  eps: float = 1e-15, device_step: bool = False):
         self.xyz = xyz.detach().contiguous().float().clone()
-        self.features = features.detach().contiguous().float().clone()        # (P, M, 3), coefficient 0 = f_dc
+        # While the model is trained at SH degree 0, coefficient 0 lives in a dense (P, 1, 3) plane of its own (dc_mode,
+        # see shs()); `features` is then brought up to date whenever it is read.
+        self.features_dc, self.dc_mode, self._dc_storage = None, False, None
+        self._features = features.detach().contiguous().float().clone()       # (P, M, 3), coefficient 0 = f_dc
         self.opacity_raw = opacity_raw.detach().contiguous().float().clone()  # (P, 1)
         self.log_scales = log_scales.detach().contiguous().float().clone()    # (P, 3)
         self.rot_raw = rot_raw.detach().contiguous().float().clone()          # (P, 4)
@@ -45,6 +48,45 @@ class FusedGaussianModel:
         # the replicas: the moments then have the padded layout and only that object may step the model
         self.shared_step_owner = None
 
+    @property
+    def features(self) -> torch.Tensor:
+        """(P, M, 3) SH coefficients.  In dc_mode coefficient 0 is copied in from the dense plane first (a strided write of
+        12 bytes per Gaussian: for evaluation, densification, checkpoints -- not for the training loop, which uses shs())."""
+        if self.dc_mode:
+            self._features[:, 0].copy_(self.features_dc[:, 0])
+        return self._features
+
+    @features.setter
+    def features(self, t: torch.Tensor) -> None:
+        self._features = t
+        self.features_dc, self.dc_mode = None, False
+
+    def shs(self, sh_degree: int) -> torch.Tensor:
+        """The tensor to hand to the rasterizer as `shs` at this SH degree.  At degree 0 only coefficient 0 is read, and of
+        a (P, 16, 3) tensor that is 12 bytes out of every 192 -- for the rasterizer, for the SH gradient it writes back and
+        for Adam.  So at degree 0 (every CF-3DGS local model, the global one's first thousand iterations) the model hands
+        out a dense (P, 1, 3) plane that holds coefficient 0 and is what step() updates (dc_mode); the first call with a
+        higher degree copies it back into `features` and leaves the mode.  The reference keeps _features_dc and
+        _features_rest apart for its optimiser groups and concatenates them for every render
+        (scene/gaussian_model_cf.py:130-160)."""
+        if int(sh_degree) == 0 and self.M > 1:
+            if not self.dc_mode:
+                src = self._features[:, :1]
+                if self._dc_storage is not None:
+                    self._dc_storage.copy_(src)
+                    self.features_dc = self._dc_storage
+                else:
+                    self.features_dc = src.contiguous()
+                self.dc_mode = True
+            return self.features_dc
+        self._leave_dc()
+        return self._features
+
+    def _leave_dc(self) -> None:
+        if self.dc_mode:
+            self._features[:, 0].copy_(self.features_dc[:, 0])
+            self.features_dc, self.dc_mode = None, False
+
     def activated(self) -> Dict[str, torch.Tensor]:
         """opacities (P,1), scales (P,3), rotations (P,4) for the rasterizer (fresh tensors, no autograd history)."""
         dev = self.xyz.device
@@ -64,6 +106,13 @@ class FusedGaussianModel:
         bands have gradient zero; as long as they never had another, their moments are zero and they are skipped."""
         if self.shared_step_owner is not None:
             raise RuntimeError("this model is stepped by a BatchedViewsStep (shared step): call that object")
+        if self.dc_mode and not (self.step_state is not None and d_features is not None and d_features.shape[1] == 1):
+            self._leave_dc()      # a gradient for the full tensor: coefficient 0 goes back where that gradient points
+        if d_features is not None and d_features.shape[1] == 1 and self.M > 1:
+            if not self.dc_mode:
+                raise ValueError("a (P,1,3) SH gradient belongs to the tensor shs(0) hands out (device_step=True): render "
+                                 "from model.shs(0)")
+            sh_degree = 0
         if sh_degree is not None and self.step_state is not None and d_features is not None:
             grads = dict(means3D=d_xyz.contiguous(), sh=d_features.contiguous(), opacity=d_opacities.contiguous(),
                          scales=d_scales.contiguous(), rotations=d_rotations.contiguous())
@@ -75,7 +124,7 @@ class FusedGaussianModel:
         lr = (ctypes.c_float * 6)(*[float(self.lrs[k]) for k in LR_ORDER])
         stats = d_means2D is not None and radii is not None
         p = lambda t: None if t is None else t.contiguous().data_ptr()
-        tail = (self.xyz.data_ptr(), self.features.data_ptr(), self.opacity_raw.data_ptr(), self.log_scales.data_ptr(),
+        tail = (self.xyz.data_ptr(), self._features.data_ptr(), self.opacity_raw.data_ptr(), self.log_scales.data_ptr(),
                 self.rot_raw.data_ptr(), p(d_xyz), p(d_features), p(d_opacities), p(d_scales), p(d_rotations),
                 self.state.data_ptr(), p(d_means2D) if stats else None, p(radii) if stats else None,
                 self.xyz_gradient_accum.data_ptr() if stats else None, self.denom.data_ptr() if stats else None,
@@ -99,6 +148,12 @@ class FusedGaussianModel:
         if self.shared_step_owner is not None:
             raise RuntimeError("this model is stepped by a BatchedViewsStep (shared step): call that object")
         rows = self.P if rows is None else rows
+        # dc_mode: the gradient is that of the dense coefficient-0 plane; the same call with M = 1 steps it (the moment
+        # arrays of coefficient 0 sit in front of the other SH moments, where a one-coefficient model has its own)
+        dc = self.dc_mode and int(M_grad) == 1 and (active is None or int(active) == 1)
+        if self.dc_mode and not dc:
+            self._leave_dc()
+        M_call, feat = (1, self.features_dc) if dc else (self.M, self._features)
         # active: coefficients that can hold a non-zero gradient in this step (default: all M_grad of them)
         self.sh_ever = max(self.sh_ever, min(int(M_grad), self.M) if active is None else min(int(active), self.M))
         if tick:
@@ -107,10 +162,10 @@ class FusedGaussianModel:
         stats = bool(what & 1) and d_means2D is not None and radii is not None
         with torch.cuda.device(self.xyz.device):
             check(lib.gsr_gaussian_adam_step_part(
-                self.P, self.M, int(M_grad), int(self.sh_ever), int(what), int(row0), int(rows), int(bool(tick)),
+                self.P, M_call, int(M_grad), min(int(self.sh_ever), M_call), int(what), int(row0), int(rows), int(bool(tick)),
                 self.step_state.data_ptr(),
                 float(self.betas[0]), float(self.betas[1]), float(self.eps), lr,
-                self.xyz.data_ptr(), self.features.data_ptr(), self.opacity_raw.data_ptr(), self.log_scales.data_ptr(),
+                self.xyz.data_ptr(), feat.data_ptr(), self.opacity_raw.data_ptr(), self.log_scales.data_ptr(),
                 self.rot_raw.data_ptr(), grads["means3D"].data_ptr(), grads["sh"].data_ptr(), grads["opacity"].data_ptr(),
                 grads["scales"].data_ptr(), grads["rotations"].data_ptr(), self.state.data_ptr(),
                 d_means2D.data_ptr() if stats else None, radii.data_ptr() if stats else None,

@@ -163,7 +163,9 @@ class BatchedViewsStep:
         dev = m.xyz.device
         rows_per = -(-(-(-m.P // W)) // 4) * 4            # rows per rank, a multiple of 4: every range moves as float4
         Pp = rows_per * W
-        per = 11 + 3 * m.M                                 # floats per Gaussian: parameters, and again gradients
+        m._leave_dc()
+        per = 11 + 3 * m.M + 3                             # floats per Gaussian: parameters (+ the dense coefficient-0 plane
+                                                           # of SH degree 0, gsr_model.FusedGaussianModel.shs), and again gradients
         need = 2 * per * Pp
         # The symmetric allocation is kept and reused when the Gaussian count changes (densification rebuilds the model
         # every 100 iterations; allocating and binding a new multicast object costs ~0.1 s): it is made with 30 % headroom
@@ -198,12 +200,16 @@ class BatchedViewsStep:
             buf[:probe_n].zero_()
             _SYMM_CACHE[key] = dict(buf=whole, hdl=hdl, mc0=mc_base, floats=whole.numel())
         off, par, grd = 0, {}, {}
-        for name, w in self._WIDTHS + (("features", 3 * m.M),):
+        for name, w in self._WIDTHS + (("features", 3 * m.M), ("features_dc", 3)):
             par[name] = (off, w)
             off += w * Pp
         # re-home the parameters: the model's tensors become views of the first P rows of the symmetric arrays
         old_state = m.state
+        o_dc = par["features_dc"][0]
+        m._dc_storage = buf[o_dc:o_dc + 3 * Pp].view(Pp, 1, 3)[:m.P]      # where shs(0) will keep coefficient 0
         for name, (o, w) in par.items():
+            if name == "features_dc":
+                continue
             src = getattr(m, name)
             dst = buf[o:o + w * Pp].view((Pp,) + tuple(src.shape[1:]))
             dst[:m.P].copy_(src)
@@ -226,8 +232,11 @@ class BatchedViewsStep:
         if mc is None:
             return
         Pp, P = mc["Pp"], m.P
+        m._leave_dc()
+        m._dc_storage = None
         for name in mc["par"]:
-            setattr(m, name, getattr(m, name).clone())
+            if name != "features_dc":
+                setattr(m, name, getattr(m, name).clone())
         state = torch.zeros(_state_floats(P, m.M), dtype=torch.float32, device=m.xyz.device)
         so, sn = 0, 0
         for w in (4, 4, 3, 3, 1, 1, 3, 3, 3, 3, 3 * m.M, 3 * m.M):
@@ -248,23 +257,28 @@ class BatchedViewsStep:
         if mc["M_grad"] != M_grad:                                 # the packing of the SH gradient changes with the degree
             buf[g0 + 11 * Pp:].zero_()
             mc["M_grad"] = M_grad
+        feat = m.shs(deg)            # degree 0: the dense coefficient-0 plane, which lives in the symmetric buffer too
+        sh_key = "features_dc" if m.dc_mode else "features"
         gv = {}
         for name, (o, w) in mc["par"].items():
-            w = 3 * M_grad if name == "features" else w
-            gv[name] = buf[g0 + o:g0 + o + w * P].view((P, M_grad, 3) if name == "features" else (P, w))
+            if name in ("features", "features_dc"):
+                if name == sh_key:
+                    gv["sh"] = buf[g0 + o:g0 + o + 3 * M_grad * P].view(P, M_grad, 3)
+            else:
+                gv[name] = buf[g0 + o:g0 + o + w * P].view(P, w)
         act = m.activated()
         e = torch.Tensor([])
         rs = settings
         R, color, depth, alpha, radii, geom, binning, img = D._forward_impl(
             rs.bg, m.xyz, e, act["opacities"], act["scales"], act["rotations"], rs.scale_modifier, e, rs.viewmatrix,
-            rs.projmatrix, rs.tanfovx, rs.tanfovy, rs.image_height, rs.image_width, m.features, deg, rs.campos, False, False)
+            rs.projmatrix, rs.tanfovx, rs.tanfovy, rs.image_height, rs.image_width, feat, deg, rs.campos, False, False)
         leaf = color.requires_grad_(True)
         loss = loss_fn(leaf, target, window)
         loss.backward()
         D._backward_impl(rs.bg, m.xyz, radii, e, act["scales"], act["rotations"], rs.scale_modifier, e, rs.viewmatrix,
-                         rs.projmatrix, rs.tanfovx, rs.tanfovy, leaf.grad, None, None, m.features, deg, rs.campos, geom, R,
+                         rs.projmatrix, rs.tanfovx, rs.tanfovy, leaf.grad, None, None, feat, deg, rs.campos, geom, R,
                          binning, img, alpha, False,
-                         out=dict(means3D=gv["xyz"], means2D=mc["m2d"], opacity=gv["opacity_raw"], sh=gv["features"],
+                         out=dict(means3D=gv["xyz"], means2D=mc["m2d"], opacity=gv["opacity_raw"], sh=gv["sh"],
                                   scales=gv["log_scales"], rotations=gv["rot_raw"]), dsh_M=M_grad)
         self._shared_update(M_grad, radii)
         return loss.detach()
@@ -281,7 +295,10 @@ class BatchedViewsStep:
         m.step_count += 1
         lr = (ctypes.c_float * 6)(*[float(m.lrs[k]) for k in LR_ORDER])
         local, mcast = buf.data_ptr(), mc["mc0"]
-        order = ("xyz", "features", "opacity_raw", "log_scales", "rot_raw")
+        # in dc_mode the SH tensor of the call is the dense coefficient-0 plane: a one-coefficient model (M = 1) whose
+        # moments are the dense dc arrays the state buffer keeps in front of the other SH moments
+        M_call = 1 if m.dc_mode else m.M
+        order = ("xyz", "features_dc" if m.dc_mode else "features", "opacity_raw", "log_scales", "rot_raw")
         loc = [local + 4 * mc["par"][k][0] for k in order]
         allp = [mcast + 4 * mc["par"][k][0] for k in order]
         gsum = [mcast + 4 * (g0 + mc["par"][k][0]) for k in order]
@@ -289,7 +306,8 @@ class BatchedViewsStep:
         mc["hdl"].barrier(channel=0)        # every replica's gradients are written, and nobody still reads the parameters
         with torch.cuda.device(m.xyz.device):
             check(lib.gsr_gaussian_adam_step_shared(
-                Pp, m.M, M_grad, int(m.sh_ever), self.rank * mc["rows_per"], mc["rows_per"], 1, 1, m.step_state.data_ptr(),
+                Pp, M_call, min(M_grad, M_call), min(int(m.sh_ever), M_call), self.rank * mc["rows_per"], mc["rows_per"], 1, 1,
+                m.step_state.data_ptr(),
                 float(m.betas[0]), float(m.betas[1]), float(m.eps), lr, *loc, *allp, *gsum, m.state.data_ptr(), stream))
             check(lib.gsr_densify_stats(P, mc["m2d"].data_ptr(), radii.data_ptr(), m.xyz_gradient_accum.data_ptr(),
                                         m.denom.data_ptr(), m.max_radii2D.data_ptr(), stream))
@@ -327,16 +345,17 @@ class BatchedViewsStep:
         M_grad = (deg + 1) * (deg + 1)
         flat, g = self.buffers(M_grad)
         act = m.activated()
+        feat = m.shs(deg)          # degree 0: the dense coefficient-0 plane (gsr_model.FusedGaussianModel.shs)
         e = torch.Tensor([])
         rs = settings
         R, color, depth, alpha, radii, geom, binning, img = D._forward_impl(
             rs.bg, m.xyz, e, act["opacities"], act["scales"], act["rotations"], rs.scale_modifier, e, rs.viewmatrix,
-            rs.projmatrix, rs.tanfovx, rs.tanfovy, rs.image_height, rs.image_width, m.features, deg, rs.campos, False, False)
+            rs.projmatrix, rs.tanfovx, rs.tanfovy, rs.image_height, rs.image_width, feat, deg, rs.campos, False, False)
         leaf = color.requires_grad_(True)
         loss = loss_fn(leaf, target, window)
         loss.backward()
         D._backward_impl(rs.bg, m.xyz, radii, e, act["scales"], act["rotations"], rs.scale_modifier, e, rs.viewmatrix,
-                         rs.projmatrix, rs.tanfovx, rs.tanfovy, leaf.grad, None, None, m.features, deg, rs.campos, geom, R,
+                         rs.projmatrix, rs.tanfovx, rs.tanfovy, leaf.grad, None, None, feat, deg, rs.campos, geom, R,
                          binning, img, alpha, False,
                          out=dict(means3D=g["means3D"], means2D=self._m2d, opacity=g["opacity"], sh=g["sh"],
                                   scales=g["scales"], rotations=g["rotations"]), dsh_M=M_grad)

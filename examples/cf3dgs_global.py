@@ -54,7 +54,7 @@ def frame_pose(i, n):
 
 def default_config(**kw):
     cfg = dict(frames=8, points_per_frame=130_000, iters=200, width=960, height=540, sh_degree=3, impl="ours", loss=None,
-               model=None, graph=False, batched=False, densify_every=0, psnr_every=0, profile=False, warmup=10, multicast="off")
+               model=None, graph=False, batched=False, densify_every=0, psnr_every=0, profile=False, warmup=10, multicast="off", dc_plane="on")
     cfg.update(kw)
     if cfg["model"] is None:
         cfg["model"] = "fused" if cfg["impl"] == "ours" else "torch"
@@ -163,7 +163,7 @@ def run_global(args, dev, rank=0, world=1):
         m = model
         act = m.activated()
         x = m.xyz.detach().requires_grad_(True)
-        sh = m.features.detach().requires_grad_(True)
+        sh = (m.shs(int(rs.sh_degree)) if args.dc_plane == "on" else m.features).detach().requires_grad_(True)     # degree 0: the dense coefficient-0 plane
         o, sc, r = act["opacities"].requires_grad_(True), act["scales"].requires_grad_(True), act["rotations"].requires_grad_(True)
         m2d = torch.zeros_like(x, requires_grad=True)
         import diff_gaussian_rasterization as D
@@ -377,6 +377,8 @@ def main():
     ap.add_argument("--multicast", default="off", choices=["on", "auto", "off"],
                     help="--batched: the optimiser step shared between the replicas over NVSwitch multicast (multimem loads / "
                          "stores) instead of NCCL collectives; auto = when the box supports it")
+    ap.add_argument("--dc-plane", default="on", choices=["on", "off"],
+                    help="off: render SH degree 0 from the full (P,16,3) tensor instead of the model's dense coefficient-0 plane (A/B)")
     ap.add_argument("--densify-every", type=int, default=0, help="change the Gaussian count every N iterations (0 = never)")
     ap.add_argument("--psnr-every", type=int, default=0, help="record the PSNR over 4 fixed views every N iterations")
     ap.add_argument("--c3", action="store_true", help="BASELINE configs[2] at its stated shape: 120 frames, ~1M Gaussians, "

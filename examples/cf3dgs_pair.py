@@ -124,7 +124,7 @@ def run_pair(p, args, dev, backend):
             mdl = fused_model
             act = mdl.activated()
             x = mdl.xyz.detach().requires_grad_(True)
-            sh = mdl.features.detach().requires_grad_(True)
+            sh = mdl.shs(0).detach().requires_grad_(True)     # local models stay at SH degree 0: the dense coefficient-0 plane
             o, sc_, r = act["opacities"].requires_grad_(True), act["scales"].requires_grad_(True), act["rotations"].requires_grad_(True)
             m2d = torch.zeros_like(x, requires_grad=True)
             img = D.GaussianRasterizer(rs)(x, m2d, o, shs=sh, scales=sc_, rotations=r)[0]

@@ -172,3 +172,38 @@ def test_densify_stats_alone_match_the_reference_update():
     check(lib.gsr_densify_stats(P, m2.data_ptr(), radii.data_ptr(), accum.data_ptr(), denom.data_ptr(), maxr.data_ptr(),
                                 torch.cuda.current_stream().cuda_stream))
     assert float((accum - want_a).abs().max()) <= 1e-6 and torch.equal(denom, want_d) and torch.equal(maxr, want_m)
+
+
+def test_dense_coefficient_0_plane_at_sh_degree_0_equals_stepping_the_full_tensor():
+    """shs(0) hands out a dense (P,1,3) plane and step() updates that; a model stepped with the full (P,16,3) gradient
+    (zeros above coefficient 0) must end up bit-identical -- at degree 0, after the switch to degree 1, and through the
+    `features` property at any time."""
+    import gsr_model
+    P, M = 4999, 16
+    g = torch.Generator().manual_seed(11)
+    mk = lambda *s, sc=1.0: (sc * torch.randn(*s, generator=g)).to(DEV)
+    init = (mk(P, 3), mk(P, M, 3, sc=0.3), mk(P, 1), mk(P, 3, sc=0.3) - 3, mk(P, 4))
+    A = gsr_model.FusedGaussianModel(*init, LRS, device_step=True)
+    B = gsr_model.FusedGaussianModel(*init, LRS, device_step=True)
+    for it in range(4):
+        d = dict(x=mk(P, 3), f0=mk(P, 1, 3), o=mk(P, 1), s=mk(P, 3), r=mk(P, 4))
+        sh = A.shs(0)
+        assert sh.shape == (P, 1, 3) and sh.is_contiguous() and A.dc_mode
+        A.step(d["x"], d["f0"], d["o"], d["s"], d["r"], sh_degree=0)
+        full = torch.zeros(P, M, 3, device=DEV)
+        full[:, :1] = d["f0"]
+        B.step(d["x"], full, d["o"], d["s"], d["r"], sh_degree=0)
+        assert torch.equal(A.features, B.features)            # the property brings coefficient 0 in
+    for it in range(2):
+        d = dict(x=mk(P, 3), f=mk(P, M, 3), o=mk(P, 1), s=mk(P, 3), r=mk(P, 4))
+        d["f"][:, 4:] = 0
+        assert A.shs(1).shape == (P, M, 3) and not A.dc_mode
+        for mdl in (A, B):
+            mdl.step(d["x"], d["f"], d["o"], d["s"], d["r"], sh_degree=1)
+    for a, b in zip((A.xyz, A.features, A.opacity_raw, A.log_scales, A.rot_raw),
+                    (B.xyz, B.features, B.opacity_raw, B.log_scales, B.rot_raw)):
+        assert torch.equal(a, b)
+    assert torch.equal(A.state, B.state)
+    # a (P,1,3) gradient for a model that is not in dc_mode is a caller's mistake
+    with pytest.raises(ValueError):
+        B.step(d["x"], d["f"][:, :1].contiguous(), d["o"], d["s"], d["r"], sh_degree=0)
