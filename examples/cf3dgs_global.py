@@ -54,7 +54,7 @@ def frame_pose(i, n):
 
 def default_config(**kw):
     cfg = dict(frames=8, points_per_frame=130_000, iters=200, width=960, height=540, sh_degree=3, impl="ours", loss=None,
-               model=None, graph=False, batched=False, densify_every=0, psnr_every=0, profile=False, warmup=10, multicast="off", dc_plane="on")
+               model=None, graph=False, batched=False, densify_every=0, psnr_every=0, profile=False, warmup=10, multicast="off", dc_plane="on", sh_up_every=0)
     cfg.update(kw)
     if cfg["model"] is None:
         cfg["model"] = "fused" if cfg["impl"] == "ours" else "torch"
@@ -126,6 +126,8 @@ def run_global(args, dev, rank=0, world=1):
         raise SystemExit("--batched needs --impl ours --model fused")
     if args.graph and not (fused and args.impl == "ours"):
         raise SystemExit("--graph needs --impl ours --model fused")
+    if args.graph and args.sh_up_every:
+        raise SystemExit("--sh-up-every changes the SH degree, which a captured graph has fixed")
 
     import gsr_parallel as GPar
     state = {"P": P0, "recaptures": 0, "recapture_s": 0.0, "overflow_warnings": 0, "densify_rounds": 0, "P_history": [P0]}
@@ -195,11 +197,20 @@ def run_global(args, dev, rank=0, world=1):
     def view_of(k):
         return int(order[k * world + rank]) if args.batched else int(order[k])
 
+    def settings_at(f, k):
+        """The view's settings at iteration k: with --sh-up-every N the active SH degree starts at 0 and rises by one every
+        N iterations up to --sh-degree (the reference's oneupSHdegree every 1000 iterations, trainer/cf3dgs_trainer.py:
+        335-337 with scene/gaussian_model_cf.py:174-176)."""
+        if not args.sh_up_every:
+            return settings[f]
+        return settings[f]._replace(sh_degree=min(args.sh_degree, max(k - args.warmup, 0) // args.sh_up_every))
+
     def eager_iteration(k):
         f = view_of(k)
+        rs = settings_at(f, k)
         if batched is not None:
-            return batched(settings[f], targets[f], loss_fn, window)
-        return fused_iteration_frame(settings[f], targets[f]) if fused else torch_iteration_frame(settings[f], targets[f])
+            return batched(rs, targets[f], loss_fn, window)
+        return fused_iteration_frame(rs, targets[f]) if fused else torch_iteration_frame(rs, targets[f])
 
     # ---- CUDA-graph form: ONE graph for all views; the view's camera and target are gathered on the device ----
     graph = {"g": None}
@@ -377,6 +388,8 @@ def main():
     ap.add_argument("--multicast", default="off", choices=["on", "auto", "off"],
                     help="--batched: the optimiser step shared between the replicas over NVSwitch multicast (multimem loads / "
                          "stores) instead of NCCL collectives; auto = when the box supports it")
+    ap.add_argument("--sh-up-every", type=int, default=0,
+                    help="start at SH degree 0 and raise the active degree by one every N iterations up to --sh-degree (0 = fixed)")
     ap.add_argument("--dc-plane", default="on", choices=["on", "off"],
                     help="off: render SH degree 0 from the full (P,16,3) tensor instead of the model's dense coefficient-0 plane (A/B)")
     ap.add_argument("--densify-every", type=int, default=0, help="change the Gaussian count every N iterations (0 = never)")

@@ -207,3 +207,20 @@ def test_dense_coefficient_0_plane_at_sh_degree_0_equals_stepping_the_full_tenso
     # a (P,1,3) gradient for a model that is not in dc_mode is a caller's mistake
     with pytest.raises(ValueError):
         B.step(d["x"], d["f"][:, :1].contiguous(), d["o"], d["s"], d["r"], sh_degree=0)
+
+
+def test_global_loop_with_a_rising_sh_degree_matches_the_loop_that_never_uses_the_dc_plane():
+    """examples/cf3dgs_global.py with --sh-up-every: degree 0 (dense coefficient-0 plane), then 1 and 2 (full tensor).  The
+    same loop rendering from the full tensor throughout (--dc-plane off) must give the same losses: the plane changes where
+    coefficient 0 is kept, not what is computed."""
+    import os, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    sys.path.insert(0, os.path.join(root, "examples"))
+    import cf3dgs_global as CG
+    res = {}
+    for mode in ("on", "off"):
+        args = CG.default_config(frames=4, points_per_frame=20_000, iters=45, width=320, height=180, sh_degree=2,
+                                 sh_up_every=15, warmup=3, dc_plane=mode)
+        res[mode] = CG.run_global(args, torch.device(DEV))
+    assert res["on"]["last_loss"] < 0.6 * res["on"]["first_loss"]
+    assert abs(res["on"]["last_loss"] - res["off"]["last_loss"]) <= 1e-3 * abs(res["off"]["last_loss"])

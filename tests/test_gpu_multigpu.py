@@ -35,3 +35,17 @@ def test_shared_step_over_multicast_trains_like_the_nccl_form(deg):
     assert abs(mc["first_loss"] - nccl["first_loss"]) <= 1e-5 * abs(nccl["first_loss"])
     assert abs(mc["last_loss"] - nccl["last_loss"]) <= 2e-2 * abs(nccl["last_loss"])
     assert mc["last_loss"] < 0.5 * mc["first_loss"]
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs on one NVSwitch / NVLink box")
+def test_shared_step_follows_the_sh_degree_schedule_like_the_nccl_form():
+    """Degree 0 -> 1 -> 2 during the run: the dense coefficient-0 plane is left, the packing of the SH gradient changes
+    twice, the NCCL form switches from one all-reduce to reduce-scatter / all-gather of the SH rows."""
+    extra = ["--sh-degree", "2", "--sh-up-every", "20"]
+    nccl = _run(2, extra + ["--multicast", "off"], 29623)
+    mc = _run(2, extra + ["--multicast", "auto"], 29624)
+    assert nccl["replicas_bit_identical"] and mc["replicas_bit_identical"]
+    if mc["shared_step_multicast"] != "in use":
+        pytest.skip("no multicast on this box: " + mc["shared_step_multicast"])
+    assert abs(mc["last_loss"] - nccl["last_loss"]) <= 2e-2 * abs(nccl["last_loss"])
+    assert mc["last_loss"] < 0.5 * mc["first_loss"]
