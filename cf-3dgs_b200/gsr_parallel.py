@@ -345,7 +345,14 @@ class BatchedViewsStep:
         M_grad = (deg + 1) * (deg + 1)
         flat, g = self.buffers(M_grad)
         act = m.activated()
-        feat = m.shs(deg)          # degree 0: the dense coefficient-0 plane (gsr_model.FusedGaussianModel.shs)
+        multi = self.world > 1
+        shard = multi and (self.shard_features if self.shard_features is not None else M_grad >= self.SHARD_FROM_M) \
+            and self._feat_store is not None
+        if shard:
+            m._leave_dc()          # the all-gather below moves rows of the full tensor
+            feat = m.features
+        else:
+            feat = m.shs(deg)      # degree 0: the dense coefficient-0 plane (gsr_model.FusedGaussianModel.shs)
         e = torch.Tensor([])
         rs = settings
         R, color, depth, alpha, radii, geom, binning, img = D._forward_impl(
@@ -359,9 +366,6 @@ class BatchedViewsStep:
                          binning, img, alpha, False,
                          out=dict(means3D=g["means3D"], means2D=self._m2d, opacity=g["opacity"], sh=g["sh"],
                                   scales=g["scales"], rotations=g["rotations"]), dsh_M=M_grad)
-        multi = self.world > 1
-        shard = multi and (self.shard_features if self.shard_features is not None else M_grad >= self.SHARD_FROM_M) \
-            and self._feat_store is not None
         if not shard:
             if multi:
                 dist.all_reduce(flat[:self._used])          # stream-ordered: the step below waits on the device, not the host
