@@ -121,6 +121,10 @@ class PoseOptimizer:
         c = lambda t: e if t is None else t.detach().contiguous().float()
         self.xyz, self.opacities = c(xyz), c(opacities)
         self.shs, self.colors, self.scales, self.rotations, self.cov3D = c(shs), c(colors_precomp), c(scales), c(rotations), c(cov3D_precomp)
+        if shs is not None and int(raster_settings.sh_degree) == 0 and self.shs.shape[1] > 1:
+            # the Gaussians are frozen and degree 0 reads coefficient 0 only: keep that as a dense (P,1,3) tensor instead of
+            # 12 bytes out of every row of the caller's (P,M,3)
+            self.shs = self.shs[:, :1].contiguous()
         self.T = (torch.eye(4, device=dev) if T0 is None else T0.detach().to(dev).float()).contiguous().clone()
         self.state = torch.zeros(13, device=dev)
         self.lr, self.betas, self.eps, self.lam, self.clamp = float(lr), betas, float(eps), float(lambda_dssim), int(bool(clamp))
