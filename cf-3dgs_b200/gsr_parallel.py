@@ -5,9 +5,13 @@ never split ("replicas only" inside a view); across the optimisation:
   (i)  independent frame pairs: pair i -> rank i mod world, no data-path collective while fitting, then ONE
        all-gather of the 4x4 relative poses and a sequential prefix product
        (trainer/cf3dgs_trainer.py:225-297: pose = rel_pose @ get_RT(fidx-1));
-  (ii) batched global views: every rank renders its own view of a replicated model, then one all-reduce(sum) of the
-       flat global-Gaussian gradient (xyz 3 + f_dc 3 + f_rest 45 + opacity 1 + scaling 3 + rotation 4 = 59 floats
-       per Gaussian, scene/gaussian_model_cf.py:254-266).
+  (ii) batched global views: every rank renders its own view of a replicated model, then the optimiser step runs on
+       the sum of the ranks' gradients (xyz 3 + f_dc 3 + f_rest 45 + opacity 1 + scaling 3 + rotation 4 = 59 floats
+       per Gaussian, scene/gaussian_model_cf.py:254-266; 14 at SH degree 0).  Two forms of that step
+       (BatchedViewsStep): shared over NVSwitch multicast -- each rank sums the replicas' gradients of its 1/N of
+       the rows with multimem.ld_reduce, steps them, and writes them to every replica with multimem.st
+       (gsr_gaussian_adam_step_shared on torch symmetric memory) -- or NCCL collectives (all-reduce; at SH degree >= 2
+       reduce-scatter / Adam on 1/N of the SH rows / all-gather).
 """
 from __future__ import annotations
 
@@ -85,6 +89,7 @@ class BatchedViewsStep:
     global Gaussian model (gsr_model.FusedGaussianModel, device_step=True), renders ITS view, and the gradients of all
     views are summed before the same Adam step reaches every replica.
 
+    (What follows describes the NCCL form; the multicast form is described at _setup_multicast.)
     * the rasterizer backward writes its gradients straight into slices of one flat buffer (no packing copies);
     * only the active SH bands travel (the packed gradient, dsh_M = (degree+1)^2): 14 floats per Gaussian at degree 0
       instead of 59;
