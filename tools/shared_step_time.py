@@ -42,7 +42,13 @@ def main():
     for deg in (0, 3):
         Mg = (deg + 1) ** 2
         model.sh_ever = Mg
+        model.shs(deg)             # degree 0: the dense coefficient-0 plane (in the symmetric buffer) is what gets stepped
         out[f"shared_update_sh{deg}_ms"] = timed(lambda: bvs._shared_update(Mg, radii))
+    if os.environ.get("GSR_PIECES", "1") == "0":
+        if rank == 0:
+            print(json.dumps(out), flush=True)
+        dist.destroy_process_group()
+        return
     # the pieces: the per-Gaussian block alone (no SH rows), and the same kernels on plain addresses (no NVLink at all)
     import ctypes
     from diff_gaussian_rasterization._cabi import check, lib
