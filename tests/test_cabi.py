@@ -58,6 +58,11 @@ def test_size_queries_need_no_gpu():
     assert lib.gsr_binning_bytes(1000, 640, 360) >= 16 * 1000
     assert lib.gsr_profile_count() == 9      # stages with a timer (the tile ranges come out of the tile sort)
     assert lib.gsr_profile_name(0) == b"preprocess"
+    # the moment buffer of the model step: 2 x (11 per-Gaussian floats + 3 dense dc floats + 3 M SH floats); gsr_parallel
+    # re-lays it out for the padded count of the shared multi-GPU step and must agree with the library on its size
+    import gsr_parallel
+    for P, M in [(0, 16), (1, 1), (4999, 16), (1036800, 16), (12, 4)]:
+        assert lib.gsr_gaussian_adam_state_floats(P, M) == 2 * (14 + 3 * M) * P == gsr_parallel._state_floats(P, M)
 
 
 def test_header_is_plain_c(tmp_path):
