@@ -83,3 +83,31 @@ def test_the_product_package_never_touches_the_oracle():
                 if pat.search(open(os.path.join(d, f), errors="ignore").read()):
                     offenders.append(os.path.join(d, f))
     assert not offenders, offenders
+
+
+def test_coefficient_0_plane_bookkeeping_of_the_fused_model():
+    """FusedGaussianModel.shs() / .features (host logic only, CPU tensors): at degree 0 a dense (P,1,3) plane is handed
+    out and is the truth for coefficient 0; reading `features` brings it in; a higher degree or assigning `features` ends
+    the mode.  (The kernels that update the plane are covered by tests/test_gpu_model.py.)"""
+    import torch
+    import gsr_model
+    P, M = 7, 16
+    g = torch.Generator().manual_seed(0)
+    feats = torch.randn(P, M, 3, generator=g)
+    lrs = dict(xyz=1e-4, f_dc=2.5e-3, f_rest=1.25e-4, opacity=0.05, scaling=5e-3, rotation=1e-3)
+    m = gsr_model.FusedGaussianModel(torch.randn(P, 3), feats, torch.randn(P, 1), torch.randn(P, 3), torch.randn(P, 4), lrs)
+    assert not m.dc_mode and torch.equal(m.features, feats)
+    sh0 = m.shs(0)
+    assert m.dc_mode and sh0.shape == (P, 1, 3) and sh0.is_contiguous() and torch.equal(sh0[:, 0], feats[:, 0])
+    assert m.shs(0) is sh0                              # stays the same tensor while the mode lasts
+    sh0.add_(1.0)                                       # what a step at degree 0 does: it updates the plane
+    full = m.features                                   # reading brings coefficient 0 up to date, the rest is untouched
+    assert torch.equal(full[:, 0], feats[:, 0] + 1.0) and torch.equal(full[:, 1:], feats[:, 1:]) and m.dc_mode
+    sh2 = m.shs(2)                                      # a higher degree renders from the full tensor and ends the mode
+    assert not m.dc_mode and sh2.shape == (P, M, 3) and torch.equal(sh2[:, 0], feats[:, 0] + 1.0)
+    m.shs(0).mul_(2.0)
+    m.features = torch.zeros(P, M, 3)                   # assigning a new tensor makes that tensor the truth
+    assert not m.dc_mode and float(m.features.abs().sum()) == 0.0
+    one = gsr_model.FusedGaussianModel(torch.randn(P, 3), feats[:, :1], torch.randn(P, 1), torch.randn(P, 3),
+                                       torch.randn(P, 4), lrs)
+    assert one.shs(0) is one.features and not one.dc_mode          # a one-coefficient model is dense already
